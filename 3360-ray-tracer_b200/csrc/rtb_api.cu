@@ -1,0 +1,571 @@
+// rtb_api.cu — implementation of the C ABI in include/rtb.h: scene upload, the wavefront
+// driver loop, and the batch-intersect seam.  All device work is issued on one library stream
+// per thread and timed with CUDA events on that stream.  No CPU fallback anywhere: without a
+// device every compute entry returns RTB_ENODEVICE.
+#include <rtb.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "rtb_kernels.cuh"
+
+namespace {
+
+thread_local std::string g_error;
+thread_local cudaStream_t g_stream = nullptr;
+thread_local int g_device = -1;
+thread_local int g_sm_count = 0;
+
+int Fail(int code, const std::string& msg) {
+  g_error = msg;
+  return code;
+}
+#define RTB_CUDA(call)                                                                                   \
+  do {                                                                                                   \
+    cudaError_t e_ = (call);                                                                             \
+    if (e_ != cudaSuccess)                                                                               \
+      return Fail(RTB_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_) + " (" __FILE__ ":" + std::to_string(__LINE__) + ")"); \
+  } while (0)
+
+int EnsureInit() {
+  if (g_stream) return RTB_OK;
+  return rtb_init(0);
+}
+
+template <class T>
+int Upload(const T* host, size_t n, T** dev) {
+  *dev = nullptr;
+  if (n == 0) return RTB_OK;
+  RTB_CUDA(cudaMalloc(reinterpret_cast<void**>(dev), n * sizeof(T)));
+  RTB_CUDA(cudaMemcpy(*dev, host, n * sizeof(T), cudaMemcpyHostToDevice));
+  return RTB_OK;
+}
+
+}  // namespace
+
+struct RtbScene {
+  rtb::DevScene dev{};
+  std::vector<void*> allocs;
+  std::vector<cudaArray_t> arrays;
+  std::vector<cudaTextureObject_t> textures;
+  rtb::HitCounters* counters = nullptr;
+  unsigned int* cursor = nullptr;  // persistent-thread work cursor + shade output counter (2 words)
+  unsigned int* host_count = nullptr;  // pinned
+  size_t smem_bytes = 0;
+  int device = 0;
+  // path pool (allocated lazily by rtb_render*)
+  uint32_t pool = 0;
+  rtb::PathQueue q[2]{};
+  float* hit_t = nullptr;
+  uint32_t* hit_ref = nullptr;
+  uint32_t* pixel_order = nullptr;
+  int order_w = 0, order_h = 0;
+
+  template <class T>
+  int Put(const T* host, size_t n, const T** out) {
+    T* d = nullptr;
+    int rc = Upload(host, n, &d);
+    if (rc != RTB_OK) return rc;
+    if (d) allocs.push_back(d);
+    *out = d;
+    return RTB_OK;
+  }
+};
+
+extern "C" {
+
+const char* rtb_last_error(void) { return g_error.c_str(); }
+int rtb_abi_version(void) { return RTB_ABI_VERSION; }
+
+int rtb_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+int rtb_init(int device) {
+  const int n = rtb_device_count();
+  if (n <= 0) return Fail(RTB_ENODEVICE, "no CUDA device visible; this library has no CPU path");
+  if (device < 0 || device >= n) return Fail(RTB_EINVAL, "device index out of range");
+  RTB_CUDA(cudaSetDevice(device));
+  if (g_stream && g_device == device) return RTB_OK;
+  if (g_stream) cudaStreamDestroy(g_stream);
+  RTB_CUDA(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking));
+  cudaDeviceProp prop;
+  RTB_CUDA(cudaGetDeviceProperties(&prop, device));
+  g_sm_count = prop.multiProcessorCount;
+  g_device = device;
+  return RTB_OK;
+}
+
+int rtb_shutdown(void) {
+  if (g_stream) {
+    cudaStreamSynchronize(g_stream);
+    cudaStreamDestroy(g_stream);
+    g_stream = nullptr;
+    g_device = -1;
+  }
+  return RTB_OK;
+}
+
+int rtb_scene_destroy(RtbScene* s) {
+  if (!s) return RTB_OK;
+  cudaSetDevice(s->device);
+  for (auto t : s->textures)
+    if (t) cudaDestroyTextureObject(t);
+  for (auto a : s->arrays) cudaFreeArray(a);
+  for (void* p : s->allocs) cudaFree(p);
+  if (s->host_count) cudaFreeHost(s->host_count);
+  delete s;
+  return RTB_OK;
+}
+
+int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
+  if (!d || !out) return Fail(RTB_EINVAL, "null argument");
+  *out = nullptr;
+  if (d->abi_version != RTB_ABI_VERSION) return Fail(RTB_EINVAL, "RtbSceneDesc.abi_version mismatch");
+  if (d->n_nodes < 2 || (d->n_nodes & 1u) || !d->nodes) return Fail(RTB_EINVAL, "scene needs an even, non-zero node count");
+  if (d->n_prim_refs >= (1u << 25)) return Fail(RTB_EINVAL, "more than 2^25 leaf entries");
+  if (d->n_top_nodes > d->n_nodes || (d->n_top_nodes & 1u)) return Fail(RTB_EINVAL, "bad n_top_nodes");
+  // structural validation: every index the kernels will follow must be in range
+  for (uint32_t i = 0; i < d->n_nodes; ++i) {
+    const RtbNode& n = d->nodes[i];
+    if (n.b == 0) {
+      if (!(n.lo[0] <= n.hi[0])) continue;  // padding slot (inverted box), never entered
+      if (n.a + 1 >= d->n_nodes || (n.a & 1u) || n.a == 0) return Fail(RTB_EINVAL, "node child index out of range");
+    } else if (n.b > RTB_MAX_LEAF || (uint64_t)n.a + n.b > d->n_prim_refs) {
+      return Fail(RTB_EINVAL, "leaf range out of bounds");
+    }
+  }
+  for (uint32_t i = 0; i < d->n_prim_refs; ++i) {
+    const uint32_t ty = RTB_REF_TYPE(d->prim_refs[i]), idx = RTB_REF_INDEX(d->prim_refs[i]);
+    const uint32_t lim = ty == RTB_PRIM_SPHERE ? d->n_spheres : ty == RTB_PRIM_TRIANGLE ? d->n_triangles : ty == RTB_PRIM_RECT ? d->n_rects : d->n_nodes;
+    if (idx >= lim || (ty == RTB_PRIM_SUBTREE && (idx & 1u))) return Fail(RTB_EINVAL, "leaf entry out of range");
+  }
+  auto mat_ok = [&](uint32_t m) { return m < d->n_materials; };
+  for (uint32_t i = 0; i < d->n_spheres; ++i) if (!mat_ok(d->sphere_mat[i])) return Fail(RTB_EINVAL, "sphere material out of range");
+  for (uint32_t i = 0; i < d->n_triangles; ++i) if (!mat_ok(d->triangles[i].mat)) return Fail(RTB_EINVAL, "triangle material out of range");
+  for (uint32_t i = 0; i < d->n_rects; ++i) if (!mat_ok(d->rects[i].mat) || d->rects[i].axis < 0 || d->rects[i].axis > 2) return Fail(RTB_EINVAL, "bad rect");
+  for (uint32_t i = 0; i < d->n_materials; ++i) {
+    const RtbMaterial& m = d->materials[i];
+    if ((m.type == RTB_MAT_LAMBERTIAN || m.type == RTB_MAT_DIFFUSE_LIGHT) && (m.tex < 0 || (uint32_t)m.tex >= d->n_textures))
+      return Fail(RTB_EINVAL, "material texture out of range");
+  }
+  for (uint32_t i = 0; i < d->n_textures; ++i) {
+    const RtbTexture& t = d->textures[i];
+    if (t.type == RTB_TEX_CHECKER && (t.even < 0 || t.odd < 0 || (uint32_t)t.even >= d->n_textures || (uint32_t)t.odd >= d->n_textures))
+      return Fail(RTB_EINVAL, "checker child out of range");
+    if (t.type == RTB_TEX_IMAGE && (t.image < 0 || (uint32_t)t.image >= d->n_images)) return Fail(RTB_EINVAL, "image out of range");
+  }
+  int rc = EnsureInit();
+  if (rc != RTB_OK) return rc;
+
+  RtbScene* s = new RtbScene();
+  s->device = g_device;
+  rtb::DevScene& v = s->dev;
+#define PUT(expr)            \
+  do {                       \
+    rc = (expr);             \
+    if (rc != RTB_OK) {      \
+      rtb_scene_destroy(s);  \
+      return rc;             \
+    }                        \
+  } while (0)
+  PUT(s->Put(reinterpret_cast<const float4*>(d->nodes), 2 * (size_t)d->n_nodes, &v.nodes));
+  PUT(s->Put(d->prim_refs, d->n_prim_refs, &v.prim_refs));
+  PUT(s->Put(reinterpret_cast<const double2*>(d->spheres), 2 * (size_t)d->n_spheres, &v.spheres));
+  PUT(s->Put(reinterpret_cast<const double2*>(d->triangles), 5 * (size_t)d->n_triangles, &v.triangles));
+  PUT(s->Put(reinterpret_cast<const double2*>(d->rects), 3 * (size_t)d->n_rects, &v.rects));
+  {  // float shadows of the double tables (shading frame + pre-filter)
+    std::vector<float4> sf(d->n_spheres);
+    for (uint32_t i = 0; i < d->n_spheres; ++i)
+      sf[i] = make_float4((float)d->spheres[i].c[0], (float)d->spheres[i].c[1], (float)d->spheres[i].c[2], (float)d->spheres[i].r);
+    PUT(s->Put(sf.data(), sf.size(), &v.sphere_f));
+    std::vector<float4> tf(3 * (size_t)d->n_triangles);
+    for (uint32_t i = 0; i < d->n_triangles; ++i) {
+      const RtbTriangle& t = d->triangles[i];
+      float4 a = make_float4((float)t.a[0], (float)t.a[1], (float)t.a[2], 0.f);
+      std::memcpy(&a.w, &t.mat, 4);
+      tf[3 * (size_t)i] = a;
+      tf[3 * (size_t)i + 1] = make_float4((float)t.e1[0], (float)t.e1[1], (float)t.e1[2], 0.f);
+      tf[3 * (size_t)i + 2] = make_float4((float)t.e2[0], (float)t.e2[1], (float)t.e2[2], 0.f);
+    }
+    PUT(s->Put(tf.data(), tf.size(), &v.triangle_f));
+  }
+  PUT(s->Put(d->sphere_mat, d->n_spheres, &v.sphere_mat));
+  PUT(s->Put(d->sphere_gid, d->n_spheres, &v.sphere_gid));
+  PUT(s->Put(d->triangle_gid, d->n_triangles, &v.triangle_gid));
+  PUT(s->Put(d->rect_gid, d->n_rects, &v.rect_gid));
+  PUT(s->Put(d->sphere_rank, d->n_spheres, &v.sphere_rank));
+  PUT(s->Put(d->triangle_rank, d->n_triangles, &v.triangle_rank));
+  PUT(s->Put(d->rect_rank, d->n_rects, &v.rect_rank));
+  PUT(s->Put(d->materials, d->n_materials, &v.materials));
+  PUT(s->Put(d->textures, d->n_textures, &v.textures));
+  {  // images -> point-sampled texture objects over RGBA8 arrays
+    std::vector<cudaTextureObject_t> objs(d->n_images, 0);
+    std::vector<int2> dims(d->n_images, make_int2(0, 0));
+    for (uint32_t i = 0; i < d->n_images; ++i) {
+      const RtbImage& im = d->images[i];
+      if (im.width <= 0 || im.height <= 0 || !im.rgb) continue;
+      std::vector<uchar4> rgba((size_t)im.width * im.height);
+      for (size_t p = 0; p < rgba.size(); ++p) rgba[p] = make_uchar4(im.rgb[3 * p], im.rgb[3 * p + 1], im.rgb[3 * p + 2], 255);
+      cudaChannelFormatDesc fmt = cudaCreateChannelDesc<uchar4>();
+      cudaArray_t arr = nullptr;
+      cudaError_t e = cudaMallocArray(&arr, &fmt, im.width, im.height);
+      if (e == cudaSuccess) {
+        s->arrays.push_back(arr);
+        e = cudaMemcpy2DToArray(arr, 0, 0, rgba.data(), (size_t)im.width * 4, (size_t)im.width * 4, im.height, cudaMemcpyHostToDevice);
+      }
+      cudaTextureObject_t tex = 0;
+      if (e == cudaSuccess) {
+        cudaResourceDesc res{};
+        res.resType = cudaResourceTypeArray;
+        res.res.array.array = arr;
+        cudaTextureDesc td{};
+        td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
+        td.filterMode = cudaFilterModePoint;
+        td.readMode = cudaReadModeElementType;
+        td.normalizedCoords = 0;
+        e = cudaCreateTextureObject(&tex, &res, &td, nullptr);
+      }
+      if (e != cudaSuccess) {
+        rtb_scene_destroy(s);
+        return Fail(RTB_ECUDA, std::string("image texture upload: ") + cudaGetErrorString(e));
+      }
+      s->textures.push_back(tex);
+      objs[i] = tex;
+      dims[i] = make_int2(im.width, im.height);
+    }
+    PUT(s->Put(objs.data(), objs.size(), &v.image_tex));
+    PUT(s->Put(dims.data(), dims.size(), &v.image_dim));
+  }
+  v.n_nodes = d->n_nodes;
+  v.n_top_nodes = d->n_top_nodes;
+  s->smem_bytes = (size_t)d->n_top_nodes * sizeof(RtbNode);
+  if (s->smem_bytes > 200 * 1024) {
+    rtb_scene_destroy(s);
+    return Fail(RTB_EINVAL, "n_top_nodes does not fit shared memory");
+  }
+  {
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, sizeof(rtb::HitCounters) + 16);
+    if (e == cudaSuccess) e = cudaMemset(p, 0, sizeof(rtb::HitCounters) + 16);
+    if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&s->host_count), 64);
+    if (e != cudaSuccess) {
+      rtb_scene_destroy(s);
+      return Fail(RTB_ECUDA, std::string("counter alloc: ") + cudaGetErrorString(e));
+    }
+    s->allocs.push_back(p);
+    s->counters = reinterpret_cast<rtb::HitCounters*>(p);
+    s->cursor = reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(p) + sizeof(rtb::HitCounters));
+  }
+  // opt in to large dynamic shared memory for the two traversal kernels
+  if (s->smem_bytes > 48 * 1024) {
+    cudaFuncSetAttribute(rtb::intersect_batch_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_bytes);
+    cudaFuncSetAttribute(rtb::extend_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_bytes);
+  }
+#undef PUT
+  *out = s;
+  return RTB_OK;
+}
+
+}  // extern "C"
+
+// Persistent grid: as many CTAs as are co-resident on the whole chip.
+template <class K>
+static int PersistentGrid(K kernel, int block, size_t smem) {
+  int per_sm = 0;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, smem);
+  if (per_sm < 1) per_sm = 1;
+  return per_sm * g_sm_count;
+}
+
+extern "C" {
+
+int rtb_intersect_batch_device(RtbScene* s, const RtbRay* d_rays, size_t n, RtbHit* d_hits, void* stream) {
+  if (!s || (!d_rays && n) || (!d_hits && n)) return Fail(RTB_EINVAL, "null argument");
+  if (n == 0) return RTB_OK;
+  if (n > 0xffffff00ull) return Fail(RTB_EINVAL, "batch too large");
+  int rc = EnsureInit();
+  if (rc != RTB_OK) return rc;
+  cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : g_stream;
+  RTB_CUDA(cudaMemsetAsync(s->cursor, 0, 8, st));
+  const bool use_smem = s->dev.n_top_nodes > 0 && !std::getenv("RTB_NO_SMEM_TOP");
+  const float4* rays4 = reinterpret_cast<const float4*>(d_rays);
+  if (use_smem) {
+    const int grid = PersistentGrid(rtb::intersect_batch_kernel<true>, 128, s->smem_bytes);
+    rtb::intersect_batch_kernel<true><<<grid, 128, s->smem_bytes, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->cursor, s->counters);
+  } else {
+    const int grid = PersistentGrid(rtb::intersect_batch_kernel<false>, 128, 0);
+    rtb::intersect_batch_kernel<false><<<grid, 128, 0, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->cursor, s->counters);
+  }
+  RTB_CUDA(cudaGetLastError());
+  return RTB_OK;
+}
+
+int rtb_intersect_batch(RtbScene* s, const RtbRay* rays, size_t n, RtbHit* hits) {
+  if (!s || (!rays && n) || (!hits && n)) return Fail(RTB_EINVAL, "null argument");
+  if (n == 0) return RTB_OK;
+  int rc = EnsureInit();
+  if (rc != RTB_OK) return rc;
+  RtbRay* d_rays = nullptr;
+  RtbHit* d_hits = nullptr;
+  RTB_CUDA(cudaMalloc(reinterpret_cast<void**>(&d_rays), n * sizeof(RtbRay)));
+  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&d_hits), n * sizeof(RtbHit));
+  if (e == cudaSuccess) e = cudaMemcpyAsync(d_rays, rays, n * sizeof(RtbRay), cudaMemcpyHostToDevice, g_stream);
+  if (e == cudaSuccess) {
+    rc = rtb_intersect_batch_device(s, d_rays, n, d_hits, g_stream);
+    if (rc == RTB_OK) e = cudaMemcpyAsync(hits, d_hits, n * sizeof(RtbHit), cudaMemcpyDeviceToHost, g_stream);
+    if (rc == RTB_OK && e == cudaSuccess) e = cudaStreamSynchronize(g_stream);
+  }
+  cudaFree(d_rays);
+  cudaFree(d_hits);
+  if (rc != RTB_OK) return rc;
+  if (e != cudaSuccess) return Fail(RTB_ECUDA, std::string("intersect_batch: ") + cudaGetErrorString(e));
+  return RTB_OK;
+}
+
+static int EnsurePool(RtbScene* s, uint32_t pool, int w, int h) {
+  if (s->pool != pool) {
+    // (re)allocate the two queues + hit arrays as one slab each
+    auto alloc = [&](void** p, size_t bytes) -> cudaError_t {
+      cudaError_t e = cudaMalloc(p, bytes);
+      if (e == cudaSuccess) s->allocs.push_back(*p);
+      return e;
+    };
+    for (int k = 0; k < 2; ++k) {
+      RTB_CUDA(alloc(reinterpret_cast<void**>(&s->q[k].ro), (size_t)pool * 16));
+      RTB_CUDA(alloc(reinterpret_cast<void**>(&s->q[k].rd), (size_t)pool * 16));
+      RTB_CUDA(alloc(reinterpret_cast<void**>(&s->q[k].thr), (size_t)pool * 16));
+      RTB_CUDA(alloc(reinterpret_cast<void**>(&s->q[k].meta), (size_t)pool * 8));
+    }
+    RTB_CUDA(alloc(reinterpret_cast<void**>(&s->hit_t), (size_t)pool * 4));
+    RTB_CUDA(alloc(reinterpret_cast<void**>(&s->hit_ref), (size_t)pool * 4));
+    s->pool = pool;
+  }
+  if (s->order_w != w || s->order_h != h) {
+    // 8x4-tiled pixel permutation: consecutive samples of a warp are neighbouring pixels
+    std::vector<uint32_t> order;
+    order.reserve((size_t)w * h);
+    for (int ty = 0; ty < h; ty += 4)
+      for (int tx = 0; tx < w; tx += 8)
+        for (int y = ty; y < std::min(ty + 4, h); ++y)
+          for (int x = tx; x < std::min(tx + 8, w); ++x) order.push_back((uint32_t)(y * w + x));
+    void* p = nullptr;
+    RTB_CUDA(cudaMalloc(&p, order.size() * 4));
+    s->allocs.push_back(p);
+    RTB_CUDA(cudaMemcpy(p, order.data(), order.size() * 4, cudaMemcpyHostToDevice));
+    s->pixel_order = static_cast<uint32_t*>(p);
+    s->order_w = w;
+    s->order_h = h;
+  }
+  return RTB_OK;
+}
+
+int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* prm, float* d_rgb_sum, RtbStats* stats) {
+  if (!s || !cam || !prm || !d_rgb_sum) return Fail(RTB_EINVAL, "null argument");
+  if (cam->width <= 0 || cam->height <= 0 || prm->spp_end < prm->spp_begin || prm->max_depth < 0) return Fail(RTB_EINVAL, "bad camera / params");
+  if (prm->mode != RTB_MODE_A && prm->mode != RTB_MODE_B) return Fail(RTB_EINVAL, "unknown estimator mode");
+  int rc = EnsureInit();
+  if (rc != RTB_OK) return rc;
+  const uint32_t n_pixels = (uint32_t)cam->width * (uint32_t)cam->height;
+  uint32_t pool = prm->pool_size ? prm->pool_size : (1u << 21);
+  pool = std::max(pool, 1u << 10);
+  rc = EnsurePool(s, pool, cam->width, cam->height);
+  if (rc != RTB_OK) return rc;
+  cudaStream_t st = g_stream;
+  rtb::RenderConsts rcst{};
+  rcst.cam = *cam;
+  rcst.key = make_uint2((uint32_t)prm->seed, (uint32_t)(prm->seed >> 32));
+  rcst.max_depth = prm->max_depth;
+  rcst.mode = prm->mode;
+  rcst.spp_begin = prm->spp_begin;
+  rcst.n_pixels = n_pixels;
+  const unsigned long long total = (unsigned long long)n_pixels * (unsigned long long)(prm->spp_end - prm->spp_begin);
+  const bool use_smem = s->dev.n_top_nodes > 0 && !(prm->flags & RTB_RENDER_NO_SMEM_TOP) && !std::getenv("RTB_NO_SMEM_TOP");
+  const int ext_grid = use_smem ? PersistentGrid(rtb::extend_kernel<true>, 128, s->smem_bytes) : PersistentGrid(rtb::extend_kernel<false>, 128, 0);
+
+  cudaEvent_t ev0, ev1;
+  RTB_CUDA(cudaEventCreate(&ev0));
+  RTB_CUDA(cudaEventCreate(&ev1));
+  RTB_CUDA(cudaEventRecord(ev0, st));
+  if (!(prm->flags & RTB_RENDER_KEEP_ACCUM)) RTB_CUDA(cudaMemsetAsync(d_rgb_sum, 0, (size_t)n_pixels * 3 * sizeof(float), st));
+#ifdef RTB_COUNTERS
+  RTB_CUDA(cudaMemsetAsync(s->counters, 0, sizeof(rtb::HitCounters), st));
+#endif
+  unsigned long long generated = 0, rays = 0;
+  uint32_t live = 0, iterations = 0, launches = 0;
+  int cur = 0;
+  // max_depth == 0: GetPixel returns black without tracing (camera.h:149-151)
+  const bool trace = prm->max_depth > 0 || prm->mode == RTB_MODE_B || cam->depth_camera;
+  while (trace) {
+    const uint32_t room = pool - live;
+    const uint32_t gen = (uint32_t)std::min<unsigned long long>(room, total - generated);
+    if (gen) {
+      rtb::generate_kernel<<<(gen + 255) / 256, 256, 0, st>>>(s->q[cur], live, gen, generated, rcst, s->pixel_order);
+      generated += gen;
+      live += gen;
+      ++launches;
+    }
+    if (live == 0) break;
+    RTB_CUDA(cudaMemsetAsync(s->cursor, 0, 8, st));
+    if (use_smem)
+      rtb::extend_kernel<true><<<ext_grid, 128, s->smem_bytes, st>>>(s->dev, s->q[cur], live, s->hit_t, s->hit_ref, s->cursor, s->counters);
+    else
+      rtb::extend_kernel<false><<<ext_grid, 128, 0, st>>>(s->dev, s->q[cur], live, s->hit_t, s->hit_ref, s->cursor, s->counters);
+    rtb::shade_kernel<<<(live + 255) / 256, 256, 0, st>>>(s->dev, s->q[cur], live, s->hit_t, s->hit_ref, s->q[cur ^ 1], s->cursor + 1,
+                                                          d_rgb_sum, rcst);
+    launches += 2;
+    rays += live;
+    RTB_CUDA(cudaMemcpyAsync(s->host_count, s->cursor + 1, 4, cudaMemcpyDeviceToHost, st));
+    RTB_CUDA(cudaStreamSynchronize(st));
+    live = *s->host_count;
+    cur ^= 1;
+    ++iterations;
+  }
+  RTB_CUDA(cudaEventRecord(ev1, st));
+  RTB_CUDA(cudaEventSynchronize(ev1));
+  RTB_CUDA(cudaGetLastError());
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, ev0, ev1);
+  cudaEventDestroy(ev0);
+  cudaEventDestroy(ev1);
+  if (stats) {
+    std::memset(stats, 0, sizeof(*stats));
+    stats->samples = generated;
+    stats->rays = rays;
+    stats->iterations = iterations;
+    stats->launches = launches;
+    stats->ms_total = ms;
+#ifdef RTB_COUNTERS
+    rtb::HitCounters hc{};
+    cudaMemcpy(&hc, s->counters, sizeof(hc), cudaMemcpyDeviceToHost);
+    stats->node_visits = hc.node_pairs;
+    stats->prim_tests = hc.prim_tests;
+    stats->exact_tests = hc.exact_tests;
+#endif
+  }
+  return RTB_OK;
+}
+
+int rtb_render(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* prm, float* rgb_sum, RtbStats* stats) {
+  if (!s || !cam || !prm || !rgb_sum) return Fail(RTB_EINVAL, "null argument");
+  int rc = EnsureInit();
+  if (rc != RTB_OK) return rc;
+  const size_t bytes = (size_t)cam->width * cam->height * 3 * sizeof(float);
+  float* d = nullptr;
+  RTB_CUDA(cudaMalloc(reinterpret_cast<void**>(&d), bytes));
+  if (prm->flags & RTB_RENDER_KEEP_ACCUM) cudaMemcpy(d, rgb_sum, bytes, cudaMemcpyHostToDevice);
+  rc = rtb_render_device(s, cam, prm, d, stats);
+  cudaError_t e = cudaSuccess;
+  if (rc == RTB_OK) e = cudaMemcpy(rgb_sum, d, bytes, cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  if (rc != RTB_OK) return rc;
+  if (e != cudaSuccess) return Fail(RTB_ECUDA, std::string("render readback: ") + cudaGetErrorString(e));
+  return RTB_OK;
+}
+
+int rtb_resolve_device(const float* d_rgb_sum, size_t n_pixels, int spp, uint8_t* d_rgb8, void* stream) {
+  if (!d_rgb_sum || !d_rgb8 || spp <= 0) return Fail(RTB_EINVAL, "bad argument");
+  int rc = EnsureInit();
+  if (rc != RTB_OK) return rc;
+  cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : g_stream;
+  const size_t n = n_pixels * 3;
+  if (n) rtb::resolve_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d_rgb_sum, n, 1.0 / (double)spp, d_rgb8);
+  RTB_CUDA(cudaGetLastError());
+  return RTB_OK;
+}
+
+int rtb_resolve(const float* rgb_sum, size_t n_pixels, int spp, uint8_t* rgb8) {
+  if (!rgb_sum || !rgb8 || spp <= 0) return Fail(RTB_EINVAL, "bad argument");
+  int rc = EnsureInit();
+  if (rc != RTB_OK) return rc;
+  const size_t n = n_pixels * 3;
+  if (n == 0) return RTB_OK;
+  float* d_in = nullptr;
+  uint8_t* d_out = nullptr;
+  RTB_CUDA(cudaMalloc(reinterpret_cast<void**>(&d_in), n * 4));
+  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&d_out), n);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(d_in, rgb_sum, n * 4, cudaMemcpyHostToDevice, g_stream);
+  if (e == cudaSuccess) {
+    rc = rtb_resolve_device(d_in, n_pixels, spp, d_out, g_stream);
+    if (rc == RTB_OK) e = cudaMemcpyAsync(rgb8, d_out, n, cudaMemcpyDeviceToHost, g_stream);
+    if (rc == RTB_OK && e == cudaSuccess) e = cudaStreamSynchronize(g_stream);
+  }
+  cudaFree(d_in);
+  cudaFree(d_out);
+  if (rc != RTB_OK) return rc;
+  if (e != cudaSuccess) return Fail(RTB_ECUDA, std::string("resolve: ") + cudaGetErrorString(e));
+  return RTB_OK;
+}
+
+// ---- roofline denominators (bench.py): L2-resident read bandwidth, FP32 and FP64 FMA rate ----
+int rtb_measure_l2_gbs(size_t bytes, int iters, float* gbs) {
+  if (!gbs || bytes < 4096 || iters < 1) return Fail(RTB_EINVAL, "bad argument");
+  int rc = EnsureInit();
+  if (rc != RTB_OK) return rc;
+  float4* buf = nullptr;
+  float* sink = nullptr;
+  const size_t n4 = bytes / 16;
+  RTB_CUDA(cudaMalloc(reinterpret_cast<void**>(&buf), n4 * 16));
+  RTB_CUDA(cudaMalloc(reinterpret_cast<void**>(&sink), 4));
+  RTB_CUDA(cudaMemsetAsync(buf, 0, n4 * 16, g_stream));
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  const int grid = g_sm_count * 8;
+  rtb::l2_read_kernel<<<grid, 256, 0, g_stream>>>(buf, n4, 2, sink);  // warm L2
+  cudaEventRecord(e0, g_stream);
+  rtb::l2_read_kernel<<<grid, 256, 0, g_stream>>>(buf, n4, iters, sink);
+  cudaEventRecord(e1, g_stream);
+  cudaError_t e = cudaEventSynchronize(e1);
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(buf);
+  cudaFree(sink);
+  if (e != cudaSuccess) return Fail(RTB_ECUDA, std::string("l2 bench: ") + cudaGetErrorString(e));
+  *gbs = (float)((double)n4 * 16 * iters / (ms * 1e-3) / 1e9);
+  return RTB_OK;
+}
+
+}  // extern "C"
+
+template <class T, class K>
+static int MeasureFma(K kernel, int iters, float* tflops) {
+  if (!tflops || iters < 1) return Fail(RTB_EINVAL, "bad argument");
+  int rc = EnsureInit();
+  if (rc != RTB_OK) return rc;
+  T* sink = nullptr;
+  RTB_CUDA(cudaMalloc(reinterpret_cast<void**>(&sink), sizeof(T)));
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  const int grid = g_sm_count * 8, block = 256;
+  kernel<<<grid, block, 0, g_stream>>>(iters / 8 + 1, sink);
+  cudaEventRecord(e0, g_stream);
+  kernel<<<grid, block, 0, g_stream>>>(iters, sink);
+  cudaEventRecord(e1, g_stream);
+  cudaError_t e = cudaEventSynchronize(e1);
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(sink);
+  if (e != cudaSuccess) return Fail(RTB_ECUDA, std::string("fma bench: ") + cudaGetErrorString(e));
+  *tflops = (float)((double)grid * block * 8.0 * 2.0 * iters / (ms * 1e-3) / 1e12);
+  return RTB_OK;
+}
+extern "C" {
+int rtb_measure_fp32_tflops(int iters, float* tflops) { return MeasureFma<float>(rtb::fp32_fma_kernel, iters, tflops); }
+int rtb_measure_fp64_tflops(int iters, float* tflops) { return MeasureFma<double>(rtb::fp64_fma_kernel, iters, tflops); }
+
+}  // extern "C"

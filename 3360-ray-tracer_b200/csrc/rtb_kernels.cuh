@@ -1,0 +1,319 @@
+// rtb_kernels.cuh — the wavefront kernels: generate, extend (BVH traverse), shade (+compact),
+// resolve, and the standalone intersect_batch.  SIMT FP32/FP64 only — tensor cores are
+// deliberately unused (traversal and shading are not contractions).
+#pragma once
+#include "rtb_shade.cuh"
+
+namespace rtb {
+
+// One wavefront queue: structure-of-arrays so that every kernel's loads and stores coalesce.
+struct PathQueue {
+  float4* ro;    // origin xyz, tmin
+  float4* rd;    // direction xyz (un-normalised), tmax
+  float4* thr;   // throughput rgb, pixel index (bits)
+  uint2* meta;   // global sample index, bounce count
+};
+
+struct RenderConsts {
+  RtbCamera cam;
+  uint2 key;  // Philox key
+  int max_depth;
+  int mode;
+  int spp_begin;
+  uint32_t n_pixels;
+};
+
+// Stage the breadth-first top of the tree in shared memory (one copy per CTA per launch).
+__device__ __forceinline__ void stage_top(const DevScene& s, float4* smem_nodes) {
+  const uint32_t n4 = 2 * s.n_top_nodes;
+  for (uint32_t i = threadIdx.x; i < n4; i += blockDim.x) smem_nodes[i] = __ldg(&s.nodes[i]);
+  __syncthreads();
+}
+
+// ---- seam 2: RayIntegrator::IntersectBatch (src/integrator/cpu_ray_integrator.h:18-46) --------
+// Persistent warps pull 32 rays at a time from a global cursor.
+template <bool kUseSmem>
+__global__ void __launch_bounds__(128) intersect_batch_kernel(DevScene s, const float4* __restrict__ rays, uint32_t n,
+                                                              RtbHit* __restrict__ hits, unsigned int* cursor, HitCounters* cnt) {
+  extern __shared__ float4 smem_nodes[];
+  if (kUseSmem) stage_top(s, smem_nodes);
+  const unsigned lane = threadIdx.x & 31u;
+  for (;;) {
+    unsigned base = 0;
+    if (lane == 0) base = atomicAdd(cursor, 32u);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= n) break;
+    const uint32_t i = base + lane;
+    if (i < n) {
+      TravRay r;
+      prepare_ray(r, __ldg(&rays[2 * (size_t)i]), __ldg(&rays[2 * (size_t)i + 1]));
+      double t;
+      const uint32_t ref = closest_hit<kUseSmem>(s, smem_nodes, r, t, cnt);
+      RtbHit h;
+      h.ref = ref;
+      if (ref == kNoHit) {
+        h.t = 0.0;
+        h.prim_id = -1;
+      } else {
+        const uint32_t ty = RTB_REF_TYPE(ref), idx = RTB_REF_INDEX(ref);
+        h.t = t;
+        h.prim_id = (int)(ty == RTB_PRIM_SPHERE ? s.sphere_gid[idx] : ty == RTB_PRIM_TRIANGLE ? s.triangle_gid[idx] : s.rect_gid[idx]);
+      }
+      hits[i] = h;
+    }
+  }
+}
+
+// ---- generate: Camera::GetRay + SampleSquare + defocus_disk_sample (camera.h:134-144,196-203) --
+// Slot q+k of the queue receives local sample g0+k; pixel order is the host-built 8x4-tiled
+// permutation so that a warp's primary rays stay coherent.
+__global__ void generate_kernel(PathQueue q, uint32_t q_offset, uint32_t count, unsigned long long g0, RenderConsts rc,
+                                const uint32_t* __restrict__ pixel_order) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= count) return;
+  const unsigned long long g = g0 + k;
+  const uint32_t s_local = (uint32_t)(g / rc.n_pixels), pl = (uint32_t)(g % rc.n_pixels);
+  const uint32_t pixel = __ldg(&pixel_order[pl]);
+  const uint32_t sample = (uint32_t)rc.spp_begin + s_local;
+  const int px = (int)(pixel % (uint32_t)rc.cam.width), py = (int)(pixel / (uint32_t)rc.cam.width);
+  const uint4 rnd = philox4x32_10(make_uint4(pixel, sample, 0xffffffffu, 0u), rc.key);
+  const RtbCamera& c = rc.cam;
+  const float jx = u01(rnd.x) - 0.5f, jy = u01(rnd.y) - 0.5f;
+  const float fi = (float)px + jx, fj = (float)py + jy;
+  f3 target = mk3(c.pixel00[0] + fi * c.delta_u[0] + fj * c.delta_v[0], c.pixel00[1] + fi * c.delta_u[1] + fj * c.delta_v[1],
+                  c.pixel00[2] + fi * c.delta_u[2] + fj * c.delta_v[2]);
+  f3 origin = mk3(c.center[0], c.center[1], c.center[2]);
+  if (c.defocus_angle > 0.0f) {
+    // uniform point in the unit disk: same distribution as RandomInUnitDisk's rejection loop (math_utils.h:83-88)
+    const float rr = sqrtf(u01(rnd.z));
+    float sn, cs;
+    sincospif(2.0f * u01(rnd.w), &sn, &cs);
+    const float dxk = rr * cs, dyk = rr * sn;
+    origin = mk3(c.center[0] + dxk * c.disk_u[0] + dyk * c.disk_v[0], c.center[1] + dxk * c.disk_u[1] + dyk * c.disk_v[1],
+                 c.center[2] + dxk * c.disk_u[2] + dyk * c.disk_v[2]);
+  }
+  f3 dir = target - origin;
+  if (c.depth_camera) dir = normalize3(dir);  // DepthCamera::GetPixel normalises first (camera.h:223)
+  const uint32_t slot = q_offset + k;
+  q.ro[slot] = make_float4(origin.x, origin.y, origin.z, 0.001f);  // Interval(0.001, inf), camera.h:158
+  q.rd[slot] = make_float4(dir.x, dir.y, dir.z, __int_as_float(0x7f800000));
+  q.thr[slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(pixel));
+  q.meta[slot] = make_uint2(sample, 0u);
+}
+
+// ---- extend: Bvh::Hit for every live path (src/geom/bvh.h:71-119) ------------------------------
+template <bool kUseSmem>
+__global__ void __launch_bounds__(128) extend_kernel(DevScene s, PathQueue q, uint32_t n, float* __restrict__ hit_t,
+                                                     uint32_t* __restrict__ hit_ref, unsigned int* cursor, HitCounters* cnt) {
+  extern __shared__ float4 smem_nodes[];
+  if (kUseSmem) stage_top(s, smem_nodes);
+  const unsigned lane = threadIdx.x & 31u;
+  for (;;) {
+    unsigned base = 0;
+    if (lane == 0) base = atomicAdd(cursor, 32u);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= n) break;
+    const uint32_t i = base + lane;
+    if (i < n) {
+      TravRay r;
+      prepare_ray(r, q.ro[i], q.rd[i]);
+      double t;
+      const uint32_t ref = closest_hit<kUseSmem>(s, smem_nodes, r, t, cnt);
+      hit_t[i] = (float)t;
+      hit_ref[i] = ref;
+    }
+  }
+}
+
+__device__ __forceinline__ void add_radiance(float* accum, uint32_t pixel, f3 L) {
+  float* a = accum + 3 * (size_t)pixel;
+  if (L.x != 0.0f) atomicAdd(a + 0, L.x);
+  if (L.y != 0.0f) atomicAdd(a + 1, L.y);
+  if (L.z != 0.0f) atomicAdd(a + 2, L.z);
+}
+
+// ---- shade + compact ---------------------------------------------------------------------------
+// Mode A: Camera::GetPixel (camera.h:148-174) with Material::Scatter (material.cc:20-34,82-94,
+// 148-172,273-280).  Mode B: the shading loop of WavefrontRenderer::Render (wavefront.cc:109-209)
+// with Material::Sample (material.cc:57-74,117-141,194-256) and Russian roulette.
+// Survivors are appended to `out` with one atomicAdd per warp (ballot + popc prefix).
+__global__ void __launch_bounds__(256) shade_kernel(DevScene s, PathQueue in, uint32_t n, const float* __restrict__ hit_t,
+                                                    const uint32_t* __restrict__ hit_ref, PathQueue out, unsigned int* out_count,
+                                                    float* accum, RenderConsts rc) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  bool alive = false;
+  float4 n_ro, n_rd, n_thr;
+  uint2 n_meta;
+  if (i < n) {
+    const float4 ro = in.ro[i], rd = in.rd[i], th = in.thr[i];
+    const uint2 meta = in.meta[i];
+    const uint32_t ref = hit_ref[i];
+    const uint32_t pixel = __float_as_uint(th.w);
+    const f3 thr = mk3(th.x, th.y, th.z);
+    const f3 d = mk3(rd.x, rd.y, rd.z);
+    const uint32_t bounce = meta.y;
+    if (rc.cam.depth_camera) {
+      // DepthCamera::GetPixel (camera.h:217-236): t of the normalised ray in red, black past max_dist 20 / on a miss
+      const float t = hit_t[i];
+      if (ref != kNoHit && t < 20.0f) add_radiance(accum, pixel, mk3(t, 0.0f, 0.0f));
+    } else if (ref == kNoHit || (rc.mode == RTB_MODE_B && (int)bounce >= rc.max_depth)) {
+      add_radiance(accum, pixel, thr * sky(d));  // camera.h:171-173 / wavefront.cc:122-129
+    } else {
+      const float t = hit_t[i];
+      const f3 p = mk3(fmaf(t, d.x, ro.x), fmaf(t, d.y, ro.y), fmaf(t, d.z, ro.z));
+      f3 n_out;
+      float u, v;
+      uint32_t mat_id;
+      surface_at(s, ref, p, n_out, u, v, mat_id);
+      const bool front = dot3(d, n_out) < 0.0f;  // HitRecord::set_face_normal, hittable.h:31-34
+      const f3 nrm = front ? n_out : -n_out;
+      const RtbMaterial m = s.materials[mat_id];
+      const uint4 rnd = philox4x32_10(make_uint4(pixel, meta.x, bounce, 0u), rc.key);
+      f3 atten = mk3(1.0f, 1.0f, 1.0f), dir = nrm;
+      if (rc.mode == RTB_MODE_A) {
+        if (m.type == RTB_MAT_LAMBERTIAN) {  // material.cc:20-34
+          dir = nrm + unit_vector(u01(rnd.x), u01(rnd.y));
+          if (fabsf(dir.x) < 1e-8f && fabsf(dir.y) < 1e-8f && fabsf(dir.z) < 1e-8f) dir = nrm;
+          atten = texture_value(s, m.tex, u, v, p);
+          alive = true;
+        } else if (m.type == RTB_MAT_METAL) {  // material.cc:82-94: reflects the UN-normalised direction
+          dir = reflect3(d, nrm) + m.fuzz * unit_vector(u01(rnd.x), u01(rnd.y));
+          atten = mk3(m.albedo[0], m.albedo[1], m.albedo[2]);
+          alive = dot3(dir, nrm) > 0.0f;
+        } else if (m.type == RTB_MAT_DIELECTRIC) {  // material.cc:148-172
+          const float eta = front ? (1.0f / m.ior) : m.ior;
+          const f3 ud = normalize3(d);
+          const float cos_theta = fminf(dot3(-ud, nrm), 1.0f);
+          const float sin_theta = sqrtf(fmaxf(0.0f, 1.0f - cos_theta * cos_theta));
+          const bool cannot_refract = eta * sin_theta > 1.0f;
+          dir = (cannot_refract || schlick(cos_theta, eta) > u01(rnd.z)) ? reflect3(ud, nrm) : refract3(ud, nrm, eta);
+          alive = true;
+        } else {  // DiffuseLight: emits, never scatters (material.cc:273-280,312-316)
+          add_radiance(accum, pixel, thr * texture_value(s, m.tex, u, v, p));
+        }
+        n_thr = make_float4(thr.x * atten.x, thr.y * atten.y, thr.z * atten.z, th.w);
+        // the recursion bottoms out in black when depth reaches 0 (camera.h:149-151)
+        if ((int)bounce + 1 >= rc.max_depth) alive = false;
+      } else {
+        // ---- mode B (wavefront.cc:131-207)
+        f3 emitted = mk3(0, 0, 0);
+        if (m.type == RTB_MAT_DIFFUSE_LIGHT) emitted = texture_value(s, m.tex, u, v, p);
+        const bool near_zero = fabsf(emitted.x) < 1e-8f && fabsf(emitted.y) < 1e-8f && fabsf(emitted.z) < 1e-8f;
+        f3 tp = thr;
+        if (!near_zero) {
+          add_radiance(accum, pixel, thr * emitted);  // wavefront.cc:134-142
+        } else if (m.type == RTB_MAT_LAMBERTIAN) {
+          // Lambertian::Sample (material.cc:57-74): cosine direction, f = albedo/pi, pdf = cos/pi;
+          // wavefront.cc:176-186 multiplies by f*cos/pdf = albedo.  RandomCosineDirection math_utils.h:104-123.
+          const float r1 = u01(rnd.x), r2 = u01(rnd.y);
+          float sn, cs;
+          sincospif(2.0f * r1, &sn, &cs);
+          const float rr = sqrtf(r2), z = sqrtf(fmaxf(0.0f, 1.0f - r2));
+          const f3 w = normalize3(nrm);
+          const f3 a = fabsf(w.x) > 0.9f ? mk3(0, 1, 0) : mk3(1, 0, 0);
+          const f3 vv = normalize3(cross3(w, a));
+          const f3 uu = cross3(vv, w);
+          dir = normalize3((rr * cs) * uu + (rr * sn) * vv + z * w);
+          const float cosv = dot3(dir, nrm);
+          const float pdf = cosv / 3.14159265358979323846f;
+          if (cosv > 0.0f && pdf >= 1e-6f) {  // material.cc:66-68, wavefront.cc:178-183
+            tp = thr * texture_value(s, m.tex, u, v, p);
+            alive = true;
+          }
+        } else if (m.type == RTB_MAT_METAL) {  // Metal::Sample, material.cc:117-141
+          const f3 wo = -normalize3(d);
+          dir = normalize3(reflect3(-wo, nrm) + m.fuzz * unit_vector(u01(rnd.x), u01(rnd.y)));
+          if (dot3(dir, nrm) > 0.0f) {
+            tp = thr * mk3(m.albedo[0], m.albedo[1], m.albedo[2]);
+            alive = true;
+          }
+        } else if (m.type == RTB_MAT_DIELECTRIC) {  // Dielectric::Sample, material.cc:194-256
+          const float eta = front ? (1.0f / m.ior) : m.ior;
+          const f3 wi_inc = normalize3(d);
+          const float cos_i = fminf(fmaxf(dot3(wi_inc, nrm), -1.0f), 1.0f);
+          const float sin_i = sqrtf(fmaxf(0.0f, 1.0f - cos_i * cos_i));
+          const float sin_t = eta * sin_i;
+          alive = true;
+          if (sin_t >= 1.0f || u01(rnd.z) < schlick(fabsf(cos_i), m.ior)) {
+            dir = reflect3(wi_inc, nrm);
+          } else {
+            dir = refract3(wi_inc, nrm, eta);
+            tp = (eta * eta) * thr;  // material.cc:252-253
+          }
+        }
+        // Russian roulette, wavefront.cc:189-205 (child depth > 5)
+        if (alive && (int)bounce + 1 > 5) {
+          const float pr = fminf(fmaxf(fmaxf(tp.x, fmaxf(tp.y, tp.z)), 0.1f), 0.95f);
+          if (u01(rnd.w) > pr) alive = false;
+          else tp = (1.0f / pr) * tp;
+        }
+        n_thr = make_float4(tp.x, tp.y, tp.z, th.w);
+      }
+      if (alive) {
+        n_ro = make_float4(p.x, p.y, p.z, 0.001f);
+        n_rd = make_float4(dir.x, dir.y, dir.z, __int_as_float(0x7f800000));
+        n_meta = make_uint2(meta.x, bounce + 1u);
+      }
+    }
+  }
+  // ---- compact: ballot + prefix inside the warp, one atomic per warp
+  const unsigned ballot = __ballot_sync(0xffffffffu, alive);
+  if (ballot) {
+    const unsigned lane = threadIdx.x & 31u;
+    unsigned base = 0;
+    if (lane == (unsigned)(__ffs(ballot) - 1)) base = atomicAdd(out_count, (unsigned)__popc(ballot));
+    base = __shfl_sync(0xffffffffu, base, __ffs(ballot) - 1);
+    if (alive) {
+      const uint32_t slot = base + __popc(ballot & ((1u << lane) - 1u));
+      out.ro[slot] = n_ro;
+      out.rd[slot] = n_rd;
+      out.thr[slot] = n_thr;
+      out.meta[slot] = n_meta;
+    }
+  }
+}
+
+// ---- resolve: core::write_color (src/core/color.h:18-33) in double, like the reference ----------
+__global__ void resolve_kernel(const float* __restrict__ rgb_sum, size_t n_values, double inv_spp, uint8_t* __restrict__ rgb8) {
+  const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i >= n_values) return;
+  const double lin = (double)rgb_sum[i] * inv_spp;
+  double g = lin > 0 ? sqrt(lin) : 0.0;
+  g = g < 0.0 ? 0.0 : (g > 0.999 ? 0.999 : g);
+  rgb8[i] = (uint8_t)(int)(256 * g);
+}
+
+// ---- roofline denominators ----------------------------------------------------------------------
+// L2-resident 128-bit read sweep.
+__global__ void l2_read_kernel(const float4* __restrict__ buf, size_t n4, int iters, float* sink) {
+  float acc = 0.f;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (int it = 0; it < iters; ++it)
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += stride) {
+      const float4 v = __ldg(&buf[i]);
+      acc += v.x + v.y + v.z + v.w;
+    }
+  if (acc == 123.456f) *sink = acc;
+}
+__global__ void fp32_fma_kernel(int iters, float* sink) {
+  float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f, a6 = a0 + 6.f, a7 = a0 + 7.f;
+  const float b = 1.0000001f, c = 1e-7f;
+  for (int i = 0; i < iters; ++i) {
+    a0 = fmaf(a0, b, c); a1 = fmaf(a1, b, c); a2 = fmaf(a2, b, c); a3 = fmaf(a3, b, c);
+    a4 = fmaf(a4, b, c); a5 = fmaf(a5, b, c); a6 = fmaf(a6, b, c); a7 = fmaf(a7, b, c);
+  }
+  const float r = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+  if (r == 123.456f) *sink = r;
+}
+__global__ void fp64_fma_kernel(int iters, double* sink) {
+  double a0 = threadIdx.x * 1e-3, a1 = a0 + 1., a2 = a0 + 2., a3 = a0 + 3., a4 = a0 + 4., a5 = a0 + 5., a6 = a0 + 6., a7 = a0 + 7.;
+  const double b = 1.0000001, c = 1e-7;
+  for (int i = 0; i < iters; ++i) {
+    a0 = fma(a0, b, c); a1 = fma(a1, b, c); a2 = fma(a2, b, c); a3 = fma(a3, b, c);
+    a4 = fma(a4, b, c); a5 = fma(a5, b, c); a6 = fma(a6, b, c); a7 = fma(a7, b, c);
+  }
+  const double r = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+  if (r == 123.456) *sink = r;
+}
+
+}  // namespace rtb

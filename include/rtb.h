@@ -1,0 +1,251 @@
+/* rtb.h — C ABI of the B200-native path-tracing hot path (librtb200.so).
+ *
+ * This is the drop-in boundary.  The reference
+ * (Luke-TS/3360-ray-tracer) has no FFI of its own: its render loop is reached
+ * through two C++ seams, and every entry point below names the seam it stands
+ * behind (paths relative to the reference root):
+ *
+ *   seam 1  renderer::MegaKernel::Render            src/renderer/mega_kernel.h:15-54
+ *           renderer::WavefrontRenderer::Render     src/renderer/wavefront.cc:40-242
+ *   seam 2  integrator::RayIntegrator::IntersectBatch
+ *                                                   src/integrator/ray_integrator.h:30-37
+ *                                                   src/integrator/cpu_ray_integrator.h:18-46
+ *
+ * Plain pointers and sizes only; no C++/torch types.  Every call returns 0 on
+ * success and a negative RTB_E* code on failure; rtb_last_error() gives the
+ * text.  There is no CPU fallback: without a CUDA device every compute entry
+ * fails with RTB_ENODEVICE.
+ */
+#ifndef RTB_H_
+#define RTB_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTB_ABI_VERSION 1
+
+/* ---- status codes ------------------------------------------------------ */
+enum {
+  RTB_OK = 0,
+  RTB_EINVAL = -1,    /* bad argument / malformed scene description        */
+  RTB_ENODEVICE = -2, /* no usable CUDA device (never falls back to CPU)   */
+  RTB_ECUDA = -3,     /* CUDA runtime error, text in rtb_last_error()      */
+  RTB_ENOMEM = -4
+};
+
+/* ---- primitive / material / texture tags ------------------------------- */
+/* Primitive tags follow geom::HittableType (src/geom/hittable.h:45-49);
+ * SUBTREE is how a nested geom::Bvh inside a leaf is represented.          */
+enum { RTB_PRIM_SPHERE = 0, RTB_PRIM_TRIANGLE = 1, RTB_PRIM_RECT = 2, RTB_PRIM_SUBTREE = 3 };
+enum { RTB_MAT_LAMBERTIAN = 0, RTB_MAT_METAL = 1, RTB_MAT_DIELECTRIC = 2, RTB_MAT_DIFFUSE_LIGHT = 3 };
+enum { RTB_TEX_SOLID = 0, RTB_TEX_CHECKER = 1, RTB_TEX_IMAGE = 2 };
+/* Estimator: A = Camera::GetPixel + Material::Scatter (src/scene/camera.h:148-174),
+ *            B = WavefrontRenderer + Material::Sample + Russian roulette
+ *                (src/renderer/wavefront.cc:85-226).                        */
+enum { RTB_MODE_A = 0, RTB_MODE_B = 1 };
+
+/* Leaf reference: type in the top 2 bits, index into that type's table below. */
+#define RTB_REF(type, index) (((uint32_t)(type) << 30) | (uint32_t)(index))
+#define RTB_REF_TYPE(ref) ((ref) >> 30)
+#define RTB_REF_INDEX(ref) ((ref) & 0x3fffffffu)
+#define RTB_MAX_LEAF 63 /* leaf prim count must fit 6 bits (flattener splits larger) */
+
+/* ---- flattened scene (host arrays; rtb_scene_create copies them) ------- */
+
+/* 32-byte BVH node, replaces geom::BvhNodeGPU (src/geom/bvh.h:20-25).
+ * Box is the reference's double box rounded OUTWARD to float.
+ *   b == 0 : internal; children are nodes[a] (left) and nodes[a+1] (right)
+ *   b  > 0 : leaf; prim_refs[a .. a+b)                                      */
+typedef struct RtbNode {
+  float lo[3];
+  uint32_t a;
+  float hi[3];
+  uint32_t b;
+} RtbNode;
+
+/* geom::Sphere (src/geom/sphere.h:81-85): exact doubles for the replay.    */
+typedef struct RtbSphere {
+  double c[3];
+  double r;
+} RtbSphere;
+
+/* geom::Triangle (src/geom/triangle.h:105-108).  e1 = b-a, e2 = c-a are the
+ * doubles Triangle::Hit recomputes on every call (triangle.h:45-46).       */
+typedef struct RtbTriangle {
+  double a[3];
+  double e1[3];
+  double e2[3];
+  uint32_t mat;
+  uint32_t pad;
+} RtbTriangle; /* 80 B = 5 x 128-bit loads */
+
+/* geom::xy_rect / xz_rect / yz_rect (src/geom/rect.h).  axis = the constant
+ * axis (2 = xy_rect, 1 = xz_rect, 0 = yz_rect); (a,b) = the other two axes
+ * in increasing order.                                                     */
+typedef struct RtbRect {
+  double k;
+  double a0, a1, b0, b1;
+  int32_t axis;
+  uint32_t mat;
+} RtbRect; /* 48 B */
+
+typedef struct RtbMaterial {
+  int32_t type;   /* RTB_MAT_*                                   */
+  int32_t tex;    /* lambertian albedo / light emission texture  */
+  float albedo[3];/* metal                                       */
+  float fuzz;     /* metal, already min(fuzz,1) (material.cc:78-80) */
+  float ior;      /* dielectric                                  */
+  float pad;
+} RtbMaterial; /* 32 B */
+
+typedef struct RtbTexture {
+  int32_t type;  /* RTB_TEX_*                      */
+  int32_t image; /* image index, RTB_TEX_IMAGE     */
+  int32_t even;  /* texture index, RTB_TEX_CHECKER */
+  int32_t odd;
+  float color[3]; /* RTB_TEX_SOLID                 */
+  float inv_scale;/* RTB_TEX_CHECKER (texture.h:34) */
+} RtbTexture; /* 32 B */
+
+/* scene::Image byte table (src/scene/image.cc:43-48): width*height*3 bytes,
+ * already gamma-2.2-linearised and re-quantised exactly as the reference.
+ * width == 0 means "failed to load" (texture.h:61 -> cyan).                */
+typedef struct RtbImage {
+  int32_t width, height;
+  const uint8_t* rgb;
+} RtbImage;
+
+typedef struct RtbSceneDesc {
+  uint32_t abi_version; /* RTB_ABI_VERSION */
+  uint32_t n_nodes;     /* nodes[0] is the root; nodes[1] is padding so that sibling pairs are 64-B aligned */
+  const RtbNode* nodes;
+  uint32_t n_prim_refs;
+  const uint32_t* prim_refs;
+  uint32_t n_spheres;
+  const RtbSphere* spheres;
+  const uint32_t* sphere_mat;
+  uint32_t n_triangles;
+  const RtbTriangle* triangles;
+  uint32_t n_rects;
+  const RtbRect* rects;
+  /* per-type: global primitive id (creation order in the host scene) and the
+   * reference's DFS slot rank used only to break exact-t ties (bvh.h:95-106) */
+  const uint32_t* sphere_gid;
+  const uint32_t* triangle_gid;
+  const uint32_t* rect_gid;
+  const uint32_t* sphere_rank;
+  const uint32_t* triangle_rank;
+  const uint32_t* rect_rank;
+  uint32_t n_materials;
+  const RtbMaterial* materials;
+  uint32_t n_textures;
+  const RtbTexture* textures;
+  uint32_t n_images;
+  const RtbImage* images;
+  uint32_t n_top_nodes; /* nodes[0..n_top_nodes) are the BFS-ordered top levels (shared-memory stage) */
+  uint32_t max_depth;   /* deepest root-to-leaf path, for the traversal stack bound */
+} RtbSceneDesc;
+
+/* ---- rays and hits (seam 2) -------------------------------------------- */
+/* core::Ray (src/core/ray.h:7-26) + the core::Interval passed to Hit.
+ * Values are float; the reference sees exactly these values widened to double. */
+typedef struct RtbRay {
+  float o[3];
+  float tmin;
+  float d[3]; /* NOT normalised, as in the reference */
+  float tmax;
+} RtbRay; /* 32 B */
+
+typedef struct RtbHit {
+  double t;        /* HitRecord::t as the reference computes it (exact replay) */
+  int32_t prim_id; /* global primitive id, -1 = miss (HitRecord::hit false)    */
+  uint32_t ref;    /* RTB_REF(type,index) of the primitive                     */
+} RtbHit; /* 16 B */
+
+/* ---- camera / render (seam 1) ------------------------------------------ */
+/* What scene::Camera::Initialize derives (src/scene/camera.h:100-131).     */
+typedef struct RtbCamera {
+  int32_t width, height;
+  float center[3];
+  float pixel00[3];
+  float delta_u[3];
+  float delta_v[3];
+  float disk_u[3];
+  float disk_v[3];
+  float defocus_angle;
+  int32_t depth_camera; /* 1 = scene::DepthCamera semantics (camera.h:215-241) */
+} RtbCamera;
+
+typedef struct RtbRenderParams {
+  int32_t spp_begin;  /* this call renders global sample indices [spp_begin, spp_end) of every pixel */
+  int32_t spp_end;
+  int32_t max_depth;
+  int32_t mode;       /* RTB_MODE_A / RTB_MODE_B */
+  uint64_t seed;      /* Philox key */
+  uint32_t pool_size; /* live paths in flight, 0 = default */
+  uint32_t flags;     /* RTB_RENDER_* */
+} RtbRenderParams;
+#define RTB_RENDER_NO_SMEM_TOP 1u  /* do not stage the top BVH levels in shared memory */
+#define RTB_RENDER_KEEP_ACCUM 2u   /* add into the accumulator instead of zeroing it first */
+
+typedef struct RtbStats {
+  uint64_t samples;     /* camera samples started                      */
+  uint64_t rays;        /* closest-hit queries issued (Bvh::Hit calls) */
+  uint64_t node_visits; /* only when the library is built with RTB_COUNTERS */
+  uint64_t prim_tests;
+  uint64_t exact_tests;
+  uint32_t iterations;  /* wavefront iterations (one bounce each)      */
+  uint32_t launches;    /* kernels launched                            */
+  float ms_total;       /* CUDA-event time, first launch -> accumulator final */
+  float ms_generate;
+  float ms_extend;
+  float ms_shade;
+} RtbStats;
+
+typedef struct RtbScene RtbScene; /* opaque; owns all device memory of one scene on one GPU */
+
+const char* rtb_last_error(void);
+int rtb_abi_version(void);
+/* Number of visible CUDA devices (0 if none); never fails. */
+int rtb_device_count(void);
+/* Bind the calling thread to `device` and create the library's stream on it. */
+int rtb_init(int device);
+int rtb_shutdown(void);
+
+int rtb_scene_create(const RtbSceneDesc* desc, RtbScene** out);
+int rtb_scene_destroy(RtbScene* scene);
+
+/* seam 2: closest hit for n rays, host buffers (copies inside). */
+int rtb_intersect_batch(RtbScene* scene, const RtbRay* rays, size_t n, RtbHit* hits);
+/* same, device buffers, asynchronous on `stream` (a cudaStream_t, 0 = library stream). */
+int rtb_intersect_batch_device(RtbScene* scene, const RtbRay* d_rays, size_t n, RtbHit* d_hits,
+                               void* stream);
+
+/* seam 1: render; rgb_sum = width*height*3 floats, SUM of sample radiance
+ * (divide by the sample count, or pass it to rtb_resolve). Host buffer. */
+int rtb_render(RtbScene* scene, const RtbCamera* cam, const RtbRenderParams* params,
+               float* rgb_sum, RtbStats* stats);
+/* same, accumulator already on the device (e.g. a torch tensor that a
+ * following ncclReduce sums across GPUs). Synchronous on return. */
+int rtb_render_device(RtbScene* scene, const RtbCamera* cam, const RtbRenderParams* params,
+                      float* d_rgb_sum, RtbStats* stats);
+
+/* core::write_color (src/core/color.h:18-33): mean -> sqrt gamma -> clamp
+ * [0,0.999] -> int(256 x); done in double like the reference.  Device in/out. */
+int rtb_resolve_device(const float* d_rgb_sum, size_t n_pixels, int spp, uint8_t* d_rgb8,
+                       void* stream);
+int rtb_resolve(const float* rgb_sum, size_t n_pixels, int spp, uint8_t* rgb8);
+
+/* Microbenchmarks used for the roofline denominators (bench.py). */
+int rtb_measure_l2_gbs(size_t bytes, int iters, float* gbs);
+int rtb_measure_fp32_tflops(int iters, float* tflops);
+int rtb_measure_fp64_tflops(int iters, float* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTB_H_ */
