@@ -403,11 +403,15 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   unsigned long long generated = 0, rays = 0;
   uint32_t live = 0, iterations = 0, launches = 0;
   int cur = 0;
+  float ms_gen = 0.f, ms_ext = 0.f, ms_shd = 0.f;
+  cudaEvent_t ek[4];  // per-kernel timing on the launching stream: before generate / extend / shade, after shade
+  for (auto& e : ek) RTB_CUDA(cudaEventCreate(&e));
   // max_depth == 0: GetPixel returns black without tracing (camera.h:149-151)
   const bool trace = prm->max_depth > 0 || prm->mode == RTB_MODE_B || cam->depth_camera;
   while (trace) {
     const uint32_t room = pool - live;
     const uint32_t gen = (uint32_t)std::min<unsigned long long>(room, total - generated);
+    RTB_CUDA(cudaEventRecord(ek[0], st));
     if (gen) {
       rtb::generate_kernel<<<(gen + 255) / 256, 256, 0, st>>>(s->q[cur], live, gen, generated, rcst, s->pixel_order);
       generated += gen;
@@ -416,20 +420,31 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
     }
     if (live == 0) break;
     RTB_CUDA(cudaMemsetAsync(s->cursor, 0, 8, st));
+    RTB_CUDA(cudaEventRecord(ek[1], st));
     if (use_smem)
       rtb::extend_kernel<true><<<ext_grid, 128, s->smem_bytes, st>>>(s->dev, s->q[cur], live, s->hit_t, s->hit_ref, s->cursor, s->counters);
     else
       rtb::extend_kernel<false><<<ext_grid, 128, 0, st>>>(s->dev, s->q[cur], live, s->hit_t, s->hit_ref, s->cursor, s->counters);
+    RTB_CUDA(cudaEventRecord(ek[2], st));
     rtb::shade_kernel<<<(live + 255) / 256, 256, 0, st>>>(s->dev, s->q[cur], live, s->hit_t, s->hit_ref, s->q[cur ^ 1], s->cursor + 1,
                                                           d_rgb_sum, rcst);
+    RTB_CUDA(cudaEventRecord(ek[3], st));
     launches += 2;
     rays += live;
     RTB_CUDA(cudaMemcpyAsync(s->host_count, s->cursor + 1, 4, cudaMemcpyDeviceToHost, st));
     RTB_CUDA(cudaStreamSynchronize(st));
+    float a = 0.f, b = 0.f, c = 0.f;
+    cudaEventElapsedTime(&a, ek[0], ek[1]);
+    cudaEventElapsedTime(&b, ek[1], ek[2]);
+    cudaEventElapsedTime(&c, ek[2], ek[3]);
+    ms_gen += a;
+    ms_ext += b;
+    ms_shd += c;
     live = *s->host_count;
     cur ^= 1;
     ++iterations;
   }
+  for (auto& e : ek) cudaEventDestroy(e);
   RTB_CUDA(cudaEventRecord(ev1, st));
   RTB_CUDA(cudaEventSynchronize(ev1));
   RTB_CUDA(cudaGetLastError());
@@ -444,6 +459,9 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
     stats->iterations = iterations;
     stats->launches = launches;
     stats->ms_total = ms;
+    stats->ms_generate = ms_gen;
+    stats->ms_extend = ms_ext;
+    stats->ms_shade = ms_shd;
 #ifdef RTB_COUNTERS
     rtb::HitCounters hc{};
     cudaMemcpy(&hc, s->counters, sizeof(hc), cudaMemcpyDeviceToHost);

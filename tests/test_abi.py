@@ -1,0 +1,78 @@
+"""The C-ABI library loads and exports every symbol include/*.h declares (no compute without a GPU)."""
+import ctypes as C
+import re
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def declared(header):
+    text = (ROOT / "include" / header).read_text()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(rt[bh]_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_every_declared_symbol_is_exported(rt):
+    lib = rt.load()
+    names = declared("rtb.h") + declared("rth.h")
+    assert len(names) >= 28
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/ but not exported by librtb200.so"
+    assert set(rt.binding.RTB_SYMBOLS) == set(declared("rtb.h"))
+    assert set(rt.binding.RTH_SYMBOLS) == set(declared("rth.h"))
+
+
+def test_counters_build_exports_the_same_abi(rt):
+    lib = rt.load(counters=True)
+    for n in declared("rtb.h"):
+        assert hasattr(lib, n)
+
+
+def test_abi_version_and_struct_sizes(rt):
+    lib = rt.load()
+    assert lib.rtb_abi_version() == 1
+    assert C.sizeof(rt.binding.RtbNode) == 32
+    assert rt.RAY_DTYPE.itemsize == 32 and rt.HIT_DTYPE.itemsize == 16
+    assert C.sizeof(rt.binding.RtbCamera) == 88
+    assert C.sizeof(rt.binding.RtbRenderParams) == 32
+
+
+def test_no_cpu_fallback_without_device(rt):
+    lib = rt.load()
+    if lib.rtb_device_count() > 0:
+        pytest.skip("a GPU is present")
+    assert lib.rtb_init(0) == rt.RTB_ENODEVICE
+    hs = rt.HostScene.build("cornell")
+    with pytest.raises(rt.RtbError) as e:
+        rt.DeviceScene(hs)
+    assert e.value.code == rt.RTB_ENODEVICE and b"no CPU path" in lib.rtb_last_error()
+
+
+def test_scene_create_rejects_malformed_descriptions(rt):
+    lib = rt.load()
+    hs = rt.HostScene.build("cornell")
+    d = rt.binding.RtbSceneDesc.from_buffer_copy(hs.desc)
+    d.abi_version = 99
+    h = C.c_void_p()
+    assert lib.rtb_scene_create(C.byref(d), C.byref(h)) == rt.RTB_EINVAL
+    d = rt.binding.RtbSceneDesc.from_buffer_copy(hs.desc)
+    d.n_nodes = 3
+    assert lib.rtb_scene_create(C.byref(d), C.byref(h)) == rt.RTB_EINVAL
+    assert lib.rtb_scene_create(None, C.byref(h)) == rt.RTB_EINVAL
+
+
+def test_missing_library_fails_loudly(rt, monkeypatch, tmp_path):
+    monkeypatch.setattr(rt.binding, "PKG_DIR", tmp_path)
+    monkeypatch.setattr(rt.binding, "_LIBS", {})
+    with pytest.raises(ImportError):
+        rt.binding.load()
+
+
+def test_product_never_imports_the_oracle():
+    pkg = ROOT / "3360-ray-tracer_b200"
+    for p in list(pkg.rglob("*.py")) + list(pkg.rglob("*.h")) + list(pkg.rglob("*.cc")) + list(pkg.rglob("*.cu")) + list(pkg.rglob("*.cuh")):
+        text = p.read_text(errors="ignore")
+        assert "oracle" not in text.replace("for the oracle", "").replace("the oracle", "").replace("oracle export", "").replace("oracle's", "").lower() \
+            or "import oracle" not in text and "from oracle" not in text and "liboracle" not in text, p
