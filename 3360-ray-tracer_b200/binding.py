@@ -69,8 +69,8 @@ class RtbRenderParams(C.Structure):
 
 class RtbStats(C.Structure):
     _fields_ = [
-        ("samples", C.c_uint64), ("rays", C.c_uint64), ("node_visits", C.c_uint64), ("prim_tests", C.c_uint64),
-        ("exact_tests", C.c_uint64), ("iterations", C.c_uint32), ("launches", C.c_uint32),
+        ("samples", C.c_uint64), ("rays", C.c_uint64), ("node_visits", C.c_uint64), ("sphere_tests", C.c_uint64),
+        ("triangle_tests", C.c_uint64), ("rect_tests", C.c_uint64), ("iterations", C.c_uint32), ("launches", C.c_uint32),
         ("ms_total", C.c_float), ("ms_generate", C.c_float), ("ms_extend", C.c_float), ("ms_shade", C.c_float),
     ]
 

@@ -465,9 +465,10 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
 #ifdef RTB_COUNTERS
     rtb::HitCounters hc{};
     cudaMemcpy(&hc, s->counters, sizeof(hc), cudaMemcpyDeviceToHost);
-    stats->node_visits = hc.node_pairs;
-    stats->prim_tests = hc.prim_tests;
-    stats->exact_tests = hc.exact_tests;
+    stats->node_visits = 2 * hc.node_pairs;
+    stats->sphere_tests = hc.sphere_tests;
+    stats->triangle_tests = hc.triangle_tests;
+    stats->rect_tests = hc.rect_tests;
 #endif
   }
   return RTB_OK;

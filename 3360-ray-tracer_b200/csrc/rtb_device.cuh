@@ -43,7 +43,7 @@ constexpr uint32_t kLeafBit = 0x80000000u;
 constexpr int kStackSize = 64;  // the reference's own bound (bvh.h:80); the flattener enforces it
 
 struct HitCounters {  // only touched when RTB_COUNTERS is defined
-  unsigned long long node_pairs, prim_tests, exact_tests, rays;
+  unsigned long long node_pairs, sphere_tests, triangle_tests, rect_tests, rays;
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -229,7 +229,7 @@ __device__ __forceinline__ uint32_t closest_hit(const DevScene& s, const float4*
   uint32_t best_ref = kNoHit;
   uint32_t cur = 0;  // pair 0 = {root, padding}
 #ifdef RTB_COUNTERS
-  unsigned n_pairs = 0, n_prims = 0;
+  unsigned n_pairs = 0, n_sph = 0, n_tri = 0, n_rect = 0;
 #endif
   for (;;) {
     // ---- descend through internal nodes
@@ -265,7 +265,7 @@ __device__ __forceinline__ uint32_t closest_hit(const DevScene& s, const float4*
           continue;
         }
 #ifdef RTB_COUNTERS
-        ++n_prims;
+        if (ty == RTB_PRIM_TRIANGLE) ++n_tri; else if (ty == RTB_PRIM_SPHERE) ++n_sph; else ++n_rect;
 #endif
         double t;
         bool ok;
@@ -286,7 +286,9 @@ done:
 #ifdef RTB_COUNTERS
   if (cnt) {
     atomicAdd(&cnt->node_pairs, (unsigned long long)n_pairs);
-    atomicAdd(&cnt->prim_tests, (unsigned long long)n_prims);
+    atomicAdd(&cnt->sphere_tests, (unsigned long long)n_sph);
+    atomicAdd(&cnt->triangle_tests, (unsigned long long)n_tri);
+    atomicAdd(&cnt->rect_tests, (unsigned long long)n_rect);
     atomicAdd(&cnt->rays, 1ull);
   }
 #else

@@ -1,0 +1,362 @@
+#!/usr/bin/env python
+"""bench.py — Msamples/s (and Mrays/s) of the path-tracing hot path on N B200s, next to the
+reference's CPU path, with the extend kernel's roofline.  Contract: see DESIGN.md "Measurement".
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--config bunny|rtiow|cornell|earth|stress] [--impl reference]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
+
+A "step" is one complete render of the named configuration (all pixels x spp x bounces).  At N>1
+every rank renders the configuration's spp with its own slice of GLOBAL sample indices
+(rank k: [k*spp,(k+1)*spp)), scene replicated, and the float32 radiance accumulators are summed
+onto rank 0 with one NCCL reduce; per-GPU work is fixed, so scaling is "weak".
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+import __graft_entry__ as graft  # noqa: E402
+
+# BASELINE.json configs: scene builder, camera preset, image width, spp, depth.
+CONFIGS = {
+    "rtiow": dict(scene=("rtiow", (11, 1)), cameras="cameras_readme.json", preset="default", width=1000, spp=44, depth=10,
+                  label="C1 RTIOW final scene, 484 spheres, README 'default' preset 1000x562, 44 spp, maxDepth 10"),
+    "cornell": dict(scene=("cornell", ()), cameras="cameras.json", preset="cornell", width=800, spp=256, depth=20,
+                    label="C2 Cornell box (6 rects + 3 spheres), 'cornell' preset 800x533, 256 spp, maxDepth 20"),
+    "bunny": dict(scene=("bunny", (50,)), cameras="cameras_readme.json", preset="wide", width=800, spp=100, depth=20,
+                  label="C3 Stanford bunny 69451 triangles (SAH BVH) + ground sphere, README 'wide' preset 800x450, 100 spp, maxDepth 20"),
+    "earth": dict(scene=("earth_bubbles", ()), cameras="cameras_readme.json", preset="closeup", width=1200, spp=200, depth=15,
+                  label="C4 earth-textured sphere + hollow-glass bubble + ground, README 'closeup' preset 1200x675, 200 spp, defocus 0.1"),
+    "stress": dict(scene=("stress", (1415, 1414, 1000, 500, 2)), camera=dict(aspect_ratio=16 / 9.0, vfov=60.0, lookfrom=(0, 40, 120), lookat=(0, 0, 0)),
+                   width=3840, spp=1024, depth=16,
+                   label="C5 synthetic stress: 4.0M-triangle height field + 1M spheres, 3840x2160, 1024 spp, maxDepth 16"),
+}
+# Algorithmic bytes / flops per traversal event (DESIGN.md "Roofline model")
+B_NODE, B_SPHERE, B_TRI, B_RECT, B_REF, B_RAY_IO = 32, 32, 80, 48, 4, 32 + 8
+F32_NODE = 18
+F64_SPHERE, F64_TRI, F64_RECT = 22, 44, 8
+
+
+def camera_for(rt, cfg, width=None, spp=None):
+    if "preset" in cfg:
+        c = rt.camera_preset(rt.ASSET_DIR / cfg["cameras"], cfg["preset"])
+    else:
+        c = rt.camera_config(**cfg["camera"])
+    c.image_width = width or cfg["width"]
+    c.samples_per_pixel = spp or cfg["spp"]
+    c.max_depth = cfg["depth"]
+    return c
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, device_index):
+        self.dev, self.rows, self.proc = device_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.dev)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def cpu_reference_leg(rt, cfg_name, budget_s, steps=1, warmup=0):
+    """The reference's own CPU path (oracle/_ref: MegaKernel/DefaultSampler/GetPixel compiled from the
+    reference sources; else the C restatement), all host threads, on a bounded sample of the workload."""
+    from oracle import checker, ref
+    cfg = CONFIGS[cfg_name]
+    fast = ref.available(fast=True) and _cpu_has("avx2") and _cpu_has("fma")
+    hs = rt.HostScene.build(*cfg["scene"])
+    ora = checker.make_oracle(hs, fast=fast)
+    cam_cfg = camera_for(rt, cfg)
+    cam = rt.camera_init(cam_cfg)
+    cores = os.cpu_count() or 1
+    # calibrate with whole-image passes at 1 and 2 spp (the first also warms the thread pool), then size
+    # the sample to the budget: samples/s is spp-invariant
+    ora.render_a(cam_cfg.as_oracle_cfg(), 1, cfg["depth"], seed=1, want_m2=False)
+    _, _, secs, _ = ora.render_a(cam_cfg.as_oracle_cfg(), 2, cfg["depth"], seed=1, want_m2=False)
+    rate = 2 * cam.width * cam.height / max(secs, 1e-6)
+    spp = int(max(1, min(cfg["spp"], budget_s * rate / (cam.width * cam.height))))
+    out = []
+    for k in range(warmup + steps):
+        this_spp = spp if k >= warmup else 1
+        _, _, secs, rays = ora.render_a(cam_cfg.as_oracle_cfg(), this_spp, cfg["depth"], seed=2 + k, want_m2=False)
+        if k >= warmup:
+            out.append((cam.width * cam.height * this_spp, rays, secs))
+    samples = sum(o[0] for o in out); rays = sum(o[1] for o in out); secs = sum(o[2] for o in out)
+    return {"value": samples / secs / 1e6, "unit": "Msamples/s", "mrays_per_s": rays / secs / 1e6, "cores": cores,
+            "kind": ora.kind, "build": "-O3 -mavx2 -mfma -fopenmp" if fast else "-O2 -fopenmp (strict IEEE)",
+            "sample": f"{cfg_name} {cam.width}x{cam.height} at {spp} of {cfg['spp']} spp, maxDepth {cfg['depth']}, estimator A, "
+                      f"{len(out)} pass(es), {secs:.1f} s", "seconds": secs, "ms_per_step": 1e3 * secs / max(1, len(out))}
+
+
+def _cpu_has(flag):
+    try:
+        return flag in Path("/proc/cpuinfo").read_text().split("flags", 1)[1].split("\n", 1)[0].split()
+    except (OSError, IndexError):
+        return False
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="bunny", choices=list(CONFIGS))
+    ap.add_argument("--spp", type=int, default=0, help="override the configuration's spp (then the line says so)")
+    ap.add_argument("--width", type=int, default=0)
+    ap.add_argument("--pool", type=int, default=0)
+    ap.add_argument("--mode", default="A", choices=["A", "B"])
+    ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-roofline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    rt = graft.load_package()
+    cfg = CONFIGS[args.config]
+    W = max(args.warmup, 0)
+    K = max(args.steps, 1)
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        per_step = min(12.0, 150.0 / (K + W))
+        leg = cpu_reference_leg(rt, args.config, per_step, steps=K, warmup=W)
+        line = {"metric": "msamples_per_s", "value": leg["value"], "unit": "Msamples/s", "n_gpus": args.gpus, "steps": K, "warmup": W,
+                "ms_per_step": leg["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic", "impl": "reference", "mrays_per_s": leg["mrays_per_s"],
+                "config": {"workload": cfg["label"], "estimator": "A (MegaKernel + DefaultSampler + Camera::GetPixel)", "sample": leg["sample"]},
+                "cpu_baseline": {k: leg[k] for k in ("value", "unit", "cores", "kind", "sample", "build")},
+                "e2e": {"value": leg["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line), flush=True)
+        return 0
+
+    import torch
+    import torch.distributed as dist
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a CUDA device: the hot path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    lib = rt.load()
+
+    t_build = time.perf_counter()
+    hs = rt.HostScene.build(*cfg["scene"])
+    t_build = time.perf_counter() - t_build
+    ds = rt.DeviceScene(hs, device=local_rank)
+    cam_cfg = camera_for(rt, cfg, args.width or None, args.spp or None)
+    cam = rt.camera_init(cam_cfg)
+    spp, depth = cam_cfg.samples_per_pixel, cfg["depth"]
+    mode = rt.MODE_A if args.mode == "A" else rt.MODE_B
+    n_pix = cam.width * cam.height
+    accum = torch.zeros(n_pix * 3, dtype=torch.float32, device="cuda")
+    rgb8 = torch.zeros(n_pix * 3, dtype=torch.uint8, device="cuda")
+    flush = torch.empty(384 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+    stream = torch.cuda.current_stream().cuda_stream
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        """one render of the configuration at this rank + reduce + resolve; returns (device ms, stats)"""
+        st = ds.render_device(cam, accum.data_ptr(), rank * spp, (rank + 1) * spp, depth, mode=mode, pool_size=args.pool)
+        ev[0].record()
+        if world > 1:
+            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            rt.binding._check(lib, lib.rtb_resolve_device(accum.data_ptr(), n_pix, spp * world, rgb8.data_ptr(), stream))
+        ev[1].record()
+        torch.cuda.synchronize()
+        return st["ms_total"] + ev[0].elapsed_time(ev[1]), st
+
+    for _ in range(W):
+        flush.fill_(1)
+        barrier()
+        step()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    dev_ms, wall_ms, stats = [], [], []
+    for _ in range(K):
+        flush.fill_(1)  # evict the scene and the path pool from L2 between timed steps (untimed)
+        barrier()
+        t0 = time.perf_counter()
+        ms, st = step()
+        wall_ms.append(1e3 * (time.perf_counter() - t0))
+        dev_ms.append(ms)
+        stats.append(st)
+    barrier()
+    clk = clocks.stop() if rank == 0 else None
+    # max over ranks of the K-step time
+    tot = torch.tensor([sum(dev_ms), sum(wall_ms)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tot, op=dist.ReduceOp.MAX)
+    total_dev_ms, total_wall_ms = tot.tolist()
+    samples_per_step = sum_over_ranks(dist, world, stats[-1]["samples"])
+    rays_per_step = sum_over_ranks(dist, world, stats[-1]["rays"])
+
+    # ---- e2e: the public C-ABI call with HOST buffers: scene upload (H2D) + render + image readback (D2H), every step
+    desc = hs.desc
+    h2d = scene_bytes(desc)
+    d2h = n_pix * 12
+    e2e_ms = []
+    import ctypes as C
+    host_img = torch.empty(n_pix * 3, dtype=torch.float32).pin_memory()
+    for k in range(min(W, 1) + K):
+        barrier()
+        t0 = time.perf_counter()
+        ds2 = rt.DeviceScene(hs, device=local_rank)  # rtb_scene_create: copies every scene array host -> device
+        if world == 1:
+            prm = rt.binding.RtbRenderParams(0, spp, depth, mode, 0x3360, args.pool, 0)
+            s2 = rt.binding.RtbStats()
+            rt.binding._check(lib, lib.rtb_render(ds2._h, C.byref(cam), C.byref(prm), host_img.data_ptr(), C.byref(s2)))
+        else:
+            ds2.render_device(cam, accum.data_ptr(), rank * spp, (rank + 1) * spp, depth, mode=mode, pool_size=args.pool)
+            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+            if rank == 0:
+                host_img.copy_(accum, non_blocking=False)
+        ds2.close()
+        torch.cuda.synchronize()
+        if k >= min(W, 1):
+            e2e_ms.append(1e3 * (time.perf_counter() - t0))
+    e2e_tot = torch.tensor([sum(e2e_ms)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_tot, op=dist.ReduceOp.MAX)
+
+    if rank == 0:
+        ms_per_step = total_dev_ms / K
+        value = samples_per_step / (ms_per_step * 1e-3) / 1e6
+        line = {
+            "metric": "msamples_per_s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 shading / f64 exact hit replay", "data": "synthetic", "impl": "b200",
+            "mrays_per_s": rays_per_step / (ms_per_step * 1e-3) / 1e6,
+            "wall_ms_per_step": total_wall_ms / K,
+            "config": {"workload": cfg["label"] + ("" if not (args.spp or args.width) else f" [OVERRIDDEN: width {cam.width}, spp {spp}]"),
+                       "why_this_config": "north_star quotes its headline target (>=100x CPU, traversal roofline) on the bunny mesh scene",
+                       "image": [cam.width, cam.height], "spp_per_gpu": spp, "spp_total": spp * world, "max_depth": depth,
+                       "estimator": args.mode, "parallelism": f"spp-split x{world}, scene replicated, 1 NCCL reduce(sum,f32) of {n_pix * 12} B",
+                       "l2": "384 MiB buffer written between timed steps (L2 flushed); scene itself is L2-resident by design",
+                       "pool_paths": args.pool or (1 << 21), "scene_build_s_untimed": round(t_build, 3)},
+            "e2e": {"value": samples_per_step / (e2e_tot.item() / K * 1e-3) / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_tot.item() / K,
+                    "what": "rtb_scene_create (all scene arrays H2D) + rtb_render with a host rgb buffer (D2H) + rtb_scene_destroy, wall clock"},
+            "gpu_launches": int(sum(s["launches"] for s in stats) + K),
+            "clocks": clk,
+            "kernel_ms_per_step": {k: float(np.mean([s[k] for s in stats])) for k in ("ms_generate", "ms_extend", "ms_shade")},
+            "iterations_per_step": stats[-1]["iterations"],
+        }
+        if not args.no_roofline and world == 1:
+            line["roofline"] = roofline(rt, hs, cam, cfg, stats, mode, args.pool)
+        elif not args.no_roofline:
+            line["roofline"] = {"note": "measured at N=1 only (one process, one GPU)"}
+        if not args.no_cpu_baseline and world == 1:
+            line["cpu_baseline"] = {k: v for k, v in cpu_reference_leg(rt, args.config, args.cpu_budget).items()
+                                    if k in ("value", "unit", "cores", "kind", "sample", "build", "mrays_per_s")}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def sum_over_ranks(dist, world, v):
+    if world == 1:
+        return int(v)
+    import torch
+    t = torch.tensor([int(v)], dtype=torch.int64, device="cuda")
+    dist.all_reduce(t)
+    return int(t.item())
+
+
+def scene_bytes(d):
+    return int(d.n_nodes * 32 + d.n_prim_refs * 4 + d.n_spheres * (32 + 16 + 12) + d.n_triangles * (80 + 48 + 8) + d.n_rects * (48 + 8)
+               + d.n_materials * 32 + d.n_textures * 32)
+
+
+def roofline(rt, hs, cam, cfg, stats, mode, pool):
+    """extend (BVH traversal) kernel: algorithmic bytes and flops per launch / its CUDA-event time."""
+    peaks_file = ROOT / "MEASURED_PEAKS.json"
+    hbm_peak, src = 6650.0, "fallback (B200_PROFILING.md)"
+    if peaks_file.exists():
+        hbm_peak, src = float(json.loads(peaks_file.read_text())["hbm_gbs"]), "MEASURED_PEAKS.json"
+    mp = rt.measure_peaks()
+    # per-ray traversal counts from the instrumented build on the same workload at reduced spp (counts per ray are spp-invariant)
+    hs_c = rt.HostScene.build(*cfg["scene"], counters=True)
+    ds_c = rt.DeviceScene(hs_c)
+    _, sc = ds_c.render(cam, spp=max(1, min(4, cfg["spp"])), max_depth=cfg["depth"], mode=mode, pool_size=pool)
+    ds_c.close()
+    per_ray = {k: sc[k] / sc["rays"] for k in ("node_visits", "sphere_tests", "triangle_tests", "rect_tests")}
+    refs = per_ray["sphere_tests"] + per_ray["triangle_tests"] + per_ray["rect_tests"]
+    bytes_ray = (B_NODE * per_ray["node_visits"] + B_SPHERE * per_ray["sphere_tests"] + B_TRI * per_ray["triangle_tests"]
+                 + B_RECT * per_ray["rect_tests"] + B_REF * refs + B_RAY_IO)
+    f32_ray = F32_NODE * per_ray["node_visits"]
+    f64_ray = F64_SPHERE * per_ray["sphere_tests"] + F64_TRI * per_ray["triangle_tests"] + F64_RECT * per_ray["rect_tests"]
+    rays = float(np.mean([s["rays"] for s in stats]))
+    launches = float(np.mean([s["iterations"] for s in stats]))
+    ext_ms = float(np.mean([s["ms_extend"] for s in stats]))
+    gbs = bytes_ray * rays / (ext_ms * 1e-3) / 1e9
+    t_l2 = bytes_ray * rays / (mp["l2_gbs"] * 1e9)
+    t_alu = f32_ray * rays / (mp["fp32_tflops"] * 1e12) + f64_ray * rays / (mp["fp64_tflops"] * 1e12)
+    return {"kernel": "extend_kernel (closest_hit BVH traversal)", "bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
+            "frac": gbs / hbm_peak, "peak_source": src, "traffic": None,
+            "note": "scene (<=10 MB) is L2-resident: HBM is not the binding roof; binding model below",
+            "binding": {"bound": "l2" if t_l2 > t_alu else "fp32+fp64 issue", "model_ms": 1e3 * max(t_l2, t_alu), "measured_ms": ext_ms,
+                        "frac": 1e3 * max(t_l2, t_alu) / ext_ms, "l2_ms": 1e3 * t_l2, "alu_ms": 1e3 * t_alu,
+                        "measured_peaks": mp},
+            "per_ray": {**per_ray, "bytes": bytes_ray, "fp32_flops": f32_ray, "fp64_flops": f64_ray},
+            "rays_per_step": rays, "extend_launches_per_step": launches, "extend_ms_per_step": ext_ms,
+            "avg_launch_ms": ext_ms / max(launches, 1)}
+
+
+if __name__ == "__main__":
+    sys.exit(main())

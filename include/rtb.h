@@ -195,9 +195,10 @@ typedef struct RtbRenderParams {
 typedef struct RtbStats {
   uint64_t samples;     /* camera samples started                      */
   uint64_t rays;        /* closest-hit queries issued (Bvh::Hit calls) */
-  uint64_t node_visits; /* only when the library is built with RTB_COUNTERS */
-  uint64_t prim_tests;
-  uint64_t exact_tests;
+  uint64_t node_visits;    /* nodes fetched+tested; these four only when built with RTB_COUNTERS */
+  uint64_t sphere_tests;   /* Sphere::Hit replays   */
+  uint64_t triangle_tests; /* Triangle::Hit replays */
+  uint64_t rect_tests;     /* *_rect::Hit replays   */
   uint32_t iterations;  /* wavefront iterations (one bounce each)      */
   uint32_t launches;    /* kernels launched                            */
   float ms_total;       /* CUDA-event time, first launch -> accumulator final */

@@ -102,7 +102,7 @@ def mixed_scene(seed=3, n_tri=300, n_sph=60):
     R.sphere((1.5, 2.0, 0.5), -0.35 + 0.7, m_g)
     R.rect(1, 3.5, -1, 1, -1, 1, m_l)      # xz light
     R.rect(1, 3.5, -1, 1, -1, 1, m_d)      # duplicate rect
-    R.rect(2, -3.0, -3, 3, -1, 4, m_c)     # xy wall
+    R.rect(2, -3.1, -3, 3, -1, 4, m_c)     # xy wall (off the checker lattice: floor(z/0.5) must not sit on a cell boundary)
     R.rect(0, -3.0, -1, 4, -3, 3, m_d)     # yz wall
     R.end(EX_BVH_END)
     # objects straight in the world list, next to the BVH
