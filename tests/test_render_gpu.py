@@ -81,7 +81,8 @@ def test_keep_accum_flag_accumulates(rt, scenes):
 def test_depth_limit_semantics(rt, scenes):
     """max_depth 0 -> black without tracing (camera.h:149-151); max_depth 1 -> only emitters and sky."""
     _, ds = scenes["cornell"]
-    cam = rt.camera_init(rt.camera_config(aspect_ratio=1.5, image_width=60, vfov=40.0, lookfrom=(5, 5, -3.6), lookat=(5, 5, 5), focus_dist=9.0))
+    # vfov 80 so that the ceiling light (y = 9.99, x,z in [3,7]) is inside the frustum; the 'cornell' preset's 40 does not see it
+    cam = rt.camera_init(rt.camera_config(aspect_ratio=1.5, image_width=60, vfov=80.0, lookfrom=(5, 5, -3.6), lookat=(5, 5, 5), focus_dist=9.0))
     img0, st0 = ds.render(cam, spp=4, max_depth=0)
     assert not img0.any() and st0["rays"] == 0
     img1, st1 = ds.render(cam, spp=4, max_depth=1)
