@@ -11,6 +11,7 @@
 #include <string>
 #include <vector>
 
+#include "rtb_compile.h"
 #include "rtb_kernels.cuh"
 
 namespace {
@@ -178,8 +179,22 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
       return rc;             \
     }                        \
   } while (0)
-  PUT(s->Put(reinterpret_cast<const float4*>(d->nodes), 2 * (size_t)d->n_nodes, &v.nodes));
-  PUT(s->Put(d->prim_refs, d->n_prim_refs, &v.prim_refs));
+  {  // interchange tree -> device-native sibling pairs (rtb_compile.h)
+    rtbc::Compiled tree;
+    try {
+      tree = rtbc::Compiler(*d).Run();
+    } catch (const std::exception& e) {
+      rtb_scene_destroy(s);
+      return Fail(RTB_EINVAL, std::string("scene compile: ") + e.what());
+    }
+    if (tree.depth + 2 > (uint32_t)rtb::kStackSize) {
+      rtb_scene_destroy(s);
+      return Fail(RTB_EINVAL, "BVH deeper than the 64-entry traversal stack (bvh.h:80)");
+    }
+    PUT(s->Put(reinterpret_cast<const float4*>(tree.pairs.data()), 4 * tree.pairs.size(), &v.pairs));
+    v.n_pairs = (uint32_t)tree.pairs.size();
+    v.n_top_pairs = tree.top_pairs;
+  }
   PUT(s->Put(reinterpret_cast<const double2*>(d->spheres), 2 * (size_t)d->n_spheres, &v.spheres));
   PUT(s->Put(reinterpret_cast<const double2*>(d->triangles), 5 * (size_t)d->n_triangles, &v.triangles));
   PUT(s->Put(reinterpret_cast<const double2*>(d->rects), 3 * (size_t)d->n_rects, &v.rects));
@@ -194,10 +209,22 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
       float4 a = make_float4((float)t.a[0], (float)t.a[1], (float)t.a[2], 0.f);
       std::memcpy(&a.w, &t.mat, 4);
       tf[3 * (size_t)i] = a;
-      tf[3 * (size_t)i + 1] = make_float4((float)t.e1[0], (float)t.e1[1], (float)t.e1[2], 0.f);
-      tf[3 * (size_t)i + 2] = make_float4((float)t.e2[0], (float)t.e2[1], (float)t.e2[2], 0.f);
+      // .w = max |component| rounded up: the filters' error bounds (rtb_device.cuh triangle_filter)
+      auto mx = [](const double* e) { return rtbc::Up(std::max(std::fabs(e[0]), std::max(std::fabs(e[1]), std::fabs(e[2])))); };
+      tf[3 * (size_t)i + 1] = make_float4((float)t.e1[0], (float)t.e1[1], (float)t.e1[2], mx(t.e1));
+      tf[3 * (size_t)i + 2] = make_float4((float)t.e2[0], (float)t.e2[1], (float)t.e2[2], mx(t.e2));
     }
     PUT(s->Put(tf.data(), tf.size(), &v.triangle_f));
+    std::vector<float4> rf(2 * (size_t)d->n_rects);
+    for (uint32_t i = 0; i < d->n_rects; ++i) {
+      const RtbRect& r = d->rects[i];
+      rf[2 * (size_t)i] = make_float4((float)r.k, (float)r.a0, (float)r.a1, (float)r.b0);
+      float4 q = make_float4((float)r.b1, 0.f, 0.f, 0.f);
+      std::memcpy(&q.y, &r.axis, 4);
+      std::memcpy(&q.z, &r.mat, 4);
+      rf[2 * (size_t)i + 1] = q;
+    }
+    PUT(s->Put(rf.data(), rf.size(), &v.rect_f));
   }
   PUT(s->Put(d->sphere_mat, d->n_spheres, &v.sphere_mat));
   PUT(s->Put(d->sphere_gid, d->n_spheres, &v.sphere_gid));
@@ -246,9 +273,7 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
     PUT(s->Put(objs.data(), objs.size(), &v.image_tex));
     PUT(s->Put(dims.data(), dims.size(), &v.image_dim));
   }
-  v.n_nodes = d->n_nodes;
-  v.n_top_nodes = d->n_top_nodes;
-  s->smem_bytes = (size_t)d->n_top_nodes * sizeof(RtbNode);
+  s->smem_bytes = (size_t)v.n_top_pairs * 64;
   if (s->smem_bytes > 200 * 1024) {
     rtb_scene_destroy(s);
     return Fail(RTB_EINVAL, "n_top_nodes does not fit shared memory");
@@ -278,6 +303,10 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
 
 }  // extern "C"
 
+// Traversal CTAs are large so that one shared-memory copy of the top of the tree serves many warps
+// and most of the 228 KB stays L1 for the rest of the tree.
+constexpr int kTraceBlock = 256;
+
 // Persistent grid: as many CTAs as are co-resident on the whole chip.
 template <class K>
 static int PersistentGrid(K kernel, int block, size_t smem) {
@@ -297,15 +326,17 @@ int rtb_intersect_batch_device(RtbScene* s, const RtbRay* d_rays, size_t n, RtbH
   if (rc != RTB_OK) return rc;
   cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : g_stream;
   RTB_CUDA(cudaMemsetAsync(s->cursor, 0, 8, st));
-  const bool use_smem = s->dev.n_top_nodes > 0 && !std::getenv("RTB_NO_SMEM_TOP");
+  const bool use_smem = s->dev.n_top_pairs > 0 && !std::getenv("RTB_NO_SMEM_TOP");
   const float4* rays4 = reinterpret_cast<const float4*>(d_rays);
   if (use_smem) {
-    const int grid = PersistentGrid(rtb::intersect_batch_kernel<true>, 128, s->smem_bytes);
-    rtb::intersect_batch_kernel<true><<<grid, 128, s->smem_bytes, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->cursor, s->counters);
+    const int grid = PersistentGrid(rtb::intersect_batch_kernel<true>, kTraceBlock, s->smem_bytes);
+    rtb::intersect_batch_kernel<true><<<grid, kTraceBlock, s->smem_bytes, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->cursor, s->counters);
   } else {
-    const int grid = PersistentGrid(rtb::intersect_batch_kernel<false>, 128, 0);
-    rtb::intersect_batch_kernel<false><<<grid, 128, 0, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->cursor, s->counters);
+    const int grid = PersistentGrid(rtb::intersect_batch_kernel<false>, kTraceBlock, 0);
+    rtb::intersect_batch_kernel<false><<<grid, kTraceBlock, 0, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->cursor, s->counters);
   }
+  // second pass: the reference's exact t for filter-settled hits, and the global primitive ids
+  rtb::exact_t_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->counters);
   RTB_CUDA(cudaGetLastError());
   return RTB_OK;
 }
@@ -389,8 +420,8 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   rcst.spp_begin = prm->spp_begin;
   rcst.n_pixels = n_pixels;
   const unsigned long long total = (unsigned long long)n_pixels * (unsigned long long)(prm->spp_end - prm->spp_begin);
-  const bool use_smem = s->dev.n_top_nodes > 0 && !(prm->flags & RTB_RENDER_NO_SMEM_TOP) && !std::getenv("RTB_NO_SMEM_TOP");
-  const int ext_grid = use_smem ? PersistentGrid(rtb::extend_kernel<true>, 128, s->smem_bytes) : PersistentGrid(rtb::extend_kernel<false>, 128, 0);
+  const bool use_smem = s->dev.n_top_pairs > 0 && !(prm->flags & RTB_RENDER_NO_SMEM_TOP) && !std::getenv("RTB_NO_SMEM_TOP");
+  const int ext_grid = use_smem ? PersistentGrid(rtb::extend_kernel<true>, kTraceBlock, s->smem_bytes) : PersistentGrid(rtb::extend_kernel<false>, kTraceBlock, 0);
 
   cudaEvent_t ev0, ev1;
   RTB_CUDA(cudaEventCreate(&ev0));
@@ -422,9 +453,9 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
     RTB_CUDA(cudaMemsetAsync(s->cursor, 0, 8, st));
     RTB_CUDA(cudaEventRecord(ek[1], st));
     if (use_smem)
-      rtb::extend_kernel<true><<<ext_grid, 128, s->smem_bytes, st>>>(s->dev, s->q[cur], live, s->hit_t, s->hit_ref, s->cursor, s->counters);
+      rtb::extend_kernel<true><<<ext_grid, kTraceBlock, s->smem_bytes, st>>>(s->dev, s->q[cur], live, s->hit_t, s->hit_ref, s->cursor, s->counters);
     else
-      rtb::extend_kernel<false><<<ext_grid, 128, 0, st>>>(s->dev, s->q[cur], live, s->hit_t, s->hit_ref, s->cursor, s->counters);
+      rtb::extend_kernel<false><<<ext_grid, kTraceBlock, 0, st>>>(s->dev, s->q[cur], live, s->hit_t, s->hit_ref, s->cursor, s->counters);
     RTB_CUDA(cudaEventRecord(ek[2], st));
     rtb::shade_kernel<<<(live + 255) / 256, 256, 0, st>>>(s->dev, s->q[cur], live, s->hit_t, s->hit_ref, s->q[cur ^ 1], s->cursor + 1,
                                                           d_rgb_sum, rcst);

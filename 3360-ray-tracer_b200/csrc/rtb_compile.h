@@ -1,0 +1,284 @@
+// rtb_compile.h — host side of rtb_scene_create: RtbSceneDesc (the interchange layout of
+// include/rtb.h) -> the device-native traversal layout.
+//
+// The closest hit the kernels return is a pure function of (exact primitive tests, tie rule)
+// (rtb_device.cuh), so the device tree only has to be CONSERVATIVE, not equal to the reference's
+// geom::Bvh (src/geom/bvh.h:166-367).  That freedom is used here:
+//   * sibling PAIRS are the unit: one 64-byte record {lo0,desc0 | hi0,- | lo1,desc1 | hi1,-} per
+//     internal node, i.e. one 128-bit x4 fetch and both slab tests per traversal step;
+//   * a child descriptor says everything needed to continue (no second fetch): internal -> pair
+//     index; leaf -> primitive type, count and first index into that type's leaf-ordered table.
+//     The prim_refs indirection of the interchange layout disappears;
+//   * leaves are homogeneous: a reference leaf holding several primitive types (Cornell: 6 rects +
+//     3 spheres in one SAH-refused leaf) or nested geom::Bvh objects (RTB_PRIM_SUBTREE) is expanded
+//     into a small subtree, with boxes recomputed from the primitives, rounded outward;
+//   * pair 0 holds the root's two children (traversal starts there);
+//   * the first `top_pairs` records are in breadth-first order (the prefix the traversal kernels
+//     stage in shared memory), the rest depth-first, near the order rays walk them.
+#pragma once
+#include <rtb.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <deque>
+#include <stdexcept>
+#include <vector>
+
+namespace rtbc {
+
+constexpr uint32_t kLeafBit = 0x80000000u;
+constexpr uint32_t kMaxLeafCount = 32;      // 5-bit count-1 field
+constexpr uint32_t kMaxFirst = 1u << 24;    // 24-bit first-index field
+
+inline uint32_t LeafDesc(uint32_t type, uint32_t first, uint32_t count) {
+  return kLeafBit | (type << 29) | ((count - 1u) << 24) | first;
+}
+
+struct Box {
+  float lo[3], hi[3];
+  void Grow(const Box& o) {
+    for (int k = 0; k < 3; ++k) {
+      lo[k] = std::min(lo[k], o.lo[k]);
+      hi[k] = std::max(hi[k], o.hi[k]);
+    }
+  }
+  static Box Empty() { return Box{{INFINITY, INFINITY, INFINITY}, {-INFINITY, -INFINITY, -INFINITY}}; }
+};
+
+inline float Down(double v) {
+  float f = static_cast<float>(v);
+  if (static_cast<double>(f) > v) f = std::nextafterf(f, -INFINITY);
+  return f;
+}
+inline float Up(double v) {
+  float f = static_cast<float>(v);
+  if (static_cast<double>(f) < v) f = std::nextafterf(f, INFINITY);
+  return f;
+}
+
+struct Pair {  // 64 bytes, the device record
+  float lo0[3]; uint32_t d0;
+  float hi0[3]; uint32_t pad0;
+  float lo1[3]; uint32_t d1;
+  float hi1[3]; uint32_t pad1;
+};
+static_assert(sizeof(Pair) == 64, "pair record is one 64-byte fetch");
+
+struct Compiled {
+  std::vector<Pair> pairs;  // pairs[0] = the root's children; empty for an empty scene
+  uint32_t top_pairs = 0;
+  uint32_t depth = 0;       // deepest chain of pairs (stack bound)
+};
+
+class Compiler {
+ public:
+  explicit Compiler(const RtbSceneDesc& d) : d_(d) {}
+
+  Compiled Run() {
+    int root = FromNode(0, 0);
+    Compiled out;
+    if (root < 0) return out;  // nothing to hit: no pairs, the kernels report a miss for every ray
+    // Traversal starts at pair 0 = the root's two children (the root's own box is never tested: a
+    // ray that misses it misses both children).  A scene that is a single leaf is split in two.
+    if (nodes_[root].left < 0) {
+      const uint32_t d = nodes_[root].desc, ty = (d >> 29) & 3u, first = d & 0x00ffffffu, count = ((d >> 24) & 31u) + 1u;
+      const uint32_t half = count > 1 ? count / 2 : 1;  // one primitive: both children hold it (a self-tie never replaces)
+      const int l = NewLeaf(RunBox(ty, first, half), ty, first, half);
+      const int r = count > 1 ? NewLeaf(RunBox(ty, first + half, count - half), ty, first + half, count - half) : l;
+      root = NewInternal(l, r);
+    }
+    Layout(root, out);
+    return out;
+  }
+
+ private:
+  struct CNode {
+    Box box;
+    int left = -1, right = -1;  // CNode indices, -1/-1 = leaf
+    uint32_t desc = 0;          // leaf descriptor
+    uint32_t pair = 0;          // device pair index of an internal node's children
+  };
+
+  int NewLeaf(const Box& b, uint32_t type, uint32_t first, uint32_t count) {
+    if (first + count > kMaxFirst) throw std::runtime_error("more than 2^24 primitives of one type");
+    if (count > kMaxLeafCount) {  // split long runs under tight halves
+      const uint32_t half = count / 2;
+      const int l = NewLeaf(RunBox(type, first, half), type, first, half);
+      const int r = NewLeaf(RunBox(type, first + half, count - half), type, first + half, count - half);
+      return NewInternal(l, r);
+    }
+    CNode n;
+    n.box = b;
+    n.desc = LeafDesc(type, first, count);
+    nodes_.push_back(n);
+    return static_cast<int>(nodes_.size()) - 1;
+  }
+  int NewInternal(int l, int r) {
+    CNode n;
+    n.box = nodes_[l].box;
+    n.box.Grow(nodes_[r].box);
+    n.left = l;
+    n.right = r;
+    nodes_.push_back(n);
+    return static_cast<int>(nodes_.size()) - 1;
+  }
+
+  // Conservative float boxes from the exact primitive parameters (only used where a reference
+  // leaf had to be regrouped; the reference's own boxes are geom/sphere.h:17-21, triangle.h:18-39
+  // (1e-6 pad), rect.h:11-17 (1e-4 pad) — these are supersets of them up to rounding).
+  Box PrimBox(uint32_t type, uint32_t i) const {
+    Box b = Box::Empty();
+    if (type == RTB_PRIM_SPHERE) {
+      const RtbSphere& s = d_.spheres[i];
+      const double r = std::fabs(s.r);
+      for (int k = 0; k < 3; ++k) {
+        b.lo[k] = Down(s.c[k] - r);
+        b.hi[k] = Up(s.c[k] + r);
+      }
+    } else if (type == RTB_PRIM_TRIANGLE) {
+      const RtbTriangle& t = d_.triangles[i];
+      for (int k = 0; k < 3; ++k) {
+        const double v0 = t.a[k], v1 = t.a[k] + t.e1[k], v2 = t.a[k] + t.e2[k];
+        const double lo = std::min(v0, std::min(v1, v2)), hi = std::max(v0, std::max(v1, v2));
+        const double pad = 2e-6 + 1e-12 * std::max(std::fabs(lo), std::fabs(hi));
+        b.lo[k] = Down(lo - pad);
+        b.hi[k] = Up(hi + pad);
+      }
+    } else {
+      const RtbRect& r = d_.rects[i];
+      const int ka = r.axis == 0 ? 1 : 0, kb = r.axis == 2 ? 1 : 2;
+      b.lo[r.axis] = Down(r.k - 2e-4);
+      b.hi[r.axis] = Up(r.k + 2e-4);
+      b.lo[ka] = Down(r.a0); b.hi[ka] = Up(r.a1);
+      b.lo[kb] = Down(r.b0); b.hi[kb] = Up(r.b1);
+    }
+    return b;
+  }
+  Box RunBox(uint32_t type, uint32_t first, uint32_t count) const {
+    Box b = Box::Empty();
+    for (uint32_t i = 0; i < count; ++i) b.Grow(PrimBox(type, first + i));
+    return b;
+  }
+
+  // Balanced tree over a short list of already-built children.
+  int Combine(std::vector<int>& kids, size_t lo, size_t hi) {
+    if (hi - lo == 1) return kids[lo];
+    const size_t mid = lo + (hi - lo) / 2;
+    const int l = Combine(kids, lo, mid), r = Combine(kids, mid, hi);
+    return NewInternal(l, r);
+  }
+
+  // Interchange node -> CNode index (-1 when the subtree holds nothing).
+  int FromNode(uint32_t i, int guard) {
+    if (guard > 256) throw std::runtime_error("scene nesting too deep (cycle in RTB_PRIM_SUBTREE refs?)");
+    const RtbNode& n = d_.nodes[i];
+    if (!(n.lo[0] <= n.hi[0]) && n.b == 0) return -1;  // padding slot
+    Box nb;
+    for (int k = 0; k < 3; ++k) {
+      nb.lo[k] = n.lo[k];
+      nb.hi[k] = n.hi[k];
+    }
+    if (n.b == 0) {
+      const int l = FromNode(n.a, guard + 1), r = FromNode(n.a + 1, guard + 1);
+      if (l < 0 || r < 0) return l < 0 ? r : l;
+      const int id = NewInternal(l, r);
+      nodes_[id].box = nb;  // the reference's (outward-rounded) box is already the tight union
+      return id;
+    }
+    // leaf: group entries by type (each type's table indices are consecutive inside one leaf)
+    uint32_t first[3] = {0, 0, 0}, count[3] = {0, 0, 0};
+    std::vector<int> kids;
+    for (uint32_t k = 0; k < n.b; ++k) {
+      const uint32_t ref = d_.prim_refs[n.a + k], ty = RTB_REF_TYPE(ref), idx = RTB_REF_INDEX(ref);
+      if (ty == RTB_PRIM_SUBTREE) {
+        if (idx == i) continue;  // the flattener's "empty leaf" marker points at itself
+        const int sub = FromNode(idx, guard + 1);
+        if (sub >= 0) kids.push_back(sub);
+        continue;
+      }
+      if (count[ty] == 0) first[ty] = idx;
+      if (idx != first[ty] + count[ty]) throw std::runtime_error("leaf entries of one type must be consecutive in that type's table");
+      ++count[ty];
+    }
+    const int n_types = (count[0] > 0) + (count[1] > 0) + (count[2] > 0);
+    if (n_types == 1 && kids.empty()) {
+      const uint32_t ty = count[0] ? 0u : count[1] ? 1u : 2u;
+      return NewLeaf(nb, ty, first[ty], count[ty]);
+    }
+    for (uint32_t ty = 0; ty < 3; ++ty)
+      if (count[ty]) kids.push_back(NewLeaf(RunBox(ty, first[ty], count[ty]), ty, first[ty], count[ty]));
+    if (kids.empty()) return -1;
+    return Combine(kids, 0, kids.size());
+  }
+
+  static void SetChild(Pair& p, int side, const Box& b, uint32_t desc) {
+    float* lo = side ? p.lo1 : p.lo0;
+    float* hi = side ? p.hi1 : p.hi0;
+    for (int k = 0; k < 3; ++k) {
+      lo[k] = b.lo[k];
+      hi[k] = b.hi[k];
+    }
+    (side ? p.d1 : p.d0) = desc;
+    (side ? p.pad1 : p.pad0) = 0;
+  }
+
+  void Layout(int root, Compiled& out) {
+    // pair 0 holds the root itself next to an empty sibling; every internal node owns one pair
+    struct Unit { int a, b; uint32_t depth; };  // the two sibling CNodes stored in this pair
+    const uint32_t budget = std::max<uint32_t>(1u, d_.n_top_nodes / 2);
+    std::vector<Unit> order;
+    std::deque<Unit> bfs{Unit{nodes_[root].left, nodes_[root].right, 1}};
+    auto children = [&](const Unit& u, std::vector<Unit>& kids) {
+      kids.clear();
+      for (int n : {u.a, u.b})
+        if (nodes_[n].left >= 0) kids.push_back(Unit{nodes_[n].left, nodes_[n].right, u.depth + 1});
+    };
+    std::vector<Unit> kids;
+    while (!bfs.empty() && order.size() < budget) {
+      const Unit u = bfs.front();
+      bfs.pop_front();
+      order.push_back(u);
+      children(u, kids);
+      for (const Unit& k : kids) bfs.push_back(k);
+    }
+    out.top_pairs = static_cast<uint32_t>(order.size());
+    std::vector<Unit> dfs(bfs.rbegin(), bfs.rend());
+    while (!dfs.empty()) {
+      const Unit u = dfs.back();
+      dfs.pop_back();
+      order.push_back(u);
+      children(u, kids);
+      for (auto it = kids.rbegin(); it != kids.rend(); ++it) dfs.push_back(*it);
+    }
+    if (order.size() >= kLeafBit) throw std::runtime_error("too many BVH nodes");
+    // a node's children live in the pair whose .a is its left child
+    for (size_t p = 0; p < order.size(); ++p) {
+      out.depth = std::max(out.depth, order[p].depth);
+      pair_of_left_[order[p].a] = static_cast<uint32_t>(p);
+    }
+    out.pairs.resize(order.size());
+    for (size_t p = 0; p < order.size(); ++p) {
+      const Unit& u = order[p];
+      int side = 0;
+      for (int n : {u.a, u.b}) {
+        const CNode& c = nodes_[n];
+        SetChild(out.pairs[p], side++, c.box, c.left >= 0 ? pair_of_left_.at(c.left) : c.desc);
+      }
+    }
+  }
+
+  const RtbSceneDesc& d_;
+  std::vector<CNode> nodes_;
+  struct IntMap {  // CNode index -> pair index (dense)
+    std::vector<uint32_t> v;
+    uint32_t& operator[](int i) {
+      if (static_cast<size_t>(i) >= v.size()) v.resize(i + 1, 0);
+      return v[i];
+    }
+    uint32_t at(int i) const { return v.at(i); }
+  } pair_of_left_;
+};
+
+}  // namespace rtbc

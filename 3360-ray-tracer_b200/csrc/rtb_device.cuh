@@ -1,13 +1,20 @@
-// rtb_device.cuh — device-side scene view, RNG, exact primitive tests and the BVH traversal.
+// rtb_device.cuh — device-side scene view, RNG, primitive tests (FP32 filters + exact FP64
+// replays) and the BVH traversal loop.
 //
 // Numerical contract (DESIGN.md "Exactness"): the closest hit returned is the one
 // geom::Bvh::Hit (reference src/geom/bvh.h:71-119) returns for the same float ray widened to
-// double.  Box culling runs in FP32 and is only ever CONSERVATIVE (outward-rounded boxes plus an
-// error slack), while every primitive decision is an FP64/FP32 replay of the reference's own
-// arithmetic, operation by operation, with contraction disabled (__dmul_rn/__dadd_rn are never
-// fused).  Because the accepted set and the t values are then exactly the reference's, the
-// winner is a pure function of (t, tie rule) and does not depend on traversal order, which
-// frees the kernel to walk near-child-first.
+// double.  Three layers make that cheap:
+//   1. box culling runs in FP32 and is only ever CONSERVATIVE (outward-rounded boxes, slack on
+//      the slab comparison);
+//   2. every primitive is first classified by an FP32 (spheres: mixed FP64/FP32) FILTER that
+//      carries a rigorous running error bound: MISS (the reference certainly rejects), HIT with an
+//      interval [t-e, t+e] that certainly contains the reference's t, or UNSURE;
+//   3. only UNSURE candidates, and HITs whose interval overlaps the current best's, are decided
+//      by an EXACT replay of the reference's own arithmetic, operation by operation, with
+//      contraction disabled (__dmul_rn/__dadd_rn are never fused).
+// Because the accepted set and the order of the t values are then exactly the reference's, the
+// winner is a pure function of (t, tie rule) and does not depend on traversal order or on the
+// shape of the device tree, which frees the kernel to walk near-child-first over its own layout.
 #pragma once
 #include <cuda_runtime.h>
 #include <rtb.h>
@@ -17,13 +24,13 @@ namespace rtb {
 
 // ---------------------------------------------------------------------------------------------
 struct DevScene {
-  const float4* nodes;        // 2 x float4 per RtbNode
-  const uint32_t* prim_refs;
+  const float4* pairs;        // 4 x float4 per sibling pair (rtb_compile.h)
   const double2* spheres;     // RtbSphere  = 2 x double2
   const double2* triangles;   // RtbTriangle = 5 x double2 (last .y holds mat/pad bits)
   const double2* rects;       // RtbRect = 3 x double2
-  const float4* sphere_f;     // (cx,cy,cz,r) float, shading + pre-filter
-  const float4* triangle_f;   // 3 x float4: (a, mat bits) (e1, 0) (e2, 0)
+  const float4* sphere_f;     // (cx,cy,cz,r) float, shading frame
+  const float4* triangle_f;   // 3 x float4: (a, mat bits) (e1, max|e1|) (e2, max|e2|)
+  const float4* rect_f;       // 2 x float4: (k, a0, a1, b0) (b1, axis bits, mat bits, 0)
   const uint32_t* sphere_mat;
   const uint32_t* sphere_gid;
   const uint32_t* triangle_gid;
@@ -35,15 +42,23 @@ struct DevScene {
   const RtbTexture* textures;
   const cudaTextureObject_t* image_tex;  // one per image (0 when the image failed to load)
   const int2* image_dim;
-  uint32_t n_nodes, n_top_nodes;
+  uint32_t n_pairs, n_top_pairs;
 };
 
 constexpr uint32_t kNoHit = 0xffffffffu;
 constexpr uint32_t kLeafBit = 0x80000000u;
-constexpr int kStackSize = 64;  // the reference's own bound (bvh.h:80); the flattener enforces it
+constexpr int kStackSize = 64;  // the reference's own bound (bvh.h:80); rtb_scene_create enforces it
+constexpr float kU = 5.9604645e-8f;  // 2^-24, FP32 unit roundoff
+
+// leaf descriptor (rtb_compile.h): bit31 | type<<29 | (count-1)<<24 | first
+__device__ __forceinline__ uint32_t desc_type(uint32_t d) { return (d >> 29) & 3u; }
+__device__ __forceinline__ uint32_t desc_first(uint32_t d) { return d & 0x00ffffffu; }
+__device__ __forceinline__ uint32_t desc_more(uint32_t d) { return d & 0x1f000000u; }  // count-1 != 0
 
 struct HitCounters {  // only touched when RTB_COUNTERS is defined
-  unsigned long long node_pairs, sphere_tests, triangle_tests, rect_tests, rays;
+  unsigned long long node_pairs, sphere_tests, triangle_tests, rect_tests, rays, exact_evals, filter_violations;
+  unsigned long long max_steps, slow_rays;  // longest traversal (steps of one ray), rays above 2000 steps
+  float slow_ray[8];                        // one of them (o, tmin, d, tmax)
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -63,15 +78,14 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
 __device__ __forceinline__ float u01(uint32_t x) { return (x >> 8) * (1.0f / 16777216.0f); }  // [0,1)
 
 // ---------------------------------------------------------------------------------------------
-// Ray prepared for traversal.
+// Per-lane ray state of the traversal loop.
 struct TravRay {
   float ox, oy, oz, dx, dy, dz;
   float tmin, tmax;
-  // FP32 slab constants: t_near_i = fma(plane_near_i, inv_i, bn_i), t_far_i = fma(plane_far_i, inv_i, bf_i)
-  float ix, iy, iz;
-  float bnx, bny, bnz, bfx, bfy, bfz;
-  // FP64 replay constants
-  double a;  // |d|^2 exactly as Vec3::length_squared sums it (vec3.h:47-49)
+  // FP32 slab constants: t_plane = fma(plane, inv, b) with b = -o*inv; eabs bounds the absolute
+  // error of that form (|o*inv| * few ulp), the relative part is applied in slab_pair()
+  float ix, iy, iz, bx, by, bz, eabs;
+  float dmax;  // max |d_i|, used by the filters' error bounds
 };
 
 __device__ __forceinline__ float safe_dir(float d) {
@@ -85,58 +99,57 @@ __device__ __forceinline__ void prepare_ray(TravRay& r, float4 o, float4 d) {
   r.ix = __frcp_rn(safe_dir(d.x));
   r.iy = __frcp_rn(safe_dir(d.y));
   r.iz = __frcp_rn(safe_dir(d.z));
-  // computed t = fma(p, inv, -o*inv); |error| <= ~2^-23 (|o*inv| + |t|).  The |o*inv| part is
-  // folded into the per-axis constants here, the relative part is applied in box_hit().
-  const float kAbs = 4.0f * 1.1920929e-7f;
+  // computed t = fma(p, inv, -o*inv): |error| <= ~2^-23 (|o*inv| + |t|)
   const float ox = o.x * r.ix, oy = o.y * r.iy, oz = o.z * r.iz;
-  const float ex = kAbs * fabsf(ox), ey = kAbs * fabsf(oy), ez = kAbs * fabsf(oz);
-  r.bnx = -ox - ex; r.bny = -oy - ey; r.bnz = -oz - ez;
-  r.bfx = -ox + ex; r.bfy = -oy + ey; r.bfz = -oz + ez;
-  const double ddx = d.x, ddy = d.y, ddz = d.z;
-  r.a = __dadd_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)), __dmul_rn(ddz, ddz));
+  r.bx = -ox; r.by = -oy; r.bz = -oz;
+  r.eabs = 8.0f * kU * fmaxf(fabsf(ox), fmaxf(fabsf(oy), fabsf(oz)));
+  r.dmax = fmaxf(fabsf(d.x), fmaxf(fabsf(d.y), fabsf(d.z)));
 }
 
-// Conservative slab test against [tmin, tbest].  Returns entry distance in tn.
-__device__ __forceinline__ bool box_hit(const TravRay& r, float4 lo, float4 hi, float tbest, float& tn) {
-  const float nx = r.ix >= 0.f ? lo.x : hi.x, fx = r.ix >= 0.f ? hi.x : lo.x;
-  const float ny = r.iy >= 0.f ? lo.y : hi.y, fy = r.iy >= 0.f ? hi.y : lo.y;
-  const float nz = r.iz >= 0.f ? lo.z : hi.z, fz = r.iz >= 0.f ? hi.z : lo.z;
-  const float t0x = fmaf(nx, r.ix, r.bnx), t0y = fmaf(ny, r.iy, r.bny), t0z = fmaf(nz, r.iz, r.bnz);
-  const float t1x = fmaf(fx, r.ix, r.bfx), t1y = fmaf(fy, r.iy, r.bfy), t1z = fmaf(fz, r.iz, r.bfz);
-  tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, r.tmin));
-  const float tf = fminf(fminf(t1x, t1y), fminf(t1z, tbest));
-  // relative slack (~8 ulp each side); fminf/fmaxf drop a NaN operand, which is the conservative side
-  return fmaf(fabsf(tn), -1e-6f, tn) <= fmaf(fabsf(tf), 1e-6f, tf);
+// Conservative slab test of one box against [tmin, thi].  Returns the entry distance in tn.
+__device__ __forceinline__ bool slab(const TravRay& r, float4 lo, float4 hi, float thi, float& tn) {
+  const float ax = fmaf(lo.x, r.ix, r.bx), bx = fmaf(hi.x, r.ix, r.bx);
+  const float ay = fmaf(lo.y, r.iy, r.by), by = fmaf(hi.y, r.iy, r.by);
+  const float az = fmaf(lo.z, r.iz, r.bz), bz = fmaf(hi.z, r.iz, r.bz);
+  // fminf/fmaxf drop a NaN operand, which is the conservative side
+  tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), r.tmin));
+  const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), thi));
+  // tf*(1+2^-19) + 2 eabs >= tn*(1-..) - ..: relative slack ~32 ulp, absolute slack from prepare_ray
+  return tn <= fmaf(fabsf(tf), 1.9073486e-6f, tf) + (r.eabs + r.eabs + fabsf(tn) * 1.9073486e-6f);
 }
 
 // ---------------------------------------------------------------------------------------------
 // Exact replays.  Each returns true with the reference's HitRecord::t in `t` when the
 // reference's Hit() would return true for the interval (tmin, tmax) of the ORIGINAL ray.
 
+struct ExactRay {
+  double ox, oy, oz, dx, dy, dz, tmin, tmax;
+};
+
 // geom::Sphere::Hit, src/geom/sphere.h:23-55
-__device__ __forceinline__ bool sphere_exact(const DevScene& s, uint32_t idx, const TravRay& r, double& t) {
-  const double2 q0 = __ldg(&s.spheres[2 * idx]), q1 = __ldg(&s.spheres[2 * idx + 1]);
-  const double ocx = __dsub_rn(q0.x, (double)r.ox), ocy = __dsub_rn(q0.y, (double)r.oy), ocz = __dsub_rn(q1.x, (double)r.oz);
-  const double dx = r.dx, dy = r.dy, dz = r.dz;
-  const double h = __dadd_rn(__dadd_rn(__dmul_rn(dx, ocx), __dmul_rn(dy, ocy)), __dmul_rn(dz, ocz));
+__device__ __forceinline__ bool sphere_exact(const double2* __restrict__ table, uint32_t idx, const ExactRay& r, double& t) {
+  const double2 q0 = __ldg(&table[2 * (size_t)idx]), q1 = __ldg(&table[2 * (size_t)idx + 1]);
+  const double ocx = __dsub_rn(q0.x, r.ox), ocy = __dsub_rn(q0.y, r.oy), ocz = __dsub_rn(q1.x, r.oz);
+  // |d|^2 exactly as Vec3::length_squared sums it (vec3.h:47-49)
+  const double a = __dadd_rn(__dadd_rn(__dmul_rn(r.dx, r.dx), __dmul_rn(r.dy, r.dy)), __dmul_rn(r.dz, r.dz));
+  const double h = __dadd_rn(__dadd_rn(__dmul_rn(r.dx, ocx), __dmul_rn(r.dy, ocy)), __dmul_rn(r.dz, ocz));
   const double oc2 = __dadd_rn(__dadd_rn(__dmul_rn(ocx, ocx), __dmul_rn(ocy, ocy)), __dmul_rn(ocz, ocz));
   const double c = __dsub_rn(oc2, __dmul_rn(q1.y, q1.y));
-  const double disc = __dsub_rn(__dmul_rn(h, h), __dmul_rn(r.a, c));
+  const double disc = __dsub_rn(__dmul_rn(h, h), __dmul_rn(a, c));
   if (disc < 0) return false;
   const double sq = __dsqrt_rn(disc);
-  const double tmin = r.tmin, tmax = r.tmax;
-  double root = __ddiv_rn(__dsub_rn(h, sq), r.a);
-  if (!(tmin < root && root < tmax)) {
-    root = __ddiv_rn(__dadd_rn(h, sq), r.a);
-    if (!(tmin < root && root < tmax)) return false;
+  double root = __ddiv_rn(__dsub_rn(h, sq), a);
+  if (!(r.tmin < root && root < r.tmax)) {
+    root = __ddiv_rn(__dadd_rn(h, sq), a);
+    if (!(r.tmin < root && root < r.tmax)) return false;
   }
   t = root;
   return true;
 }
 
 // geom::Triangle::Hit, src/geom/triangle.h:41-87 (double products, float det/inv_det/u/v/t)
-__device__ __forceinline__ bool triangle_exact(const DevScene& s, uint32_t idx, const TravRay& r, double& t) {
-  const double2* p = s.triangles + 5 * (size_t)idx;
+__device__ __forceinline__ bool triangle_exact(const double2* __restrict__ table, uint32_t idx, const ExactRay& r, double& t) {
+  const double2* p = table + 5 * (size_t)idx;
   const double2 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2), q3 = __ldg(p + 3), q4 = __ldg(p + 4);
   const double ax = q0.x, ay = q0.y, az = q1.x, e1x = q1.y, e1y = q2.x, e1z = q2.y, e2x = q3.x, e2y = q3.y, e2z = q4.x;
   const double dx = r.dx, dy = r.dy, dz = r.dz;
@@ -148,7 +161,7 @@ __device__ __forceinline__ bool triangle_exact(const DevScene& s, uint32_t idx, 
   if (fabsf(det) < 1e-6f) return false;
   const float inv_det = __fdiv_rn(1.0f, det);
   const double inv = inv_det;
-  const double tx = __dsub_rn((double)r.ox, ax), ty = __dsub_rn((double)r.oy, ay), tz = __dsub_rn((double)r.oz, az);
+  const double tx = __dsub_rn(r.ox, ax), ty = __dsub_rn(r.oy, ay), tz = __dsub_rn(r.oz, az);
   const float u = __double2float_rn(__dmul_rn(__dadd_rn(__dadd_rn(__dmul_rn(tx, px), __dmul_rn(ty, py)), __dmul_rn(tz, pz)), inv));
   if (u < 0.0f || u > 1.0f) return false;
   // qvec = Cross(tvec, edge1)
@@ -159,14 +172,14 @@ __device__ __forceinline__ bool triangle_exact(const DevScene& s, uint32_t idx, 
   if (v < 0.0f || __fadd_rn(u, v) > 1.0f) return false;
   const float tf = __double2float_rn(__dmul_rn(__dadd_rn(__dadd_rn(__dmul_rn(e2x, qx), __dmul_rn(e2y, qy)), __dmul_rn(e2z, qz)), inv));
   const double td = tf;
-  if (td < (double)r.tmin || td > (double)r.tmax) return false;
+  if (td < r.tmin || td > r.tmax) return false;
   t = td;
   return true;
 }
 
 // geom::xy_rect / xz_rect / yz_rect::Hit, src/geom/rect.h:19-40,65-85,109-130
-__device__ __forceinline__ bool rect_exact(const DevScene& s, uint32_t idx, const TravRay& r, double& t) {
-  const double2* p = s.rects + 3 * (size_t)idx;
+__device__ __forceinline__ bool rect_exact(const double2* __restrict__ table, uint32_t idx, const ExactRay& r, double& t) {
+  const double2* p = table + 3 * (size_t)idx;
   const double2 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2);  // (k,a0) (a1,b0) (b1, axis|mat)
   const int axis = (int)(__double_as_longlong(q2.y) & 0xffffffffll);
   // constant axis k, in-plane axes (a,b) = the other two in increasing order
@@ -174,7 +187,7 @@ __device__ __forceinline__ bool rect_exact(const DevScene& s, uint32_t idx, cons
   const double oa = axis == 0 ? r.oy : r.ox, da = axis == 0 ? r.dy : r.dx;
   const double ob = axis == 2 ? r.oy : r.oz, db = axis == 2 ? r.dy : r.dz;
   const double tt = __ddiv_rn(__dsub_rn(q0.x, ok), dk);
-  if (!((double)r.tmin < tt && tt < (double)r.tmax)) return false;
+  if (!(r.tmin < tt && tt < r.tmax)) return false;
   const double a = __dadd_rn(oa, __dmul_rn(tt, da));
   const double b = __dadd_rn(ob, __dmul_rn(tt, db));
   if (a < q0.y || a > q1.x || b < q1.y || b > q2.x) return false;
@@ -182,13 +195,146 @@ __device__ __forceinline__ bool rect_exact(const DevScene& s, uint32_t idx, cons
   return true;
 }
 
+// One out-of-line entry for all three replays: it is the rare path (see the filters below), so
+// it must not bloat the traversal loop's registers or instruction footprint.  Everything travels
+// in registers (no references): returns the reference's t, or NaN when the reference rejects.
+__device__ __noinline__ double exact_eval(const double2* __restrict__ table, uint32_t type, uint32_t idx, float ox, float oy, float oz,
+                                          float dx, float dy, float dz, float tmin, float tmax) {
+  ExactRay r{(double)ox, (double)oy, (double)oz, (double)dx, (double)dy, (double)dz, (double)tmin, (double)tmax};
+  double t = 0.0;
+  bool ok;
+  if (type == RTB_PRIM_TRIANGLE) ok = triangle_exact(table, idx, r, t);
+  else if (type == RTB_PRIM_SPHERE) ok = sphere_exact(table, idx, r, t);
+  else ok = rect_exact(table, idx, r, t);
+  return ok ? t : __longlong_as_double(0x7ff8000000000000ll);
+}
+__device__ __forceinline__ const double2* exact_table(const DevScene& s, uint32_t type) {
+  return type == RTB_PRIM_TRIANGLE ? s.triangles : type == RTB_PRIM_SPHERE ? s.spheres : s.rects;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Filters.  Result classes; for kHit, t/e satisfy |t_reference - t| <= e.
+enum { kMiss = 0, kHit = 1, kUnsure = 2 };
+
+// Triangle: FP32 Moeller-Trumbore on the float copies of (a, e1, e2) with a running error bound.
+// With u = 2^-24, D = max|d_i|, M1 = max|e1_i|, M2 = max|e2_i|, MA = max|a_i|, MT = max|tvec_i|
+// (float inputs carry <= u relative representation error, every FP32 op <= u relative):
+//   |P - P^| <= 8u D M2 per component,  |DET - DET^| <= 48u D M1 M2,
+//   |T - T^| <= u (MA + MT),            |NU - NU^| <= 60u D M2 (MA+MT),
+//   |Q - Q^| <= 8u M1 (MA+MT),          |NV - NV^| <= 48u D M1 (MA+MT),  |NT - NT^| <= 54u M1 M2 (MA+MT).
+// All are rounded up to 64u below.  The reference's own float roundings of det/inv_det/u/v/t
+// (triangle.h:50-71) add <= 4u relative and are covered by the 8u term in rho.
+__device__ __forceinline__ int triangle_filter(const DevScene& s, uint32_t idx, const TravRay& r, float thi, float& t_out, float& e_out) {
+  const float4* p = s.triangle_f + 3 * (size_t)idx;
+  const float4 A = __ldg(p), E1 = __ldg(p + 1), E2 = __ldg(p + 2);
+  const float px = r.dy * E2.z - r.dz * E2.y, py = r.dz * E2.x - r.dx * E2.z, pz = r.dx * E2.y - r.dy * E2.x;
+  const float det = E1.x * px + E1.y * py + E1.z * pz;
+  const float w = E1.w * E2.w;
+  const float edet = (64.0f * kU) * w * r.dmax;
+  const float adet = fabsf(det);
+  if (adet + edet < 0.999999e-6f) return kMiss;  // triangle.h:55 rejects |det| < 1e-6
+  if (!(adet > 8.0f * edet) || !(adet - edet > 1.000001e-6f)) return kUnsure;
+  const float tx = r.ox - A.x, ty = r.oy - A.y, tz = r.oz - A.z;
+  const float sA = (64.0f * kU) * (fmaxf(fabsf(A.x), fmaxf(fabsf(A.y), fabsf(A.z))) + fmaxf(fabsf(tx), fmaxf(fabsf(ty), fabsf(tz))));
+  const float inv = __frcp_rn(det);
+  const float g = 1.25f * fabsf(inv);
+  const float rho = g * edet + 8.0f * kU;
+  const float u = (tx * px + ty * py + tz * pz) * inv;
+  const float eu = g * (sA * r.dmax * E2.w) + fabsf(u) * rho;
+  if (u < -eu || u > 1.0f + eu) return kMiss;
+  const float qx = ty * E1.z - tz * E1.y, qy = tz * E1.x - tx * E1.z, qz = tx * E1.y - ty * E1.x;
+  const float v = (r.dx * qx + r.dy * qy + r.dz * qz) * inv;
+  const float ev = g * (sA * r.dmax * E1.w) + fabsf(v) * rho;
+  const float euv = eu + ev + 4.0f * kU;
+  if (v < -ev || u + v > 1.0f + euv) return kMiss;
+  const float t = (E2.x * qx + E2.y * qy + E2.z * qz) * inv;
+  const float et = g * (sA * w) + fabsf(t) * rho;
+  if (t + et < r.tmin || t - et > thi) return kMiss;
+  t_out = t;
+  e_out = et;
+  const bool inside = u >= eu && v >= ev && u + v <= 1.0f - euv && t - et >= r.tmin && t + et <= r.tmax;
+  return inside ? kHit : kUnsure;
+}
+
+// Sphere: the cancellation-prone part (oc, h, c, disc — sphere.h:25-31) in FP64 with FMA, then
+// FP32 for the square root and the stable root forms (root1*root2 = c/a).  Relative error of
+// each root <= 16u unless disc is within its own rounding noise of 0.
+__device__ __forceinline__ int sphere_filter(const DevScene& s, uint32_t idx, const TravRay& r, float thi, float& t_out, float& e_out) {
+  const double2 q0 = __ldg(&s.spheres[2 * idx]), q1 = __ldg(&s.spheres[2 * idx + 1]);
+  const double ocx = q0.x - (double)r.ox, ocy = q0.y - (double)r.oy, ocz = q1.x - (double)r.oz;
+  const double dx = r.dx, dy = r.dy, dz = r.dz;
+  const double a = fma(dx, dx, fma(dy, dy, dz * dz));
+  const double h = fma(dx, ocx, fma(dy, ocy, dz * ocz));
+  const double oc2 = fma(ocx, ocx, fma(ocy, ocy, ocz * ocz));
+  const double r2 = q1.y * q1.y;
+  const double c = oc2 - r2;
+  const double h2 = h * h, ac = a * c;
+  const double disc = h2 - ac;
+  // double rounding noise of disc (and of the reference's own, differently-ordered, unfused sums)
+  const double noise = 1e-14 * (h2 + fabs(ac) + a * (oc2 + r2));
+  if (disc < -noise) return kMiss;
+  if (!(disc * 1e-3 > noise)) return kUnsure;  // grazing: sqrt amplifies the noise
+  const float rel_q = 0.5f * (float)(noise / disc) + 4.0f * kU;  // relative error of hf +- sq (same signs: no cancellation)
+  const float hf = (float)h, af = (float)a, cf = (float)c;
+  const float c_abs = (float)(4e-16 * (oc2 + r2));               // absolute error of c (origin on the surface: c ~ 0)
+  const float sq = sqrtf((float)disc);
+  // roots of a t^2 - 2 h t + c = 0 without cancellation (root1 * root2 = c / a)
+  const float qv = hf >= 0.0f ? hf + sq : hf - sq;
+  const float iq = __frcp_rn(qv);
+  const float td = qv / af, tc = cf * iq;
+  const float ed = fabsf(td) * (rel_q + 3.0f * kU) + 1e-37f;
+  const float ec = fabsf(tc) * (rel_q + 4.0f * kU) + c_abs * fabsf(iq) * 1.01f + 1e-37f;
+  const float t1 = hf >= 0.0f ? tc : td, e1 = hf >= 0.0f ? ec : ed;
+  const float t2 = hf >= 0.0f ? td : tc, e2 = hf >= 0.0f ? ed : ec;
+  // sphere.h:37-44: nearest root strictly inside (tmin, tmax), else the far root
+  const float lim = fminf(thi, r.tmax);
+  float t, e;
+  if (t1 - e1 > r.tmin) {
+    if (t1 - e1 > thi) return kMiss;  // both roots beyond the current best
+    if (!(t1 + e1 < r.tmax)) return t1 - e1 >= r.tmax ? kMiss : kUnsure;
+    t = t1; e = e1;
+  } else {
+    if (!(t1 + e1 < r.tmin)) return kUnsure;  // root1 straddles tmin
+    if (t2 + e2 <= r.tmin || t2 - e2 > lim) return kMiss;
+    if (!(t2 - e2 > r.tmin && t2 + e2 < r.tmax)) return kUnsure;
+    t = t2; e = e2;
+  }
+  t_out = t;
+  e_out = e;
+  return kHit;
+}
+
+// Rect: FP32 throughout (rect.h:19-40).  |t - t^| <= (u|k| + u|k-o_k|)/|d_k| + 3u|t|.
+__device__ __forceinline__ int rect_filter(const DevScene& s, uint32_t idx, const TravRay& r, float thi, float& t_out, float& e_out) {
+  const float4 q0 = __ldg(&s.rect_f[2 * (size_t)idx]), q1 = __ldg(&s.rect_f[2 * (size_t)idx + 1]);  // (k,a0,a1,b0) (b1,axis,mat,-)
+  const int axis = __float_as_int(q1.y);
+  const float ok = axis == 0 ? r.ox : axis == 1 ? r.oy : r.oz, dk = axis == 0 ? r.dx : axis == 1 ? r.dy : r.dz;
+  const float oa = axis == 0 ? r.oy : r.ox, da = axis == 0 ? r.dy : r.dx;
+  const float ob = axis == 2 ? r.oy : r.oz, db = axis == 2 ? r.dy : r.dz;
+  if (dk == 0.0f) return kMiss;  // t = +-inf or NaN: rect.h:22 rejects both
+  const float diff = q0.x - ok, inv = __frcp_rn(dk);
+  const float t = diff * inv;
+  const float et = 4.0f * kU * ((fabsf(q0.x) + fabsf(diff)) * fabsf(inv) + fabsf(t));
+  if (t + et <= r.tmin || t - et > fminf(thi, r.tmax)) return kMiss;
+  const float a = fmaf(t, da, oa), b = fmaf(t, db, ob);
+  const float ea = et * fabsf(da) + 4.0f * kU * (fabsf(oa) + fabsf(t * da)), eb = et * fabsf(db) + 4.0f * kU * (fabsf(ob) + fabsf(t * db));
+  // bounds are float roundings of the doubles: one more ulp each
+  const float a0 = q0.y, a1 = q0.z, b0 = q0.w, b1 = q1.x;
+  const float sa0 = ea + kU * fabsf(a0), sa1 = ea + kU * fabsf(a1), sb0 = eb + kU * fabsf(b0), sb1 = eb + kU * fabsf(b1);
+  if (a < a0 - sa0 || a > a1 + sa1 || b < b0 - sb0 || b > b1 + sb1) return kMiss;
+  t_out = t;
+  e_out = et;
+  const bool inside = a >= a0 + sa0 && a <= a1 - sa1 && b >= b0 + sb0 && b <= b1 - sb1 && t - et > r.tmin && t + et < r.tmax;
+  return inside ? kHit : kUnsure;
+}
+
 __device__ __forceinline__ uint32_t rank_of(const DevScene& s, uint32_t ref) {
   const uint32_t ty = RTB_REF_TYPE(ref), i = RTB_REF_INDEX(ref);
   return ty == RTB_PRIM_SPHERE ? __ldg(&s.sphere_rank[i]) : ty == RTB_PRIM_TRIANGLE ? __ldg(&s.triangle_rank[i]) : __ldg(&s.rect_rank[i]);
 }
 
-// Does candidate (t, ref) replace (best_t, best_ref)?  Strictly smaller t wins.  On an exact
-// tie the reference's slot order decides (bvh.h:95-106 visits slots in rank order with the
+// Does candidate (t, ref) replace (best_t, best_ref), both EXACT?  Strictly smaller t wins.  On an
+// exact tie the reference's slot order decides (bvh.h:95-106 visits slots in rank order with the
 // interval (tmin, closest)): Triangle::Hit accepts t == closest (triangle.h:74), Sphere/rect
 // use the strict Interval::Surrounds (sphere.h:39-41, rect.h:22) and so never replace.
 __device__ __forceinline__ bool replaces(const DevScene& s, double t, uint32_t ref, double best_t, uint32_t best_ref) {
@@ -201,101 +347,62 @@ __device__ __forceinline__ bool replaces(const DevScene& s, double t, uint32_t r
 }
 
 // ---------------------------------------------------------------------------------------------
-template <bool kUseSmem>
-__device__ __forceinline__ void load_pair(const DevScene& s, const float4* smem_nodes, uint32_t pair, float4& llo, float4& lhi,
-                                          float4& rlo, float4& rhi) {
-  if (kUseSmem && pair < s.n_top_nodes) {
-    const float4* p = smem_nodes + 2 * (size_t)pair;
-    llo = p[0]; lhi = p[1]; rlo = p[2]; rhi = p[3];
-  } else {
-    const float4* p = s.nodes + 2 * (size_t)pair;
-    llo = __ldg(p); lhi = __ldg(p + 1); rlo = __ldg(p + 2); rhi = __ldg(p + 3);
-  }
-}
+// Current best hit of a lane.  exact == true: td is the reference's t.  Otherwise the reference's
+// t lies in [tf - ef, tf + ef] (a filter HIT that no other candidate has contested yet).
+struct Best {
+  uint32_t ref;
+  float tf, ef;
+  float hi;  // float upper bound of the best t: the culling bound of the slab tests
+  double td;
+  bool exact;
+};
 
-__device__ __forceinline__ uint32_t node_desc(float4 lo, float4 hi) {
-  const uint32_t a = __float_as_uint(lo.w), b = __float_as_uint(hi.w);
-  return b == 0 ? a : (kLeafBit | (b << 25) | a);
-}
-
-// Closest hit.  Returns the primitive ref (kNoHit on a miss) and the reference's t.
-template <bool kUseSmem>
-__device__ __forceinline__ uint32_t closest_hit(const DevScene& s, const float4* smem_nodes, const TravRay& r, double& t_out,
-                                                HitCounters* cnt) {
-  uint32_t stack[kStackSize];
-  int sp = 0;
-  double best_t = r.tmax;
-  float best_f = r.tmax;  // float upper bound of best_t for the box test
-  uint32_t best_ref = kNoHit;
-  uint32_t cur = 0;  // pair 0 = {root, padding}
-#ifdef RTB_COUNTERS
-  unsigned n_pairs = 0, n_sph = 0, n_tri = 0, n_rect = 0;
-#endif
-  for (;;) {
-    // ---- descend through internal nodes
-    while (!(cur & kLeafBit)) {
-      float4 llo, lhi, rlo, rhi;
-      load_pair<kUseSmem>(s, smem_nodes, cur, llo, lhi, rlo, rhi);
-#ifdef RTB_COUNTERS
-      ++n_pairs;
-#endif
-      float tl, tr;
-      const bool hl = box_hit(r, llo, lhi, best_f, tl);
-      const bool hr = box_hit(r, rlo, rhi, best_f, tr);
-      const uint32_t dl = node_desc(llo, lhi), dr = node_desc(rlo, rhi);
-      if (hl && hr) {
-        const bool left_first = tl <= tr;
-        stack[sp++] = left_first ? dr : dl;
-        cur = left_first ? dl : dr;
-      } else if (hl || hr) {
-        cur = hl ? dl : dr;
-      } else {
-        if (sp == 0) goto done;
-        cur = stack[--sp];
-      }
-    }
-    // ---- leaf
-    {
-      const uint32_t first = cur & 0x01ffffffu, count = (cur >> 25) & 63u;
-      for (uint32_t i = 0; i < count; ++i) {
-        const uint32_t ref = __ldg(&s.prim_refs[first + i]);
-        const uint32_t ty = RTB_REF_TYPE(ref), idx = RTB_REF_INDEX(ref);
-        if (ty == RTB_PRIM_SUBTREE) {
-          stack[sp++] = idx;  // pair {subtree root, padding}
-          continue;
-        }
-#ifdef RTB_COUNTERS
-        if (ty == RTB_PRIM_TRIANGLE) ++n_tri; else if (ty == RTB_PRIM_SPHERE) ++n_sph; else ++n_rect;
-#endif
-        double t;
-        bool ok;
-        if (ty == RTB_PRIM_TRIANGLE) ok = triangle_exact(s, idx, r, t);
-        else if (ty == RTB_PRIM_SPHERE) ok = sphere_exact(s, idx, r, t);
-        else ok = rect_exact(s, idx, r, t);
-        if (ok && replaces(s, t, ref, best_t, best_ref)) {
-          best_t = t;
-          best_ref = ref;
-          best_f = __double2float_ru(t);
-        }
-      }
-      if (sp == 0) goto done;
-      cur = stack[--sp];
+// Fold one primitive into the lane's best hit.
+__device__ __forceinline__ void consider(const DevScene& s, const TravRay& r, uint32_t type, uint32_t idx, Best& b, HitCounters* cnt) {
+  float t = 0.f, e = 0.f;
+  int cls;
+  if (type == RTB_PRIM_TRIANGLE) cls = triangle_filter(s, idx, r, b.hi, t, e);
+  else if (type == RTB_PRIM_SPHERE) cls = sphere_filter(s, idx, r, b.hi, t, e);
+  else cls = rect_filter(s, idx, r, b.hi, t, e);
+  if (cls == kMiss) return;
+  const uint32_t ref = RTB_REF(type, idx);
+  if (cls == kHit) {
+    const float blo = b.exact ? __double2float_rd(b.td) : b.tf - b.ef;
+    if (t - e > b.hi) return;                                  // certainly farther than the best
+    if (b.ref == kNoHit || t + e < blo) {                      // certainly nearer: take it, still inexact
+      b.ref = ref; b.tf = t; b.ef = e; b.exact = false;
+      b.hi = t + e;
+      return;
     }
   }
-done:
+  // ---- rare path: decide by exact replays
 #ifdef RTB_COUNTERS
-  if (cnt) {
-    atomicAdd(&cnt->node_pairs, (unsigned long long)n_pairs);
-    atomicAdd(&cnt->sphere_tests, (unsigned long long)n_sph);
-    atomicAdd(&cnt->triangle_tests, (unsigned long long)n_tri);
-    atomicAdd(&cnt->rect_tests, (unsigned long long)n_rect);
-    atomicAdd(&cnt->rays, 1ull);
-  }
+  if (cnt) atomicAdd(&cnt->exact_evals, 1ull);
 #else
   (void)cnt;
 #endif
-  t_out = best_t;
-  return best_ref;
+  if (b.ref != kNoHit && !b.exact) {
+    const uint32_t bty = RTB_REF_TYPE(b.ref);
+    const double tb = exact_eval(exact_table(s, bty), bty, RTB_REF_INDEX(b.ref), r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, r.tmin, r.tmax);
+    if (tb == tb) {
+      b.td = tb;
+    } else {  // a filter HIT the reference rejects would be a bug in the bounds; keep the interval midpoint
+      b.td = (double)b.tf;
+#ifdef RTB_COUNTERS
+      if (cnt) atomicAdd(&cnt->filter_violations, 1ull);
+#endif
+    }
+    b.exact = true;
+    b.hi = __double2float_ru(b.td);
+  }
+  const double tc = exact_eval(exact_table(s, type), type, idx, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, r.tmin, r.tmax);
+  if (!(tc == tc)) return;
+  const double bt = b.ref == kNoHit ? (double)r.tmax : b.td;
+  if (replaces(s, tc, ref, bt, b.ref)) {
+    b.ref = ref; b.td = tc; b.exact = true;
+    b.tf = (float)tc; b.ef = 0.f;
+    b.hi = __double2float_ru(tc);
+  }
 }
 
 }  // namespace rtb

@@ -24,44 +24,210 @@ struct RenderConsts {
 };
 
 // Stage the breadth-first top of the tree in shared memory (one copy per CTA per launch).
-__device__ __forceinline__ void stage_top(const DevScene& s, float4* smem_nodes) {
-  const uint32_t n4 = 2 * s.n_top_nodes;
-  for (uint32_t i = threadIdx.x; i < n4; i += blockDim.x) smem_nodes[i] = __ldg(&s.nodes[i]);
+__device__ __forceinline__ void stage_top(const DevScene& s, float4* smem_pairs) {
+  const uint32_t n4 = 4 * s.n_top_pairs;
+  for (uint32_t i = threadIdx.x; i < n4; i += blockDim.x) smem_pairs[i] = __ldg(&s.pairs[i]);
   __syncthreads();
 }
 
-// ---- seam 2: RayIntegrator::IntersectBatch (src/integrator/cpu_ray_integrator.h:18-46) --------
-// Persistent warps pull 32 rays at a time from a global cursor.
-template <bool kUseSmem>
-__global__ void __launch_bounds__(128) intersect_batch_kernel(DevScene s, const float4* __restrict__ rays, uint32_t n,
-                                                              RtbHit* __restrict__ hits, unsigned int* cursor, HitCounters* cnt) {
-  extern __shared__ float4 smem_nodes[];
-  if (kUseSmem) stage_top(s, smem_nodes);
+// ---- the traversal loop shared by intersect_batch (seam 2) and extend (seam 1) ------------------
+// Persistent warps; every LANE owns one ray at a time and takes a new one from the global cursor
+// as soon as enough lanes of its warp have run dry (no lane waits for the warp's longest ray).
+// Per iteration the warp votes: the larger group — lanes standing at an internal pair, or lanes
+// standing at a leaf — takes one step, so at least half of the occupied lanes do useful work in
+// every issued instruction, whatever the mix of ray lengths.
+//
+// Io: { uint32_t n; load(i, float4& o, float4& d); store(i, ref, t, exact) }.
+#ifndef RTB_TRACE_MIN_BLOCKS
+#define RTB_TRACE_MIN_BLOCKS 3  // 256-thread CTAs per SM the traversal kernels are compiled for (register cap 85)
+#endif
+constexpr unsigned kFull = 0xffffffffu;
+constexpr int kRefillLanes = 8;    // refill when at least this many lanes are idle
+constexpr unsigned kChunk = 64;    // rays claimed per atomicAdd on the cursor
+
+template <bool kUseSmem, class Io>
+__device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem_pairs, Io io, unsigned int* cursor, HitCounters* cnt) {
   const unsigned lane = threadIdx.x & 31u;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  uint32_t stack[kStackSize];
+  int sp = 0;
+  TravRay r;
+  Best b;
+  uint32_t cur = 0, slot = 0;
+  bool active = false;
+  unsigned pool_next = 0, pool_end = 0;  // warp-uniform: claimed, not yet assigned ray indices
+  bool exhausted = false;                 // warp-uniform: the global cursor ran past n
+#ifdef RTB_COUNTERS
+  unsigned n_pairs = 0, n_sph = 0, n_tri = 0, n_rect = 0, n_rays = 0, steps = 0;
+#endif
+  // generic pointers: one load instruction serves the shared-memory prefix and the global rest
+  const float4* const top = kUseSmem ? smem_pairs : s.pairs;
+  const uint32_t n_top = kUseSmem ? s.n_top_pairs : 0u;
+
   for (;;) {
-    unsigned base = 0;
-    if (lane == 0) base = atomicAdd(cursor, 32u);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (base >= n) break;
-    const uint32_t i = base + lane;
-    if (i < n) {
-      TravRay r;
-      prepare_ray(r, __ldg(&rays[2 * (size_t)i]), __ldg(&rays[2 * (size_t)i + 1]));
-      double t;
-      const uint32_t ref = closest_hit<kUseSmem>(s, smem_nodes, r, t, cnt);
-      RtbHit h;
-      h.ref = ref;
-      if (ref == kNoHit) {
-        h.t = 0.0;
-        h.prim_id = -1;
-      } else {
-        const uint32_t ty = RTB_REF_TYPE(ref), idx = RTB_REF_INDEX(ref);
-        h.t = t;
-        h.prim_id = (int)(ty == RTB_PRIM_SPHERE ? s.sphere_gid[idx] : ty == RTB_PRIM_TRIANGLE ? s.triangle_gid[idx] : s.rect_gid[idx]);
+    // ---- refill idle lanes
+    unsigned idle = __ballot_sync(kFull, !active);
+    if (idle && !(exhausted && pool_next == pool_end) && (__popc(idle) >= kRefillLanes || idle == kFull)) {
+      for (int round = 0; round < 2 && idle; ++round) {
+        if (pool_next == pool_end) {
+          if (exhausted) break;
+          unsigned base = 0;
+          if (lane == 0) base = atomicAdd(cursor, kChunk);
+          base = __shfl_sync(kFull, base, 0);
+          if (base >= io.n) {
+            exhausted = true;
+            break;
+          }
+          pool_next = base;
+          pool_end = min(base + kChunk, io.n);
+          exhausted = pool_end == io.n;
+        }
+        const unsigned mine = pool_next + __popc(idle & lt_mask);
+        const bool take = !active && mine < pool_end;
+        if (take) {
+          float4 o, d;
+          io.load(mine, o, d);
+          prepare_ray(r, o, d);
+          slot = mine;
+          b.ref = kNoHit; b.tf = d.w; b.ef = 0.f; b.hi = d.w; b.td = (double)d.w; b.exact = true;
+          cur = 0;  // pair 0 = the root's two children
+          sp = 0;
+          active = true;
+          if (s.n_pairs == 0) {  // empty scene: Bvh::Hit returns false (bvh.h:72-73)
+            io.store(slot, kNoHit, d.w, (double)d.w, true);
+            active = false;
+          }
+#ifdef RTB_COUNTERS
+          ++n_rays;
+          steps = 0;
+#endif
+        }
+        pool_next = min(pool_next + (unsigned)__popc(idle), pool_end);
+        idle = __ballot_sync(kFull, !active);
       }
-      hits[i] = h;
+    }
+    const unsigned act = __ballot_sync(kFull, active);
+    if (!act) {
+      if (exhausted && pool_next == pool_end) break;
+      continue;
+    }
+    const bool at_leaf = active && (cur & kLeafBit);
+    const unsigned leaf_mask = __ballot_sync(kFull, at_leaf);
+    bool pop = false;
+    if (__popc(act & ~leaf_mask) >= __popc(leaf_mask)) {
+      // ---- node step: fetch one sibling pair, slab-test both, descend into the nearer hit
+      if (active && !at_leaf) {
+        const float4* p = ((kUseSmem && cur < n_top) ? top : s.pairs) + 4 * (size_t)cur;
+        const float4 llo = p[0], lhi = p[1], rlo = p[2], rhi = p[3];
+#ifdef RTB_COUNTERS
+        ++n_pairs;
+        ++steps;
+#endif
+        float tl, tr;
+        const bool hl = slab(r, llo, lhi, b.hi, tl);
+        const bool hr = slab(r, rlo, rhi, b.hi, tr);
+        const uint32_t dl = __float_as_uint(llo.w), dr = __float_as_uint(rlo.w);
+        if (hl && hr) {
+          const bool left_first = tl <= tr;
+          stack[sp++] = left_first ? dr : dl;
+          cur = left_first ? dl : dr;
+        } else if (hl || hr) {
+          cur = hl ? dl : dr;
+        } else {
+          pop = true;
+        }
+      }
+    } else {
+      // ---- leaf step: one primitive of the current leaf
+      if (at_leaf) {
+        const uint32_t type = desc_type(cur), idx = desc_first(cur);
+#ifdef RTB_COUNTERS
+        if (type == RTB_PRIM_TRIANGLE) ++n_tri; else if (type == RTB_PRIM_SPHERE) ++n_sph; else ++n_rect;
+#endif
+        consider(s, r, type, idx, b, cnt);
+        if (desc_more(cur)) cur += 1u - (1u << 24);  // first+1, count-1
+        else pop = true;
+      }
+    }
+    if (pop) {
+      if (sp > 0) {
+        cur = stack[--sp];
+      } else {
+        io.store(slot, b.ref, b.exact ? (float)b.td : b.tf, b.exact ? b.td : (double)b.tf, b.exact);
+        active = false;
+#ifdef RTB_COUNTERS
+        if (cnt) {
+          atomicMax(&cnt->max_steps, (unsigned long long)steps);
+          if (steps > 2000u && atomicAdd(&cnt->slow_rays, 1ull) == 0ull) {
+            cnt->slow_ray[0] = r.ox; cnt->slow_ray[1] = r.oy; cnt->slow_ray[2] = r.oz; cnt->slow_ray[3] = r.tmin;
+            cnt->slow_ray[4] = r.dx; cnt->slow_ray[5] = r.dy; cnt->slow_ray[6] = r.dz; cnt->slow_ray[7] = r.tmax;
+          }
+        }
+#endif
+      }
     }
   }
+#ifdef RTB_COUNTERS
+  if (cnt) {
+    atomicAdd(&cnt->node_pairs, (unsigned long long)n_pairs);
+    atomicAdd(&cnt->sphere_tests, (unsigned long long)n_sph);
+    atomicAdd(&cnt->triangle_tests, (unsigned long long)n_tri);
+    atomicAdd(&cnt->rect_tests, (unsigned long long)n_rect);
+    atomicAdd(&cnt->rays, (unsigned long long)n_rays);
+  }
+#endif
+}
+
+// ---- seam 2: RayIntegrator::IntersectBatch (src/integrator/cpu_ray_integrator.h:18-46) --------
+struct BatchIo {
+  uint32_t n;
+  const float4* rays;
+  RtbHit* hits;
+  const DevScene* s;
+  __device__ __forceinline__ void load(uint32_t i, float4& o, float4& d) const {
+    o = __ldg(&rays[2 * (size_t)i]);
+    d = __ldg(&rays[2 * (size_t)i + 1]);
+  }
+  // inexact hits carry the filter's t and ref with bit 31 of prim_id's slot marked for the
+  // exact_t pass below (prim_id is filled there)
+  __device__ __forceinline__ void store(uint32_t i, uint32_t ref, float, double td, bool exact) const {
+    RtbHit h;
+    h.ref = ref;
+    h.t = ref == kNoHit ? 0.0 : td;
+    h.prim_id = ref == kNoHit ? -1 : (exact ? 0 : 1);
+    hits[i] = h;
+  }
+};
+
+template <bool kUseSmem>
+__global__ void __launch_bounds__(256, RTB_TRACE_MIN_BLOCKS) intersect_batch_kernel(DevScene s, const float4* __restrict__ rays, uint32_t n,
+                                                              RtbHit* __restrict__ hits, unsigned int* cursor, HitCounters* cnt) {
+  extern __shared__ float4 smem_pairs[];
+  if (kUseSmem) stage_top(s, smem_pairs);
+  trace_loop<kUseSmem>(s, smem_pairs, BatchIo{n, rays, hits, &s}, cursor, cnt);
+}
+
+// Second pass of seam 2: HitRecord::t exactly as the reference computes it, for the hits the
+// traversal settled with the FP32 filter alone, and the global primitive id.  Fully convergent.
+__global__ void exact_t_kernel(DevScene s, const float4* __restrict__ rays, uint32_t n, RtbHit* __restrict__ hits, HitCounters* cnt) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  RtbHit h = hits[i];
+  if (h.ref == kNoHit) return;
+  const uint32_t ty = RTB_REF_TYPE(h.ref), idx = RTB_REF_INDEX(h.ref);
+  if (h.prim_id == 1) {
+    const float4 o = __ldg(&rays[2 * (size_t)i]), d = __ldg(&rays[2 * (size_t)i + 1]);
+    const double t = exact_eval(exact_table(s, ty), ty, idx, o.x, o.y, o.z, d.x, d.y, d.z, o.w, d.w);
+    const bool ok = t == t;
+    if (ok) h.t = t;
+#ifdef RTB_COUNTERS
+    if (!ok && cnt) atomicAdd(&cnt->filter_violations, 1ull);
+#else
+    (void)cnt;
+#endif
+  }
+  h.prim_id = (int)(ty == RTB_PRIM_SPHERE ? s.sphere_gid[idx] : ty == RTB_PRIM_TRIANGLE ? s.triangle_gid[idx] : s.rect_gid[idx]);
+  hits[i] = h;
 }
 
 // ---- generate: Camera::GetRay + SampleSquare + defocus_disk_sample (camera.h:134-144,196-203) --
@@ -102,27 +268,28 @@ __global__ void generate_kernel(PathQueue q, uint32_t q_offset, uint32_t count, 
 }
 
 // ---- extend: Bvh::Hit for every live path (src/geom/bvh.h:71-119) ------------------------------
-template <bool kUseSmem>
-__global__ void __launch_bounds__(128) extend_kernel(DevScene s, PathQueue q, uint32_t n, float* __restrict__ hit_t,
-                                                     uint32_t* __restrict__ hit_ref, unsigned int* cursor, HitCounters* cnt) {
-  extern __shared__ float4 smem_nodes[];
-  if (kUseSmem) stage_top(s, smem_nodes);
-  const unsigned lane = threadIdx.x & 31u;
-  for (;;) {
-    unsigned base = 0;
-    if (lane == 0) base = atomicAdd(cursor, 32u);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (base >= n) break;
-    const uint32_t i = base + lane;
-    if (i < n) {
-      TravRay r;
-      prepare_ray(r, q.ro[i], q.rd[i]);
-      double t;
-      const uint32_t ref = closest_hit<kUseSmem>(s, smem_nodes, r, t, cnt);
-      hit_t[i] = (float)t;
-      hit_ref[i] = ref;
-    }
+struct ExtendIo {
+  uint32_t n;
+  const float4* ro;
+  const float4* rd;
+  float* hit_t;
+  uint32_t* hit_ref;
+  __device__ __forceinline__ void load(uint32_t i, float4& o, float4& d) const {
+    o = ro[i];
+    d = rd[i];
   }
+  __device__ __forceinline__ void store(uint32_t i, uint32_t ref, float tf, double, bool) const {
+    hit_t[i] = tf;
+    hit_ref[i] = ref;
+  }
+};
+
+template <bool kUseSmem>
+__global__ void __launch_bounds__(256, RTB_TRACE_MIN_BLOCKS) extend_kernel(DevScene s, PathQueue q, uint32_t n, float* __restrict__ hit_t,
+                                                     uint32_t* __restrict__ hit_ref, unsigned int* cursor, HitCounters* cnt) {
+  extern __shared__ float4 smem_pairs[];
+  if (kUseSmem) stage_top(s, smem_pairs);
+  trace_loop<kUseSmem>(s, smem_pairs, ExtendIo{n, q.ro, q.rd, hit_t, hit_ref}, cursor, cnt);
 }
 
 __device__ __forceinline__ void add_radiance(float* accum, uint32_t pixel, f3 L) {

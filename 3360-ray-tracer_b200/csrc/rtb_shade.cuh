@@ -101,15 +101,13 @@ __device__ __forceinline__ void surface_at(const DevScene& s, uint32_t ref, f3 p
     n_out = normalize3(cross3(mk3(e1.x, e1.y, e1.z), mk3(e2.x, e2.y, e2.z)));
     mat = __float_as_uint(a.w);
   } else {
-    const double2* q = s.rects + 3 * (size_t)idx;
-    const double2 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2);
-    const long long bits = __double_as_longlong(q2.y);
-    const int axis = (int)(bits & 0xffffffffll);
-    mat = (uint32_t)((unsigned long long)bits >> 32);
+    const float4 q0 = __ldg(&s.rect_f[2 * (size_t)idx]), q1 = __ldg(&s.rect_f[2 * (size_t)idx + 1]);  // (k,a0,a1,b0) (b1,axis,mat,-)
+    const int axis = __float_as_int(q1.y);
+    mat = __float_as_uint(q1.z);
     n_out = mk3(axis == 0 ? 1.0f : 0.0f, axis == 1 ? 1.0f : 0.0f, axis == 2 ? 1.0f : 0.0f);
     const float pa = axis == 0 ? p.y : p.x, pb = axis == 2 ? p.y : p.z;
-    u = (pa - (float)q0.y) / (float)(q1.x - q0.y);
-    v = (pb - (float)q1.y) / (float)(q2.x - q1.y);
+    u = (pa - q0.y) / (q0.z - q0.y);
+    v = (pb - q0.w) / (q1.x - q0.w);
   }
 }
 
