@@ -19,7 +19,7 @@ ASSET_DIR = REPO_ROOT / "assets"
 RTB_OK, RTB_EINVAL, RTB_ENODEVICE, RTB_ECUDA, RTB_ENOMEM = 0, -1, -2, -3, -4
 PRIM_SPHERE, PRIM_TRIANGLE, PRIM_RECT, PRIM_SUBTREE = 0, 1, 2, 3
 MODE_A, MODE_B = 0, 1
-RENDER_NO_SMEM_TOP, RENDER_KEEP_ACCUM = 1, 2
+RENDER_NO_SMEM_TOP, RENDER_KEEP_ACCUM, RENDER_SERIAL = 1, 2, 4
 EX_SPHERE, EX_TRIANGLE, EX_RECT, EX_BVH_BEGIN, EX_BVH_END, EX_LIST_BEGIN, EX_LIST_END = 0, 1, 2, 10, 11, 12, 13
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_DIFFUSE_LIGHT = 0, 1, 2, 3
 TEX_SOLID, TEX_CHECKER, TEX_IMAGE = 0, 1, 2

@@ -46,6 +46,44 @@ int Upload(const T* host, size_t n, T** dev) {
   return RTB_OK;
 }
 
+// Wavefront state, per host thread (= per device), allocated lazily by rtb_render* and kept across
+// scenes and calls.  A Wave is one independent wavefront: its own path pool (two queues), hit
+// arrays, counters and stream.  Several waves are kept in flight so that the drain tail of one
+// wave's persistent extend kernel, and the host's read of its survivor count, overlap the other
+// waves' kernels.
+struct Wave {
+  rtb::PathQueue q[2]{};
+  float* hit_t = nullptr;
+  uint32_t* hit_ref = nullptr;
+  unsigned int* counts = nullptr;      // device: [0] extend cursor, [1] shade survivor count
+  unsigned int* host_count = nullptr;  // pinned
+  cudaStream_t stream = nullptr;
+  cudaEvent_t done = nullptr;
+  std::vector<void*> mem;
+  uint32_t live = 0;
+  int cur = 0;
+  bool pending = false;
+};
+struct RenderCtx {
+  std::vector<Wave> waves;
+  uint32_t pool = 0;
+  uint32_t* pixel_order = nullptr;
+  int order_w = 0, order_h = 0;
+};
+thread_local RenderCtx g_ctx;
+
+void FreeWaves(RenderCtx* s) {
+  for (auto& w : s->waves) {
+    if (w.stream) cudaStreamSynchronize(w.stream);
+    for (void* p : w.mem) cudaFree(p);
+    if (w.host_count) cudaFreeHost(w.host_count);
+    if (w.done) cudaEventDestroy(w.done);
+    if (w.stream) cudaStreamDestroy(w.stream);
+  }
+  s->waves.clear();
+  s->pool = 0;
+}
+
 }  // namespace
 
 struct RtbScene {
@@ -58,14 +96,6 @@ struct RtbScene {
   unsigned int* host_count = nullptr;  // pinned
   size_t smem_bytes = 0;
   int device = 0;
-  // path pool (allocated lazily by rtb_render*)
-  uint32_t pool = 0;
-  rtb::PathQueue q[2]{};
-  float* hit_t = nullptr;
-  uint32_t* hit_ref = nullptr;
-  uint32_t* pixel_order = nullptr;
-  int order_w = 0, order_h = 0;
-
   template <class T>
   int Put(const T* host, size_t n, const T** out) {
     T* d = nullptr;
@@ -97,7 +127,7 @@ int rtb_init(int device) {
   if (device < 0 || device >= n) return Fail(RTB_EINVAL, "device index out of range");
   RTB_CUDA(cudaSetDevice(device));
   if (g_stream && g_device == device) return RTB_OK;
-  if (g_stream) cudaStreamDestroy(g_stream);
+  if (g_stream) rtb_shutdown();  // switching device: the wavefront pools belong to the old one
   RTB_CUDA(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking));
   cudaDeviceProp prop;
   RTB_CUDA(cudaGetDeviceProperties(&prop, device));
@@ -109,6 +139,10 @@ int rtb_init(int device) {
 int rtb_shutdown(void) {
   if (g_stream) {
     cudaStreamSynchronize(g_stream);
+    FreeWaves(&g_ctx);
+    if (g_ctx.pixel_order) cudaFree(g_ctx.pixel_order);
+    g_ctx.pixel_order = nullptr;
+    g_ctx.order_w = g_ctx.order_h = 0;
     cudaStreamDestroy(g_stream);
     g_stream = nullptr;
     g_device = -1;
@@ -363,22 +397,29 @@ int rtb_intersect_batch(RtbScene* s, const RtbRay* rays, size_t n, RtbHit* hits)
   return RTB_OK;
 }
 
-static int EnsurePool(RtbScene* s, uint32_t pool, int w, int h) {
-  if (s->pool != pool) {
-    // (re)allocate the two queues + hit arrays as one slab each
-    auto alloc = [&](void** p, size_t bytes) -> cudaError_t {
-      cudaError_t e = cudaMalloc(p, bytes);
-      if (e == cudaSuccess) s->allocs.push_back(*p);
-      return e;
-    };
-    for (int k = 0; k < 2; ++k) {
-      RTB_CUDA(alloc(reinterpret_cast<void**>(&s->q[k].ro), (size_t)pool * 16));
-      RTB_CUDA(alloc(reinterpret_cast<void**>(&s->q[k].rd), (size_t)pool * 16));
-      RTB_CUDA(alloc(reinterpret_cast<void**>(&s->q[k].thr), (size_t)pool * 16));
-      RTB_CUDA(alloc(reinterpret_cast<void**>(&s->q[k].meta), (size_t)pool * 8));
+static int EnsurePool(RenderCtx* s, uint32_t pool, size_t n_waves, int w, int h) {
+  if (s->pool != pool || s->waves.size() < n_waves) {
+    FreeWaves(s);
+    s->waves.resize(n_waves);
+    for (auto& wv : s->waves) {
+      auto alloc = [&](void** p, size_t bytes) -> cudaError_t {
+        cudaError_t e = cudaMalloc(p, bytes);
+        if (e == cudaSuccess) wv.mem.push_back(*p);
+        return e;
+      };
+      for (int k = 0; k < 2; ++k) {
+        RTB_CUDA(alloc(reinterpret_cast<void**>(&wv.q[k].ro), (size_t)pool * 16));
+        RTB_CUDA(alloc(reinterpret_cast<void**>(&wv.q[k].rd), (size_t)pool * 16));
+        RTB_CUDA(alloc(reinterpret_cast<void**>(&wv.q[k].thr), (size_t)pool * 16));
+        RTB_CUDA(alloc(reinterpret_cast<void**>(&wv.q[k].meta), (size_t)pool * 8));
+      }
+      RTB_CUDA(alloc(reinterpret_cast<void**>(&wv.hit_t), (size_t)pool * 4));
+      RTB_CUDA(alloc(reinterpret_cast<void**>(&wv.hit_ref), (size_t)pool * 4));
+      RTB_CUDA(alloc(reinterpret_cast<void**>(&wv.counts), 16));
+      RTB_CUDA(cudaMallocHost(reinterpret_cast<void**>(&wv.host_count), 64));
+      RTB_CUDA(cudaStreamCreateWithFlags(&wv.stream, cudaStreamNonBlocking));
+      RTB_CUDA(cudaEventCreateWithFlags(&wv.done, cudaEventDisableTiming));
     }
-    RTB_CUDA(alloc(reinterpret_cast<void**>(&s->hit_t), (size_t)pool * 4));
-    RTB_CUDA(alloc(reinterpret_cast<void**>(&s->hit_ref), (size_t)pool * 4));
     s->pool = pool;
   }
   if (s->order_w != w || s->order_h != h) {
@@ -390,8 +431,9 @@ static int EnsurePool(RtbScene* s, uint32_t pool, int w, int h) {
         for (int y = ty; y < std::min(ty + 4, h); ++y)
           for (int x = tx; x < std::min(tx + 8, w); ++x) order.push_back((uint32_t)(y * w + x));
     void* p = nullptr;
+    if (s->pixel_order) cudaFree(s->pixel_order);
+    s->pixel_order = nullptr;
     RTB_CUDA(cudaMalloc(&p, order.size() * 4));
-    s->allocs.push_back(p);
     RTB_CUDA(cudaMemcpy(p, order.data(), order.size() * 4, cudaMemcpyHostToDevice));
     s->pixel_order = static_cast<uint32_t*>(p);
     s->order_w = w;
@@ -409,9 +451,20 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   const uint32_t n_pixels = (uint32_t)cam->width * (uint32_t)cam->height;
   uint32_t pool = prm->pool_size ? prm->pool_size : (1u << 21);
   pool = std::max(pool, 1u << 10);
-  rc = EnsurePool(s, pool, cam->width, cam->height);
+  // RTB_RENDER_SERIAL: one wave, every kernel timed alone with events (the roofline measurement);
+  // otherwise several waves in flight and only the whole render is timed.
+  const bool serial = (prm->flags & RTB_RENDER_SERIAL) != 0;
+  size_t n_waves = serial ? 1 : 4;
+  if (!serial)
+    if (const char* e = std::getenv("RTB_WAVES")) n_waves = (size_t)std::min(8, std::max(1, std::atoi(e)));
+  const unsigned long long total = (unsigned long long)n_pixels * (unsigned long long)(prm->spp_end - prm->spp_begin);
+  while (n_waves > 1 && total < (unsigned long long)pool * n_waves) --n_waves;  // small renders: fewer waves
+  RenderCtx* ctx = &g_ctx;
+  rc = EnsurePool(ctx, pool, n_waves, cam->width, cam->height);
   if (rc != RTB_OK) return rc;
   cudaStream_t st = g_stream;
+  std::vector<Wave*> waves;  // the first n_waves of the context (it may hold more from an earlier call)
+  for (size_t k = 0; k < n_waves; ++k) waves.push_back(&ctx->waves[k]);
   rtb::RenderConsts rcst{};
   rcst.cam = *cam;
   rcst.key = make_uint2((uint32_t)prm->seed, (uint32_t)(prm->seed >> 32));
@@ -419,63 +472,92 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   rcst.mode = prm->mode;
   rcst.spp_begin = prm->spp_begin;
   rcst.n_pixels = n_pixels;
-  const unsigned long long total = (unsigned long long)n_pixels * (unsigned long long)(prm->spp_end - prm->spp_begin);
   const bool use_smem = s->dev.n_top_pairs > 0 && !(prm->flags & RTB_RENDER_NO_SMEM_TOP) && !std::getenv("RTB_NO_SMEM_TOP");
   const int ext_grid = use_smem ? PersistentGrid(rtb::extend_kernel<true>, kTraceBlock, s->smem_bytes) : PersistentGrid(rtb::extend_kernel<false>, kTraceBlock, 0);
+  const bool trace_iters = std::getenv("RTB_TRACE_ITERS") != nullptr;
 
-  cudaEvent_t ev0, ev1;
+  cudaEvent_t ev0, ev1, ev_ready;
   RTB_CUDA(cudaEventCreate(&ev0));
   RTB_CUDA(cudaEventCreate(&ev1));
+  RTB_CUDA(cudaEventCreateWithFlags(&ev_ready, cudaEventDisableTiming));
   RTB_CUDA(cudaEventRecord(ev0, st));
   if (!(prm->flags & RTB_RENDER_KEEP_ACCUM)) RTB_CUDA(cudaMemsetAsync(d_rgb_sum, 0, (size_t)n_pixels * 3 * sizeof(float), st));
 #ifdef RTB_COUNTERS
   RTB_CUDA(cudaMemsetAsync(s->counters, 0, sizeof(rtb::HitCounters), st));
 #endif
+  RTB_CUDA(cudaEventRecord(ev_ready, st));
+  for (Wave* wp : waves) {
+    Wave& w = *wp;
+    RTB_CUDA(cudaStreamWaitEvent(w.stream, ev_ready, 0));
+    w.live = 0;
+    w.cur = 0;
+    w.pending = false;
+  }
   unsigned long long generated = 0, rays = 0;
-  uint32_t live = 0, iterations = 0, launches = 0;
-  int cur = 0;
+  uint32_t iterations = 0, launches = 0;
   float ms_gen = 0.f, ms_ext = 0.f, ms_shd = 0.f;
-  cudaEvent_t ek[4];  // per-kernel timing on the launching stream: before generate / extend / shade, after shade
-  for (auto& e : ek) RTB_CUDA(cudaEventCreate(&e));
+  cudaEvent_t ek[4] = {nullptr, nullptr, nullptr, nullptr};  // serial mode: before generate / extend / shade, after shade
+  if (serial)
+    for (auto& e : ek) RTB_CUDA(cudaEventCreate(&e));
   // max_depth == 0: GetPixel returns black without tracing (camera.h:149-151)
   const bool trace = prm->max_depth > 0 || prm->mode == RTB_MODE_B || cam->depth_camera;
-  while (trace) {
-    const uint32_t room = pool - live;
-    const uint32_t gen = (uint32_t)std::min<unsigned long long>(room, total - generated);
-    RTB_CUDA(cudaEventRecord(ek[0], st));
-    if (gen) {
-      rtb::generate_kernel<<<(gen + 255) / 256, 256, 0, st>>>(s->q[cur], live, gen, generated, rcst, s->pixel_order);
-      generated += gen;
-      live += gen;
-      ++launches;
+  bool any = trace;
+  while (any) {
+    any = false;
+    for (Wave* wp : waves) {
+    Wave& w = *wp;
+      if (w.pending) {  // collect the previous iteration of this wave: its survivor count
+        RTB_CUDA(cudaEventSynchronize(w.done));
+        w.pending = false;
+        if (serial) {
+          float a = 0.f, b = 0.f, c = 0.f;
+          cudaEventElapsedTime(&a, ek[0], ek[1]);
+          cudaEventElapsedTime(&b, ek[1], ek[2]);
+          cudaEventElapsedTime(&c, ek[2], ek[3]);
+          ms_gen += a;
+          ms_ext += b;
+          ms_shd += c;
+          if (trace_iters) std::fprintf(stderr, "[rtb iter %u] rays %u gen %.3f ext %.3f shade %.3f ms -> live %u\n", iterations, w.live, a, b, c, *w.host_count);
+        }
+        w.live = *w.host_count;
+        w.cur ^= 1;
+      }
+      const uint32_t room = pool - w.live;
+      const uint32_t gen = (uint32_t)std::min<unsigned long long>(room, total - generated);
+      if (gen == 0 && w.live == 0) continue;  // this wave is finished
+      cudaStream_t ws = w.stream;
+      if (serial) RTB_CUDA(cudaEventRecord(ek[0], ws));
+      if (gen) {
+        rtb::generate_kernel<<<(gen + 255) / 256, 256, 0, ws>>>(w.q[w.cur], w.live, gen, generated, rcst, ctx->pixel_order);
+        generated += gen;
+        w.live += gen;
+        ++launches;
+      }
+      RTB_CUDA(cudaMemsetAsync(w.counts, 0, 8, ws));
+      if (serial) RTB_CUDA(cudaEventRecord(ek[1], ws));
+      if (use_smem)
+        rtb::extend_kernel<true><<<ext_grid, kTraceBlock, s->smem_bytes, ws>>>(s->dev, w.q[w.cur], w.live, w.hit_t, w.hit_ref, w.counts, s->counters);
+      else
+        rtb::extend_kernel<false><<<ext_grid, kTraceBlock, 0, ws>>>(s->dev, w.q[w.cur], w.live, w.hit_t, w.hit_ref, w.counts, s->counters);
+      if (serial) RTB_CUDA(cudaEventRecord(ek[2], ws));
+      rtb::shade_kernel<<<(w.live + 255) / 256, 256, 0, ws>>>(s->dev, w.q[w.cur], w.live, w.hit_t, w.hit_ref, w.q[w.cur ^ 1], w.counts + 1, d_rgb_sum, rcst);
+      if (serial) RTB_CUDA(cudaEventRecord(ek[3], ws));
+      launches += 2;
+      rays += w.live;
+      ++iterations;
+      RTB_CUDA(cudaMemcpyAsync(w.host_count, w.counts + 1, 4, cudaMemcpyDeviceToHost, ws));
+      RTB_CUDA(cudaEventRecord(w.done, ws));
+      w.pending = true;
+      any = true;
     }
-    if (live == 0) break;
-    RTB_CUDA(cudaMemsetAsync(s->cursor, 0, 8, st));
-    RTB_CUDA(cudaEventRecord(ek[1], st));
-    if (use_smem)
-      rtb::extend_kernel<true><<<ext_grid, kTraceBlock, s->smem_bytes, st>>>(s->dev, s->q[cur], live, s->hit_t, s->hit_ref, s->cursor, s->counters);
-    else
-      rtb::extend_kernel<false><<<ext_grid, kTraceBlock, 0, st>>>(s->dev, s->q[cur], live, s->hit_t, s->hit_ref, s->cursor, s->counters);
-    RTB_CUDA(cudaEventRecord(ek[2], st));
-    rtb::shade_kernel<<<(live + 255) / 256, 256, 0, st>>>(s->dev, s->q[cur], live, s->hit_t, s->hit_ref, s->q[cur ^ 1], s->cursor + 1,
-                                                          d_rgb_sum, rcst);
-    RTB_CUDA(cudaEventRecord(ek[3], st));
-    launches += 2;
-    rays += live;
-    RTB_CUDA(cudaMemcpyAsync(s->host_count, s->cursor + 1, 4, cudaMemcpyDeviceToHost, st));
-    RTB_CUDA(cudaStreamSynchronize(st));
-    float a = 0.f, b = 0.f, c = 0.f;
-    cudaEventElapsedTime(&a, ek[0], ek[1]);
-    cudaEventElapsedTime(&b, ek[1], ek[2]);
-    cudaEventElapsedTime(&c, ek[2], ek[3]);
-    ms_gen += a;
-    ms_ext += b;
-    ms_shd += c;
-    live = *s->host_count;
-    cur ^= 1;
-    ++iterations;
   }
-  for (auto& e : ek) cudaEventDestroy(e);
+  for (auto& e : ek)
+    if (e) cudaEventDestroy(e);
+  for (Wave* wp : waves) {
+    Wave& w = *wp;  // the library stream joins every wave
+    RTB_CUDA(cudaEventRecord(w.done, w.stream));
+    RTB_CUDA(cudaStreamWaitEvent(st, w.done, 0));
+  }
   RTB_CUDA(cudaEventRecord(ev1, st));
   RTB_CUDA(cudaEventSynchronize(ev1));
   RTB_CUDA(cudaGetLastError());
@@ -483,6 +565,7 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   cudaEventElapsedTime(&ms, ev0, ev1);
   cudaEventDestroy(ev0);
   cudaEventDestroy(ev1);
+  cudaEventDestroy(ev_ready);
   if (stats) {
     std::memset(stats, 0, sizeof(*stats));
     stats->samples = generated;
@@ -500,6 +583,9 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
     stats->sphere_tests = hc.sphere_tests;
     stats->triangle_tests = hc.triangle_tests;
     stats->rect_tests = hc.rect_tests;
+    if (std::getenv("RTB_DEBUG_COUNTERS"))
+      std::fprintf(stderr, "[rtb counters] rays %llu pairs %llu exact_evals %llu filter_violations %llu max_steps %llu slow_rays %llu\n", hc.rays,
+                   hc.node_pairs, hc.exact_evals, hc.filter_violations, hc.max_steps, hc.slow_rays);
 #endif
   }
   return RTB_OK;

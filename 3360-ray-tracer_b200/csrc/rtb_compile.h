@@ -4,7 +4,7 @@
 // The closest hit the kernels return is a pure function of (exact primitive tests, tie rule)
 // (rtb_device.cuh), so the device tree only has to be CONSERVATIVE, not equal to the reference's
 // geom::Bvh (src/geom/bvh.h:166-367).  That freedom is used here:
-//   * sibling PAIRS are the unit: one 64-byte record {lo0,desc0 | hi0,- | lo1,desc1 | hi1,-} per
+//   * sibling PAIRS are the unit: one 64-byte record {lo0 hi0 lo1 hi1 | desc0 desc1 | pad} per
 //     internal node, i.e. one 128-bit x4 fetch and both slab tests per traversal step;
 //   * a child descriptor says everything needed to continue (no second fetch): internal -> pair
 //     index; leaf -> primitive type, count and first index into that type's leaf-ordered table.
@@ -58,11 +58,11 @@ inline float Up(double v) {
   return f;
 }
 
-struct Pair {  // 64 bytes, the device record
-  float lo0[3]; uint32_t d0;
-  float hi0[3]; uint32_t pad0;
-  float lo1[3]; uint32_t d1;
-  float hi1[3]; uint32_t pad1;
+struct Pair {  // 64 bytes, the device record: three 128-bit loads of boxes + one 64-bit load of descriptors
+  float lo0[3], hi0[3];
+  float lo1[3], hi1[3];
+  uint32_t d0, d1;
+  uint32_t pad[2];
 };
 static_assert(sizeof(Pair) == 64, "pair record is one 64-byte fetch");
 
@@ -221,7 +221,7 @@ class Compiler {
       hi[k] = b.hi[k];
     }
     (side ? p.d1 : p.d0) = desc;
-    (side ? p.pad1 : p.pad0) = 0;
+    p.pad[0] = p.pad[1] = 0;
   }
 
   void Layout(int root, Compiled& out) {

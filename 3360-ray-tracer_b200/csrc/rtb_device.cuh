@@ -102,11 +102,15 @@ __device__ __forceinline__ void prepare_ray(TravRay& r, float4 o, float4 d) {
   // computed t = fma(p, inv, -o*inv): |error| <= ~2^-23 (|o*inv| + |t|)
   const float ox = o.x * r.ix, oy = o.y * r.iy, oz = o.z * r.iz;
   r.bx = -ox; r.by = -oy; r.bz = -oz;
-  r.eabs = 8.0f * kU * fmaxf(fabsf(ox), fmaxf(fabsf(oy), fabsf(oz)));
+  // absolute slack of the comparison tn <= tf: twice the |o*inv| rounding term, plus the relative
+  // term of a negative tmin (tn, tf >= 0 otherwise, where the (1 + 2^-18) factor in slab() covers it)
+  r.eabs = 16.0f * kU * fmaxf(fabsf(ox), fmaxf(fabsf(oy), fabsf(oz))) + (o.w < 0.0f ? -1.6e-5f * o.w : 0.0f);
   r.dmax = fmaxf(fabsf(d.x), fmaxf(fabsf(d.y), fabsf(d.z)));
 }
 
 // Conservative slab test of one box against [tmin, thi].  Returns the entry distance in tn.
+// Computed plane distances carry <= 2^-22 relative + eabs/2 absolute error; the test widens the
+// far side by 2^-18 relative + eabs, so a box the exact test enters is never culled.
 __device__ __forceinline__ bool slab(const TravRay& r, float4 lo, float4 hi, float thi, float& tn) {
   const float ax = fmaf(lo.x, r.ix, r.bx), bx = fmaf(hi.x, r.ix, r.bx);
   const float ay = fmaf(lo.y, r.iy, r.by), by = fmaf(hi.y, r.iy, r.by);
@@ -114,8 +118,7 @@ __device__ __forceinline__ bool slab(const TravRay& r, float4 lo, float4 hi, flo
   // fminf/fmaxf drop a NaN operand, which is the conservative side
   tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), r.tmin));
   const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), thi));
-  // tf*(1+2^-19) + 2 eabs >= tn*(1-..) - ..: relative slack ~32 ulp, absolute slack from prepare_ray
-  return tn <= fmaf(fabsf(tf), 1.9073486e-6f, tf) + (r.eabs + r.eabs + fabsf(tn) * 1.9073486e-6f);
+  return tn <= fmaf(tf, 1.0000038f, r.eabs);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -33,17 +33,28 @@ __device__ __forceinline__ void stage_top(const DevScene& s, float4* smem_pairs)
 // ---- the traversal loop shared by intersect_batch (seam 2) and extend (seam 1) ------------------
 // Persistent warps; every LANE owns one ray at a time and takes a new one from the global cursor
 // as soon as enough lanes of its warp have run dry (no lane waits for the warp's longest ray).
-// Per iteration the warp votes: the larger group — lanes standing at an internal pair, or lanes
-// standing at a leaf — takes one step, so at least half of the occupied lanes do useful work in
-// every issued instruction, whatever the mix of ray lengths.
+// The body is a while-while traversal with a vote: lanes standing at an internal pair keep
+// descending while they are the majority of the warp's live lanes; then every lane standing at a
+// leaf works through its whole leaf.  One ballot per node step is the only warp-level overhead.
 //
-// Io: { uint32_t n; load(i, float4& o, float4& d); store(i, ref, t, exact) }.
+// Io: { uint32_t n; load(i, float4& o, float4& d); store(i, ref, tf, td, exact) }.
 #ifndef RTB_TRACE_MIN_BLOCKS
 #define RTB_TRACE_MIN_BLOCKS 3  // 256-thread CTAs per SM the traversal kernels are compiled for (register cap 85)
 #endif
 constexpr unsigned kFull = 0xffffffffu;
 constexpr int kRefillLanes = 8;    // refill when at least this many lanes are idle
-constexpr unsigned kChunk = 64;    // rays claimed per atomicAdd on the cursor
+constexpr unsigned kChunk = 32;    // rays claimed per atomicAdd on the cursor
+
+__device__ __forceinline__ float4 ld_pair_generic(unsigned long long addr) {  // shared or global
+  float4 v;
+  asm("ld.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(addr));
+  return v;
+}
+__device__ __forceinline__ float4 ld_pair_global(unsigned long long addr) {
+  float4 v;
+  asm("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(addr));
+  return v;
+}
 
 template <bool kUseSmem, class Io>
 __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem_pairs, Io io, unsigned int* cursor, HitCounters* cnt) {
@@ -60,8 +71,11 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
 #ifdef RTB_COUNTERS
   unsigned n_pairs = 0, n_sph = 0, n_tri = 0, n_rect = 0, n_rays = 0, steps = 0;
 #endif
-  // generic pointers: one load instruction serves the shared-memory prefix and the global rest
-  const float4* const top = kUseSmem ? smem_pairs : s.pairs;
+  // Base addresses held in registers: the shared-memory prefix through its generic address, so one
+  // load instruction serves both (no branch); volatile keeps ptxas from re-deriving it per step.
+  unsigned long long base_top = 0, base_all;
+  asm volatile("mov.u64 %0, %1;" : "=l"(base_all) : "l"(s.pairs));
+  if (kUseSmem) asm volatile("mov.u64 %0, %1;" : "=l"(base_top) : "l"(smem_pairs));
   const uint32_t n_top = kUseSmem ? s.n_top_pairs : 0u;
 
   for (;;) {
@@ -106,19 +120,30 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
         idle = __ballot_sync(kFull, !active);
       }
     }
-    const unsigned act = __ballot_sync(kFull, active);
-    if (!act) {
+    const int n_act = __popc(~idle);
+    if (n_act == 0) {
       if (exhausted && pool_next == pool_end) break;
       continue;
     }
-    const bool at_leaf = active && (cur & kLeafBit);
-    const unsigned leaf_mask = __ballot_sync(kFull, at_leaf);
-    bool pop = false;
-    if (__popc(act & ~leaf_mask) >= __popc(leaf_mask)) {
-      // ---- node step: fetch one sibling pair, slab-test both, descend into the nearer hit
-      if (active && !at_leaf) {
-        const float4* p = ((kUseSmem && cur < n_top) ? top : s.pairs) + 4 * (size_t)cur;
-        const float4 llo = p[0], lhi = p[1], rlo = p[2], rhi = p[3];
+    // ---- node phase: descend while the descending lanes are the majority
+    for (;;) {
+      const bool at_node = active && !(cur & kLeafBit);
+      const unsigned nm = __ballot_sync(kFull, at_node);
+      if (nm == 0u || 2 * __popc(nm) < n_act) break;
+      if (at_node) {
+        const unsigned long long addr = ((kUseSmem && cur < n_top) ? base_top : base_all) + (unsigned long long)cur * 64ull;
+        // record = {lo0.xyz hi0.xyz lo1.xyz hi1.xyz desc0 desc1 - -}
+        float4 q0, q1, q2;
+        uint2 dd;
+        if (kUseSmem) {
+          q0 = ld_pair_generic(addr); q1 = ld_pair_generic(addr + 16); q2 = ld_pair_generic(addr + 32);
+          asm("ld.v2.u32 {%0,%1}, [%2];" : "=r"(dd.x), "=r"(dd.y) : "l"(addr + 48));
+        } else {
+          q0 = ld_pair_global(addr); q1 = ld_pair_global(addr + 16); q2 = ld_pair_global(addr + 32);
+          asm("ld.global.nc.v2.u32 {%0,%1}, [%2];" : "=r"(dd.x), "=r"(dd.y) : "l"(addr + 48));
+        }
+        const float4 llo = make_float4(q0.x, q0.y, q0.z, 0.f), lhi = make_float4(q0.w, q1.x, q1.y, 0.f);
+        const float4 rlo = make_float4(q1.z, q1.w, q2.x, 0.f), rhi = make_float4(q2.y, q2.z, q2.w, 0.f);
 #ifdef RTB_COUNTERS
         ++n_pairs;
         ++steps;
@@ -126,43 +151,50 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
         float tl, tr;
         const bool hl = slab(r, llo, lhi, b.hi, tl);
         const bool hr = slab(r, rlo, rhi, b.hi, tr);
-        const uint32_t dl = __float_as_uint(llo.w), dr = __float_as_uint(rlo.w);
+        const uint32_t dl = dd.x, dr = dd.y;
         if (hl && hr) {
           const bool left_first = tl <= tr;
           stack[sp++] = left_first ? dr : dl;
           cur = left_first ? dl : dr;
         } else if (hl || hr) {
           cur = hl ? dl : dr;
+        } else if (sp > 0) {
+          cur = stack[--sp];
         } else {
-          pop = true;
+          io.store(slot, b.ref, b.exact ? (float)b.td : b.tf, b.exact ? b.td : (double)b.tf, b.exact);
+          active = false;
+#ifdef RTB_COUNTERS
+          if (cnt) {
+            atomicMax(&cnt->max_steps, (unsigned long long)steps);
+            if (steps > 2000u && atomicAdd(&cnt->slow_rays, 1ull) == 0ull) {
+              cnt->slow_ray[0] = r.ox; cnt->slow_ray[1] = r.oy; cnt->slow_ray[2] = r.oz; cnt->slow_ray[3] = r.tmin;
+              cnt->slow_ray[4] = r.dx; cnt->slow_ray[5] = r.dy; cnt->slow_ray[6] = r.dz; cnt->slow_ray[7] = r.tmax;
+            }
+          }
+#endif
         }
       }
-    } else {
-      // ---- leaf step: one primitive of the current leaf
-      if (at_leaf) {
-        const uint32_t type = desc_type(cur), idx = desc_first(cur);
+    }
+    // ---- leaf phase: every lane standing at a leaf works through all of its primitives
+    if (active && (cur & kLeafBit)) {
+      const uint32_t type = desc_type(cur);
+      uint32_t idx = desc_first(cur);
+      const uint32_t last = idx + ((cur >> 24) & 31u);
+      for (;;) {
 #ifdef RTB_COUNTERS
         if (type == RTB_PRIM_TRIANGLE) ++n_tri; else if (type == RTB_PRIM_SPHERE) ++n_sph; else ++n_rect;
 #endif
         consider(s, r, type, idx, b, cnt);
-        if (desc_more(cur)) cur += 1u - (1u << 24);  // first+1, count-1
-        else pop = true;
+        if (idx == last) break;
+        ++idx;
       }
-    }
-    if (pop) {
       if (sp > 0) {
         cur = stack[--sp];
       } else {
         io.store(slot, b.ref, b.exact ? (float)b.td : b.tf, b.exact ? b.td : (double)b.tf, b.exact);
         active = false;
 #ifdef RTB_COUNTERS
-        if (cnt) {
-          atomicMax(&cnt->max_steps, (unsigned long long)steps);
-          if (steps > 2000u && atomicAdd(&cnt->slow_rays, 1ull) == 0ull) {
-            cnt->slow_ray[0] = r.ox; cnt->slow_ray[1] = r.oy; cnt->slow_ray[2] = r.oz; cnt->slow_ray[3] = r.tmin;
-            cnt->slow_ray[4] = r.dx; cnt->slow_ray[5] = r.dy; cnt->slow_ray[6] = r.dz; cnt->slow_ray[7] = r.tmax;
-          }
-        }
+        if (cnt) atomicMax(&cnt->max_steps, (unsigned long long)steps);
 #endif
       }
     }

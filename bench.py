@@ -206,9 +206,9 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step():
+    def step(flags=0):
         """one render of the configuration at this rank + reduce + resolve; returns (device ms, stats)"""
-        st = ds.render_device(cam, accum.data_ptr(), rank * spp, (rank + 1) * spp, depth, mode=mode, pool_size=args.pool)
+        st = ds.render_device(cam, accum.data_ptr(), rank * spp, (rank + 1) * spp, depth, mode=mode, pool_size=args.pool, flags=flags)
         ev[0].record()
         if world > 1:
             dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
@@ -236,6 +236,13 @@ def main():
         stats.append(st)
     barrier()
     clk = clocks.stop() if rank == 0 else None
+    # per-kernel times: the same step with ONE wavefront in flight and an event pair around every launch
+    # (RTB_RENDER_SERIAL); in the timed steps above several wavefronts overlap, so kernels cannot be timed singly
+    serial_stats = []
+    for _ in range(min(K, 3)):
+        flush.fill_(1)
+        barrier()
+        serial_stats.append(step(rt.RENDER_SERIAL)[1])
     # max over ranks of the K-step time
     tot = torch.tensor([sum(dev_ms), sum(wall_ms)], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -286,17 +293,18 @@ def main():
                        "image": [cam.width, cam.height], "spp_per_gpu": spp, "spp_total": spp * world, "max_depth": depth,
                        "estimator": args.mode, "parallelism": f"spp-split x{world}, scene replicated, 1 NCCL reduce(sum,f32) of {n_pix * 12} B",
                        "l2": "384 MiB buffer written between timed steps (L2 flushed); scene itself is L2-resident by design",
-                       "pool_paths": args.pool or (1 << 21), "scene_build_s_untimed": round(t_build, 3)},
+                       "pool_paths": args.pool or (1 << 21), "wavefronts_in_flight": int(os.environ.get("RTB_WAVES", "4")), "scene_build_s_untimed": round(t_build, 3)},
             "e2e": {"value": samples_per_step / (e2e_tot.item() / K * 1e-3) / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_tot.item() / K,
                     "what": "rtb_scene_create (all scene arrays H2D) + rtb_render with a host rgb buffer (D2H) + rtb_scene_destroy, wall clock"},
             "gpu_launches": int(sum(s["launches"] for s in stats) + K),
             "clocks": clk,
-            "kernel_ms_per_step": {k: float(np.mean([s[k] for s in stats])) for k in ("ms_generate", "ms_extend", "ms_shade")},
+            "kernel_ms_per_step": {**{k: float(np.mean([s[k] for s in serial_stats])) for k in ("ms_generate", "ms_extend", "ms_shade", "ms_total")},
+                                   "how": "same step re-run with one wavefront in flight (RTB_RENDER_SERIAL), CUDA events around every launch"},
             "iterations_per_step": stats[-1]["iterations"],
         }
         if not args.no_roofline and world == 1:
-            line["roofline"] = roofline(rt, hs, cam, cfg, stats, mode, args.pool)
+            line["roofline"] = roofline(rt, hs, cam, cfg, serial_stats, mode, args.pool)
         elif not args.no_roofline:
             line["roofline"] = {"note": "measured at N=1 only (one process, one GPU)"}
         if not args.no_cpu_baseline and world == 1:

@@ -186,11 +186,12 @@ typedef struct RtbRenderParams {
   int32_t max_depth;
   int32_t mode;       /* RTB_MODE_A / RTB_MODE_B */
   uint64_t seed;      /* Philox key */
-  uint32_t pool_size; /* live paths in flight, 0 = default */
+  uint32_t pool_size; /* live paths in flight per wavefront, 0 = default */
   uint32_t flags;     /* RTB_RENDER_* */
 } RtbRenderParams;
 #define RTB_RENDER_NO_SMEM_TOP 1u  /* do not stage the top BVH levels in shared memory */
 #define RTB_RENDER_KEEP_ACCUM 2u   /* add into the accumulator instead of zeroing it first */
+#define RTB_RENDER_SERIAL 4u       /* one wavefront, each kernel timed alone (fills RtbStats.ms_generate/extend/shade) */
 
 typedef struct RtbStats {
   uint64_t samples;     /* camera samples started                      */
@@ -202,7 +203,7 @@ typedef struct RtbStats {
   uint32_t iterations;  /* wavefront iterations (one bounce each)      */
   uint32_t launches;    /* kernels launched                            */
   float ms_total;       /* CUDA-event time, first launch -> accumulator final */
-  float ms_generate;
+  float ms_generate;    /* per-kernel sums: only with RTB_RENDER_SERIAL (0 otherwise: wavefronts overlap) */
   float ms_extend;
   float ms_shade;
 } RtbStats;
