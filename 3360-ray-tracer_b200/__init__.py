@@ -6,3 +6,4 @@ bench.py.  The directory name is not a valid Python identifier: load it with
 """
 from .binding import *  # noqa: F401,F403
 from . import binding  # noqa: F401
+from . import multigpu  # noqa: F401,E402

@@ -208,7 +208,8 @@ def main():
 
     def step(flags=0):
         """one render of the configuration at this rank + reduce + resolve; returns (device ms, stats)"""
-        st = ds.render_device(cam, accum.data_ptr(), rank * spp, (rank + 1) * spp, depth, mode=mode, pool_size=args.pool, flags=flags)
+        b_, e_ = rt.multigpu.weak_slice(spp, rank)
+        st = ds.render_device(cam, accum.data_ptr(), b_, e_, depth, mode=mode, pool_size=args.pool, flags=flags)
         ev[0].record()
         if world > 1:
             dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
