@@ -19,7 +19,7 @@ ASSET_DIR = REPO_ROOT / "assets"
 RTB_OK, RTB_EINVAL, RTB_ENODEVICE, RTB_ECUDA, RTB_ENOMEM = 0, -1, -2, -3, -4
 PRIM_SPHERE, PRIM_TRIANGLE, PRIM_RECT, PRIM_SUBTREE = 0, 1, 2, 3
 MODE_A, MODE_B = 0, 1
-RENDER_NO_SMEM_TOP, RENDER_KEEP_ACCUM, RENDER_SERIAL = 1, 2, 4
+RENDER_SMEM_TOP, RENDER_KEEP_ACCUM, RENDER_SERIAL, RENDER_WAVEFRONT, RENDER_NO_DRAIN = 1, 2, 4, 8, 16
 EX_SPHERE, EX_TRIANGLE, EX_RECT, EX_BVH_BEGIN, EX_BVH_END, EX_LIST_BEGIN, EX_LIST_END = 0, 1, 2, 10, 11, 12, 13
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_DIFFUSE_LIGHT = 0, 1, 2, 3
 TEX_SOLID, TEX_CHECKER, TEX_IMAGE = 0, 1, 2
@@ -72,6 +72,7 @@ class RtbStats(C.Structure):
         ("samples", C.c_uint64), ("rays", C.c_uint64), ("node_visits", C.c_uint64), ("sphere_tests", C.c_uint64),
         ("triangle_tests", C.c_uint64), ("rect_tests", C.c_uint64), ("iterations", C.c_uint32), ("launches", C.c_uint32),
         ("ms_total", C.c_float), ("ms_generate", C.c_float), ("ms_extend", C.c_float), ("ms_shade", C.c_float),
+        ("ms_drain", C.c_float), ("drain_paths", C.c_uint32),
     ]
 
     def as_dict(self):
@@ -110,6 +111,9 @@ RTH_SYMBOLS = [
 
 
 def lib_path(counters: bool = False) -> Path:
+    # RTB_LIB=<file name in this directory>: a tuning variant built by `make VARIANT=...` (tools/gpu_variants.py)
+    if not counters and os.environ.get("RTB_LIB"):
+        return PKG_DIR / os.environ["RTB_LIB"]
     return PKG_DIR / ("librtb200_counters.so" if counters else "librtb200.so")
 
 

@@ -55,7 +55,7 @@ struct Wave {
   rtb::PathQueue q[2]{};
   float* hit_t = nullptr;
   uint32_t* hit_ref = nullptr;
-  unsigned int* counts = nullptr;      // device: [0] extend cursor, [1] shade survivor count
+  unsigned int* counts = nullptr;      // device: [0] traversal cursor, [1] shade survivor count, [2..3] 64-bit ray counter of the path kernel
   unsigned int* host_count = nullptr;  // pinned
   cudaStream_t stream = nullptr;
   cudaEvent_t done = nullptr;
@@ -66,6 +66,7 @@ struct Wave {
 };
 struct RenderCtx {
   std::vector<Wave> waves;
+  Wave fused;  // default mode: no queues, only the counters, their pinned mirror and a stream
   uint32_t pool = 0;
   uint32_t* pixel_order = nullptr;
   int order_w = 0, order_h = 0;
@@ -83,8 +84,19 @@ void FreeWaves(RenderCtx* s) {
   s->waves.clear();
   s->pool = 0;
 }
+void FreeFused(RenderCtx* s) {
+  Wave& w = s->fused;
+  if (w.stream) cudaStreamSynchronize(w.stream);
+  for (void* p : w.mem) cudaFree(p);
+  if (w.done) cudaEventDestroy(w.done);
+  if (w.stream) cudaStreamDestroy(w.stream);
+  w = Wave{};
+}
 
 }  // namespace
+
+// shared memory of the traversal kernels besides the staged top of the tree: the stack columns
+constexpr size_t kStackSmem = (size_t)rtb::kSmemStack * rtb::kTraceBlock * sizeof(uint32_t);
 
 struct RtbScene {
   rtb::DevScene dev{};
@@ -140,6 +152,7 @@ int rtb_shutdown(void) {
   if (g_stream) {
     cudaStreamSynchronize(g_stream);
     FreeWaves(&g_ctx);
+    FreeFused(&g_ctx);
     if (g_ctx.pixel_order) cudaFree(g_ctx.pixel_order);
     g_ctx.pixel_order = nullptr;
     g_ctx.order_w = g_ctx.order_h = 0;
@@ -216,10 +229,18 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
   {  // interchange tree -> device-native sibling pairs (rtb_compile.h)
     rtbc::Compiled tree;
     try {
-      tree = rtbc::Compiler(*d).Run();
+      RtbSceneDesc dd = *d;
+#ifdef RTB_TOP_PAIRS  // tuning builds: size of the shared-memory prefix, overriding the flattener's
+      dd.n_top_nodes = 2u * (uint32_t)(RTB_TOP_PAIRS);
+#endif
+      tree = rtbc::Compiler(dd).Run();
     } catch (const std::exception& e) {
       rtb_scene_destroy(s);
       return Fail(RTB_EINVAL, std::string("scene compile: ") + e.what());
+    }
+    if (tree.pairs.size() >= (1u << 29)) {
+      rtb_scene_destroy(s);
+      return Fail(RTB_EINVAL, "more than 2^29 BVH pairs");
     }
     if (tree.depth + 2 > (uint32_t)rtb::kStackSize) {
       rtb_scene_destroy(s);
@@ -307,8 +328,8 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
     PUT(s->Put(objs.data(), objs.size(), &v.image_tex));
     PUT(s->Put(dims.data(), dims.size(), &v.image_dim));
   }
-  s->smem_bytes = (size_t)v.n_top_pairs * 64;
-  if (s->smem_bytes > 200 * 1024) {
+  s->smem_bytes = (size_t)v.n_top_pairs * 64;  // + the stack columns, added at launch (TraceSmem)
+  if (s->smem_bytes + kStackSmem > 200 * 1024) {
     rtb_scene_destroy(s);
     return Fail(RTB_EINVAL, "n_top_nodes does not fit shared memory");
   }
@@ -326,9 +347,20 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
     s->cursor = reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(p) + sizeof(rtb::HitCounters));
   }
   // opt in to large dynamic shared memory for the two traversal kernels
-  if (s->smem_bytes > 48 * 1024) {
-    cudaFuncSetAttribute(rtb::intersect_batch_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_bytes);
-    cudaFuncSetAttribute(rtb::extend_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_bytes);
+  {
+    const int with_top = (int)(s->smem_bytes + kStackSmem), without = (int)kStackSmem;
+    if (with_top > 48 * 1024) {
+      cudaFuncSetAttribute(rtb::intersect_batch_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, with_top);
+      cudaFuncSetAttribute(rtb::extend_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, with_top);
+      cudaFuncSetAttribute(rtb::path_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, with_top);
+      cudaFuncSetAttribute(rtb::path_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, with_top);
+    }
+    if (without > 48 * 1024) {
+      cudaFuncSetAttribute(rtb::intersect_batch_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, without);
+      cudaFuncSetAttribute(rtb::extend_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, without);
+      cudaFuncSetAttribute(rtb::path_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, without);
+      cudaFuncSetAttribute(rtb::path_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, without);
+    }
   }
 #undef PUT
   *out = s;
@@ -339,7 +371,7 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
 
 // Traversal CTAs are large so that one shared-memory copy of the top of the tree serves many warps
 // and most of the 228 KB stays L1 for the rest of the tree.
-constexpr int kTraceBlock = 256;
+using rtb::kTraceBlock;
 
 // Persistent grid: as many CTAs as are co-resident on the whole chip.
 template <class K>
@@ -360,14 +392,15 @@ int rtb_intersect_batch_device(RtbScene* s, const RtbRay* d_rays, size_t n, RtbH
   if (rc != RTB_OK) return rc;
   cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : g_stream;
   RTB_CUDA(cudaMemsetAsync(s->cursor, 0, 8, st));
-  const bool use_smem = s->dev.n_top_pairs > 0 && !std::getenv("RTB_NO_SMEM_TOP");
+  const bool use_smem = s->dev.n_top_pairs > 0 && std::getenv("RTB_SMEM_TOP") != nullptr;
   const float4* rays4 = reinterpret_cast<const float4*>(d_rays);
   if (use_smem) {
-    const int grid = PersistentGrid(rtb::intersect_batch_kernel<true>, kTraceBlock, s->smem_bytes);
-    rtb::intersect_batch_kernel<true><<<grid, kTraceBlock, s->smem_bytes, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->cursor, s->counters);
+    const size_t smem = s->smem_bytes + kStackSmem;
+    const int grid = PersistentGrid(rtb::intersect_batch_kernel<true>, kTraceBlock, smem);
+    rtb::intersect_batch_kernel<true><<<grid, kTraceBlock, smem, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->cursor, s->counters);
   } else {
-    const int grid = PersistentGrid(rtb::intersect_batch_kernel<false>, kTraceBlock, 0);
-    rtb::intersect_batch_kernel<false><<<grid, kTraceBlock, 0, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->cursor, s->counters);
+    const int grid = PersistentGrid(rtb::intersect_batch_kernel<false>, kTraceBlock, kStackSmem);
+    rtb::intersect_batch_kernel<false><<<grid, kTraceBlock, kStackSmem, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->cursor, s->counters);
   }
   // second pass: the reference's exact t for filter-settled hits, and the global primitive ids
   rtb::exact_t_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->counters);
@@ -397,7 +430,7 @@ int rtb_intersect_batch(RtbScene* s, const RtbRay* rays, size_t n, RtbHit* hits)
   return RTB_OK;
 }
 
-static int EnsurePool(RenderCtx* s, uint32_t pool, size_t n_waves, int w, int h) {
+static int EnsurePool(RenderCtx* s, uint32_t pool, size_t n_waves) {
   if (s->pool != pool || s->waves.size() < n_waves) {
     FreeWaves(s);
     s->waves.resize(n_waves);
@@ -415,13 +448,29 @@ static int EnsurePool(RenderCtx* s, uint32_t pool, size_t n_waves, int w, int h)
       }
       RTB_CUDA(alloc(reinterpret_cast<void**>(&wv.hit_t), (size_t)pool * 4));
       RTB_CUDA(alloc(reinterpret_cast<void**>(&wv.hit_ref), (size_t)pool * 4));
-      RTB_CUDA(alloc(reinterpret_cast<void**>(&wv.counts), 16));
+      RTB_CUDA(alloc(reinterpret_cast<void**>(&wv.counts), 16));  // see Wave::counts
       RTB_CUDA(cudaMallocHost(reinterpret_cast<void**>(&wv.host_count), 64));
       RTB_CUDA(cudaStreamCreateWithFlags(&wv.stream, cudaStreamNonBlocking));
       RTB_CUDA(cudaEventCreateWithFlags(&wv.done, cudaEventDisableTiming));
     }
     s->pool = pool;
   }
+  return RTB_OK;
+}
+
+static int EnsureFused(RenderCtx* s) {
+  Wave& wv = s->fused;
+  if (wv.stream) return RTB_OK;
+  void* p = nullptr;
+  RTB_CUDA(cudaMalloc(&p, 16));
+  wv.mem.push_back(p);
+  wv.counts = static_cast<unsigned int*>(p);
+  RTB_CUDA(cudaStreamCreateWithFlags(&wv.stream, cudaStreamNonBlocking));
+  RTB_CUDA(cudaEventCreateWithFlags(&wv.done, cudaEventDisableTiming));
+  return RTB_OK;
+}
+
+static int EnsureOrder(RenderCtx* s, int w, int h) {
   if (s->order_w != w || s->order_h != h) {
     // 8x4-tiled pixel permutation: consecutive samples of a warp are neighbouring pixels
     std::vector<uint32_t> order;
@@ -460,11 +509,15 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   const unsigned long long total = (unsigned long long)n_pixels * (unsigned long long)(prm->spp_end - prm->spp_begin);
   while (n_waves > 1 && total < (unsigned long long)pool * n_waves) --n_waves;  // small renders: fewer waves
   RenderCtx* ctx = &g_ctx;
-  rc = EnsurePool(ctx, pool, n_waves, cam->width, cam->height);
+  const bool fused = !(prm->flags & (RTB_RENDER_WAVEFRONT | RTB_RENDER_SERIAL));
+  rc = fused ? EnsureFused(ctx) : EnsurePool(ctx, pool, n_waves);
+  if (rc == RTB_OK) rc = EnsureOrder(ctx, cam->width, cam->height);
   if (rc != RTB_OK) return rc;
   cudaStream_t st = g_stream;
   std::vector<Wave*> waves;  // the first n_waves of the context (it may hold more from an earlier call)
-  for (size_t k = 0; k < n_waves; ++k) waves.push_back(&ctx->waves[k]);
+  if (fused) waves.push_back(&ctx->fused);
+  else
+    for (size_t k = 0; k < n_waves; ++k) waves.push_back(&ctx->waves[k]);
   rtb::RenderConsts rcst{};
   rcst.cam = *cam;
   rcst.key = make_uint2((uint32_t)prm->seed, (uint32_t)(prm->seed >> 32));
@@ -472,9 +525,15 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   rcst.mode = prm->mode;
   rcst.spp_begin = prm->spp_begin;
   rcst.n_pixels = n_pixels;
-  const bool use_smem = s->dev.n_top_pairs > 0 && !(prm->flags & RTB_RENDER_NO_SMEM_TOP) && !std::getenv("RTB_NO_SMEM_TOP");
-  const int ext_grid = use_smem ? PersistentGrid(rtb::extend_kernel<true>, kTraceBlock, s->smem_bytes) : PersistentGrid(rtb::extend_kernel<false>, kTraceBlock, 0);
+  const bool use_smem = s->dev.n_top_pairs > 0 && ((prm->flags & RTB_RENDER_SMEM_TOP) || std::getenv("RTB_SMEM_TOP") != nullptr);
+  const size_t ext_smem = (use_smem ? s->smem_bytes : 0) + kStackSmem;
+  const int ext_grid = use_smem ? PersistentGrid(rtb::extend_kernel<true>, kTraceBlock, ext_smem) : PersistentGrid(rtb::extend_kernel<false>, kTraceBlock, ext_smem);
   const bool trace_iters = std::getenv("RTB_TRACE_ITERS") != nullptr;
+  // path kernel (rtb_kernels.cuh): the whole render (default) or, in wavefront mode, the drain of a wavefront's last paths
+  uint32_t drain_max = (prm->flags & RTB_RENDER_NO_DRAIN) ? 0u : pool / 8;
+  if (const char* e = std::getenv("RTB_DRAIN_MAX")) drain_max = (uint32_t)std::max(0, std::atoi(e));
+  const int path_grid = use_smem ? PersistentGrid(fused ? rtb::path_kernel<true, false> : rtb::path_kernel<true, true>, kTraceBlock, ext_smem)
+                                 : PersistentGrid(fused ? rtb::path_kernel<false, false> : rtb::path_kernel<false, true>, kTraceBlock, ext_smem);
 
   cudaEvent_t ev0, ev1, ev_ready;
   RTB_CUDA(cudaEventCreate(&ev0));
@@ -492,16 +551,35 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
     w.live = 0;
     w.cur = 0;
     w.pending = false;
+    RTB_CUDA(cudaMemsetAsync(w.counts, 0, 16, w.stream));
   }
   unsigned long long generated = 0, rays = 0;
-  uint32_t iterations = 0, launches = 0;
-  float ms_gen = 0.f, ms_ext = 0.f, ms_shd = 0.f;
+  uint32_t iterations = 0, launches = 0, drain_paths = 0;
+  float ms_gen = 0.f, ms_ext = 0.f, ms_shd = 0.f, ms_drain = 0.f;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> drain_events;  // serial mode: around each drain launch
   cudaEvent_t ek[4] = {nullptr, nullptr, nullptr, nullptr};  // serial mode: before generate / extend / shade, after shade
   if (serial)
     for (auto& e : ek) RTB_CUDA(cudaEventCreate(&e));
   // max_depth == 0: GetPixel returns black without tracing (camera.h:149-151)
   const bool trace = prm->max_depth > 0 || prm->mode == RTB_MODE_B || cam->depth_camera;
-  bool any = trace;
+  bool any = trace && !fused;
+  if (trace && fused) {
+    Wave& w = *waves[0];
+    while (generated < total) {
+      const uint32_t chunk = (uint32_t)std::min<unsigned long long>(total - generated, 1ull << 30);
+      RTB_CUDA(cudaMemsetAsync(w.counts, 0, 4, w.stream));
+      auto* rc64 = reinterpret_cast<unsigned long long*>(w.counts + 2);
+      if (use_smem)
+        rtb::path_kernel<true, false><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, generated, rcst, ctx->pixel_order,
+                                                                                  d_rgb_sum, w.counts, rc64, s->counters);
+      else
+        rtb::path_kernel<false, false><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, generated, rcst, ctx->pixel_order,
+                                                                                   d_rgb_sum, w.counts, rc64, s->counters);
+      generated += chunk;
+      ++launches;
+      ++iterations;
+    }
+  }
   while (any) {
     any = false;
     for (Wave* wp : waves) {
@@ -521,6 +599,31 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
         }
         w.live = *w.host_count;
         w.cur ^= 1;
+        if (generated == total && w.live > 0 && w.live <= drain_max) {
+          // nothing left to generate and few paths alive: finish them in ONE launch of the path kernel instead of
+          // one latency-bound extend + shade pair per remaining bounce
+          cudaStream_t ws = w.stream;
+          cudaEvent_t d0 = nullptr, d1 = nullptr;
+          if (serial) {
+            RTB_CUDA(cudaEventCreate(&d0));
+            RTB_CUDA(cudaEventCreate(&d1));
+            drain_events.emplace_back(d0, d1);
+          }
+          RTB_CUDA(cudaMemsetAsync(w.counts, 0, 4, ws));
+          if (serial) RTB_CUDA(cudaEventRecord(d0, ws));
+          auto* rc64 = reinterpret_cast<unsigned long long*>(w.counts + 2);
+          if (use_smem)
+            rtb::path_kernel<true, true><<<path_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, 0ull, rcst, ctx->pixel_order, d_rgb_sum,
+                                                                               w.counts, rc64, s->counters);
+          else
+            rtb::path_kernel<false, true><<<path_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, 0ull, rcst, ctx->pixel_order, d_rgb_sum,
+                                                                                w.counts, rc64, s->counters);
+          if (serial) RTB_CUDA(cudaEventRecord(d1, ws));
+          if (trace_iters) std::fprintf(stderr, "[rtb drain] %u paths\n", w.live);
+          drain_paths += w.live;
+          w.live = 0;
+          ++launches;
+        }
       }
       const uint32_t room = pool - w.live;
       const uint32_t gen = (uint32_t)std::min<unsigned long long>(room, total - generated);
@@ -536,9 +639,9 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
       RTB_CUDA(cudaMemsetAsync(w.counts, 0, 8, ws));
       if (serial) RTB_CUDA(cudaEventRecord(ek[1], ws));
       if (use_smem)
-        rtb::extend_kernel<true><<<ext_grid, kTraceBlock, s->smem_bytes, ws>>>(s->dev, w.q[w.cur], w.live, w.hit_t, w.hit_ref, w.counts, s->counters);
+        rtb::extend_kernel<true><<<ext_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, w.hit_t, w.hit_ref, w.counts, s->counters);
       else
-        rtb::extend_kernel<false><<<ext_grid, kTraceBlock, 0, ws>>>(s->dev, w.q[w.cur], w.live, w.hit_t, w.hit_ref, w.counts, s->counters);
+        rtb::extend_kernel<false><<<ext_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, w.hit_t, w.hit_ref, w.counts, s->counters);
       if (serial) RTB_CUDA(cudaEventRecord(ek[2], ws));
       rtb::shade_kernel<<<(w.live + 255) / 256, 256, 0, ws>>>(s->dev, w.q[w.cur], w.live, w.hit_t, w.hit_ref, w.q[w.cur ^ 1], w.counts + 1, d_rgb_sum, rcst);
       if (serial) RTB_CUDA(cudaEventRecord(ek[3], ws));
@@ -561,6 +664,18 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   RTB_CUDA(cudaEventRecord(ev1, st));
   RTB_CUDA(cudaEventSynchronize(ev1));
   RTB_CUDA(cudaGetLastError());
+  for (Wave* wp : waves) {  // rays traced inside the path kernel (it bounces on the device)
+    unsigned long long c = 0;
+    RTB_CUDA(cudaMemcpy(&c, wp->counts + 2, 8, cudaMemcpyDeviceToHost));
+    rays += c;
+  }
+  for (auto& de : drain_events) {
+    float d = 0.f;
+    cudaEventElapsedTime(&d, de.first, de.second);
+    ms_drain += d;
+    cudaEventDestroy(de.first);
+    cudaEventDestroy(de.second);
+  }
   float ms = 0.f;
   cudaEventElapsedTime(&ms, ev0, ev1);
   cudaEventDestroy(ev0);
@@ -576,6 +691,8 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
     stats->ms_generate = ms_gen;
     stats->ms_extend = ms_ext;
     stats->ms_shade = ms_shd;
+    stats->ms_drain = ms_drain;
+    stats->drain_paths = drain_paths;
 #ifdef RTB_COUNTERS
     rtb::HitCounters hc{};
     cudaMemcpy(&hc, s->counters, sizeof(hc), cudaMemcpyDeviceToHost);
@@ -586,6 +703,12 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
     if (std::getenv("RTB_DEBUG_COUNTERS"))
       std::fprintf(stderr, "[rtb counters] rays %llu pairs %llu exact_evals %llu filter_violations %llu max_steps %llu slow_rays %llu\n", hc.rays,
                    hc.node_pairs, hc.exact_evals, hc.filter_violations, hc.max_steps, hc.slow_rays);
+    if (std::getenv("RTB_DEBUG_COUNTERS")) {
+      std::fprintf(stderr, "[rtb counters] rays by log2(steps+1):");
+      for (int k = 0; k < 16; ++k) std::fprintf(stderr, " %llu", hc.step_hist[k]);
+      std::fprintf(stderr, "\n[rtb counters] a slow ray: o %.9g %.9g %.9g d %.9g %.9g %.9g\n", hc.slow_ray[0], hc.slow_ray[1], hc.slow_ray[2],
+                   hc.slow_ray[4], hc.slow_ray[5], hc.slow_ray[6]);
+    }
 #endif
   }
   return RTB_OK;

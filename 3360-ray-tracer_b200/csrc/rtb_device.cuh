@@ -57,8 +57,9 @@ __device__ __forceinline__ uint32_t desc_more(uint32_t d) { return d & 0x1f00000
 
 struct HitCounters {  // only touched when RTB_COUNTERS is defined
   unsigned long long node_pairs, sphere_tests, triangle_tests, rect_tests, rays, exact_evals, filter_violations;
-  unsigned long long max_steps, slow_rays;  // longest traversal (steps of one ray), rays above 2000 steps
+  unsigned long long max_steps, slow_rays;  // longest traversal (steps of one ray), rays above 256 steps
   float slow_ray[8];                        // one of them (o, tmin, d, tmax)
+  unsigned long long step_hist[16];         // rays by floor(log2(steps + 1))
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -85,8 +86,9 @@ struct TravRay {
   // FP32 slab constants: t_plane = fma(plane, inv, b) with b = -o*inv; eabs bounds the absolute
   // error of that form (|o*inv| * few ulp), the relative part is applied in slab_pair()
   float ix, iy, iz, bx, by, bz, eabs;
-  float dmax;  // max |d_i|, used by the filters' error bounds
 };
+// max |d_i|: the filters' error bounds scale with it (one FMNMX3, cheaper than a live register)
+__device__ __forceinline__ float ray_dmax(const TravRay& r) { return fmaxf(fabsf(r.dx), fmaxf(fabsf(r.dy), fabsf(r.dz))); }
 
 __device__ __forceinline__ float safe_dir(float d) {
   // Box test only: |d| below 1e-20 behaves like an axis-parallel ray; keeps 1/d and o/d finite.
@@ -105,7 +107,6 @@ __device__ __forceinline__ void prepare_ray(TravRay& r, float4 o, float4 d) {
   // absolute slack of the comparison tn <= tf: twice the |o*inv| rounding term, plus the relative
   // term of a negative tmin (tn, tf >= 0 otherwise, where the (1 + 2^-18) factor in slab() covers it)
   r.eabs = 16.0f * kU * fmaxf(fabsf(ox), fmaxf(fabsf(oy), fabsf(oz))) + (o.w < 0.0f ? -1.6e-5f * o.w : 0.0f);
-  r.dmax = fmaxf(fabsf(d.x), fmaxf(fabsf(d.y), fabsf(d.z)));
 }
 
 // Conservative slab test of one box against [tmin, thi].  Returns the entry distance in tn.
@@ -233,7 +234,8 @@ __device__ __forceinline__ int triangle_filter(const DevScene& s, uint32_t idx, 
   const float px = r.dy * E2.z - r.dz * E2.y, py = r.dz * E2.x - r.dx * E2.z, pz = r.dx * E2.y - r.dy * E2.x;
   const float det = E1.x * px + E1.y * py + E1.z * pz;
   const float w = E1.w * E2.w;
-  const float edet = (64.0f * kU) * w * r.dmax;
+  const float dmax = ray_dmax(r);
+  const float edet = (64.0f * kU) * w * dmax;
   const float adet = fabsf(det);
   if (adet + edet < 0.999999e-6f) return kMiss;  // triangle.h:55 rejects |det| < 1e-6
   if (!(adet > 8.0f * edet) || !(adet - edet > 1.000001e-6f)) return kUnsure;
@@ -243,11 +245,11 @@ __device__ __forceinline__ int triangle_filter(const DevScene& s, uint32_t idx, 
   const float g = 1.25f * fabsf(inv);
   const float rho = g * edet + 8.0f * kU;
   const float u = (tx * px + ty * py + tz * pz) * inv;
-  const float eu = g * (sA * r.dmax * E2.w) + fabsf(u) * rho;
+  const float eu = g * (sA * dmax * E2.w) + fabsf(u) * rho;
   if (u < -eu || u > 1.0f + eu) return kMiss;
   const float qx = ty * E1.z - tz * E1.y, qy = tz * E1.x - tx * E1.z, qz = tx * E1.y - ty * E1.x;
   const float v = (r.dx * qx + r.dy * qy + r.dz * qz) * inv;
-  const float ev = g * (sA * r.dmax * E1.w) + fabsf(v) * rho;
+  const float ev = g * (sA * dmax * E1.w) + fabsf(v) * rho;
   const float euv = eu + ev + 4.0f * kU;
   if (v < -ev || u + v > 1.0f + euv) return kMiss;
   const float t = (E2.x * qx + E2.y * qy + E2.z * qz) * inv;
@@ -350,15 +352,50 @@ __device__ __forceinline__ bool replaces(const DevScene& s, double t, uint32_t r
 }
 
 // ---------------------------------------------------------------------------------------------
-// Current best hit of a lane.  exact == true: td is the reference's t.  Otherwise the reference's
-// t lies in [tf - ef, tf + ef] (a filter HIT that no other candidate has contested yet).
+// Current best hit of a lane: the reference's t of primitive `ref` lies in [tf - ef, tf + ef]
+// (ef == 0: tf IS the reference's t, which happens for every exactly-replayed triangle because
+// Triangle::Hit rounds t to float, triangle.h:71).  hi >= tf + ef is the culling bound of the slab
+// tests.  With nothing hit yet ref == kNoHit and tf = hi = the ray's tmax.  The exact double is
+// deliberately NOT carried: the rare contested case replays both contenders.
 struct Best {
   uint32_t ref;
   float tf, ef;
-  float hi;  // float upper bound of the best t: the culling bound of the slab tests
-  double td;
-  bool exact;
+  float hi;
 };
+
+__device__ __forceinline__ void best_set_exact(Best& b, uint32_t ref, double t) {
+  b.ref = ref;
+  b.tf = (float)t;
+  b.ef = (double)b.tf == t ? 0.0f : fabsf(b.tf) * 1.2e-7f;  // one ulp covers the rounding of a double t
+  b.hi = __double2float_ru(t);
+}
+
+// Rare path of consider(): candidate (type, idx) cannot be ordered against the best by the FP32
+// filters alone.  Replays the reference's own arithmetic for both and applies its tie rule.
+__device__ __forceinline__ void consider_exact(const DevScene& s, float ox, float oy, float oz, float dx, float dy, float dz, float tmin,
+                                            float tmax, uint32_t type, uint32_t idx, Best& b, HitCounters* cnt) {
+#ifdef RTB_COUNTERS
+  if (cnt) atomicAdd(&cnt->exact_evals, 1ull);
+#else
+  (void)cnt;
+#endif
+  double tb = (double)tmax;
+  if (b.ref != kNoHit) {
+    const uint32_t bty = RTB_REF_TYPE(b.ref);
+    tb = exact_eval(exact_table(s, bty), bty, RTB_REF_INDEX(b.ref), ox, oy, oz, dx, dy, dz, tmin, tmax);
+    if (!(tb == tb)) {  // a filter HIT the reference rejects would be a bug in the bounds; keep the interval midpoint
+      tb = (double)b.tf;
+#ifdef RTB_COUNTERS
+      if (cnt) atomicAdd(&cnt->filter_violations, 1ull);
+#endif
+    }
+    best_set_exact(b, b.ref, tb);
+  }
+  const double tc = exact_eval(exact_table(s, type), type, idx, ox, oy, oz, dx, dy, dz, tmin, tmax);
+  if (!(tc == tc)) return;
+  const uint32_t ref = RTB_REF(type, idx);
+  if (replaces(s, tc, ref, tb, b.ref)) best_set_exact(b, ref, tc);
+}
 
 // Fold one primitive into the lane's best hit.
 __device__ __forceinline__ void consider(const DevScene& s, const TravRay& r, uint32_t type, uint32_t idx, Best& b, HitCounters* cnt) {
@@ -368,44 +405,15 @@ __device__ __forceinline__ void consider(const DevScene& s, const TravRay& r, ui
   else if (type == RTB_PRIM_SPHERE) cls = sphere_filter(s, idx, r, b.hi, t, e);
   else cls = rect_filter(s, idx, r, b.hi, t, e);
   if (cls == kMiss) return;
-  const uint32_t ref = RTB_REF(type, idx);
   if (cls == kHit) {
-    const float blo = b.exact ? __double2float_rd(b.td) : b.tf - b.ef;
     if (t - e > b.hi) return;                                  // certainly farther than the best
-    if (b.ref == kNoHit || t + e < blo) {                      // certainly nearer: take it, still inexact
-      b.ref = ref; b.tf = t; b.ef = e; b.exact = false;
+    if (b.ref == kNoHit || t + e < b.tf - b.ef) {              // certainly nearer: take it, still inexact
+      b.ref = RTB_REF(type, idx); b.tf = t; b.ef = e;
       b.hi = t + e;
       return;
     }
   }
-  // ---- rare path: decide by exact replays
-#ifdef RTB_COUNTERS
-  if (cnt) atomicAdd(&cnt->exact_evals, 1ull);
-#else
-  (void)cnt;
-#endif
-  if (b.ref != kNoHit && !b.exact) {
-    const uint32_t bty = RTB_REF_TYPE(b.ref);
-    const double tb = exact_eval(exact_table(s, bty), bty, RTB_REF_INDEX(b.ref), r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, r.tmin, r.tmax);
-    if (tb == tb) {
-      b.td = tb;
-    } else {  // a filter HIT the reference rejects would be a bug in the bounds; keep the interval midpoint
-      b.td = (double)b.tf;
-#ifdef RTB_COUNTERS
-      if (cnt) atomicAdd(&cnt->filter_violations, 1ull);
-#endif
-    }
-    b.exact = true;
-    b.hi = __double2float_ru(b.td);
-  }
-  const double tc = exact_eval(exact_table(s, type), type, idx, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, r.tmin, r.tmax);
-  if (!(tc == tc)) return;
-  const double bt = b.ref == kNoHit ? (double)r.tmax : b.td;
-  if (replaces(s, tc, ref, bt, b.ref)) {
-    b.ref = ref; b.td = tc; b.exact = true;
-    b.tf = (float)tc; b.ef = 0.f;
-    b.hi = __double2float_ru(tc);
-  }
+  consider_exact(s, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, r.tmin, r.tmax, type, idx, b, cnt);
 }
 
 }  // namespace rtb

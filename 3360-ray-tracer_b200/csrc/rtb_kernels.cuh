@@ -33,17 +33,37 @@ __device__ __forceinline__ void stage_top(const DevScene& s, float4* smem_pairs)
 // ---- the traversal loop shared by intersect_batch (seam 2) and extend (seam 1) ------------------
 // Persistent warps; every LANE owns one ray at a time and takes a new one from the global cursor
 // as soon as enough lanes of its warp have run dry (no lane waits for the warp's longest ray).
-// The body is a while-while traversal with a vote: lanes standing at an internal pair keep
-// descending while they are the majority of the warp's live lanes; then every lane standing at a
-// leaf works through its whole leaf.  One ballot per node step is the only warp-level overhead.
 //
-// Io: { uint32_t n; load(i, float4& o, float4& d); store(i, ref, tf, td, exact) }.
+// The body is a while-while traversal with a vote: lanes standing at an internal pair keep
+// descending while they are the majority of the warp's live lanes; then the lanes standing at
+// leaves work through them, one primitive type after the other.  A leaf descriptor counts itself
+// down (first + 1, count - 1), so the leaf loop carries no registers besides `cur`.
+// (A flat "census" loop that ran whichever state had the most lanes was measured and rejected:
+// it lifted the triangle filter from 5 to 13 active lanes but dropped the node step from 21 to 14
+// and paid ~20 warp-wide instructions per iteration for the vote: DESIGN.md section 3.1.)
+//
+// Io: { uint32_t n; unsigned rays; load(i, float4& o, float4& d);
+//       bool finish(i, ref, tf, const TravRay&, float4& o, float4& d)  -> true: the lane continues with ray (o, d) }.
 #ifndef RTB_TRACE_MIN_BLOCKS
-#define RTB_TRACE_MIN_BLOCKS 3  // 256-thread CTAs per SM the traversal kernels are compiled for (register cap 85)
+#define RTB_TRACE_MIN_BLOCKS 3  // 256-thread CTAs per SM the traversal kernels are compiled for
+#endif
+#ifndef RTB_REFILL_LANES  // service phase threshold of extend / intersect_batch (store + refill)
+#define RTB_REFILL_LANES 8
+#endif
+#ifndef RTB_PATH_REFILL_LANES  // ... of the path kernel, whose service phase also shades: worth waiting for more lanes
+#define RTB_PATH_REFILL_LANES 16
+#endif
+#ifndef RTB_SMEM_STACK  // traversal-stack entries per thread kept in shared memory (the rest: local memory)
+#define RTB_SMEM_STACK 0
 #endif
 constexpr unsigned kFull = 0xffffffffu;
-constexpr int kRefillLanes = 8;    // refill when at least this many lanes are idle
-constexpr unsigned kChunk = 32;    // rays claimed per atomicAdd on the cursor
+constexpr unsigned kChunk = 32;                 // rays claimed per atomicAdd on the cursor
+constexpr int kSmemStack = RTB_SMEM_STACK;
+#ifndef RTB_TRACE_BLOCK
+#define RTB_TRACE_BLOCK 256
+#endif
+constexpr int kTraceBlock = RTB_TRACE_BLOCK;  // threads per traversal CTA
+constexpr uint32_t kDoneMark = 0xffffffffu;      // `cur` of a lane whose traversal is finished (leaf bit + the unused type 3)
 
 __device__ __forceinline__ float4 ld_pair_generic(unsigned long long addr) {  // shared or global
   float4 v;
@@ -56,14 +76,31 @@ __device__ __forceinline__ float4 ld_pair_global(unsigned long long addr) {
   return v;
 }
 
+// Per-thread traversal stack: the first kSmemStack entries in shared memory, laid out [entry][thread]
+// so that any mix of stack depths across a warp is bank-conflict free; deeper entries in local memory.
+struct TravStack {
+  uint32_t* sm;  // this thread's column
+  uint32_t deep[kStackSize - kSmemStack];
+  __device__ __forceinline__ void push(int sp, uint32_t v) {
+    if (kSmemStack > 0 && sp < kSmemStack) sm[sp * kTraceBlock] = v;
+    else deep[sp - kSmemStack] = v;
+  }
+  __device__ __forceinline__ uint32_t at(int sp) const {
+    if (kSmemStack > 0 && sp < kSmemStack) return sm[sp * kTraceBlock];
+    return deep[sp - kSmemStack];
+  }
+};
+
 template <bool kUseSmem, class Io>
-__device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem_pairs, Io io, unsigned int* cursor, HitCounters* cnt) {
+__device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem_pairs, uint32_t* smem_stack, Io& io, unsigned int* cursor,
+                                           HitCounters* cnt) {
   const unsigned lane = threadIdx.x & 31u;
   const unsigned lt_mask = (1u << lane) - 1u;
-  uint32_t stack[kStackSize];
+  TravStack stack;
+  stack.sm = smem_stack + threadIdx.x;
   int sp = 0;
   TravRay r;
-  Best b;
+  Best b{kNoHit, 0.f, 0.f, 0.f};
   uint32_t cur = 0, slot = 0;
   bool active = false;
   unsigned pool_next = 0, pool_end = 0;  // warp-uniform: claimed, not yet assigned ray indices
@@ -71,18 +108,92 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
 #ifdef RTB_COUNTERS
   unsigned n_pairs = 0, n_sph = 0, n_tri = 0, n_rect = 0, n_rays = 0, steps = 0;
 #endif
-  // Base addresses held in registers: the shared-memory prefix through its generic address, so one
-  // load instruction serves both (no branch); volatile keeps ptxas from re-deriving it per step.
-  unsigned long long base_top = 0, base_all;
-  asm volatile("mov.u64 %0, %1;" : "=l"(base_all) : "l"(s.pairs));
-  if (kUseSmem) asm volatile("mov.u64 %0, %1;" : "=l"(base_top) : "l"(smem_pairs));
+  const unsigned long long base_all = (unsigned long long)s.pairs;
+  const unsigned long long base_top = kUseSmem ? (unsigned long long)smem_pairs : 0ull;  // generic address of the staged prefix
   const uint32_t n_top = kUseSmem ? s.n_top_pairs : 0u;
 
+  // a lane's ray is finished: it waits (state DONE) for the next service phase, where Io::finish
+  // stores or shades it together with the other waiting lanes
+  auto finish = [&]() {
+    cur = kDoneMark;
+#ifdef RTB_COUNTERS
+    if (cnt) {
+      atomicMax(&cnt->max_steps, (unsigned long long)steps);
+      atomicAdd(&cnt->step_hist[min(15, 31 - __clz((int)steps + 1))], 1ull);
+      if (steps > 256u && atomicAdd(&cnt->slow_rays, 1ull) == 0ull) {
+        cnt->slow_ray[0] = r.ox; cnt->slow_ray[1] = r.oy; cnt->slow_ray[2] = r.oz; cnt->slow_ray[3] = r.tmin;
+        cnt->slow_ray[4] = r.dx; cnt->slow_ray[5] = r.dy; cnt->slow_ray[6] = r.dz; cnt->slow_ray[7] = r.tmax;
+      }
+    }
+#endif
+  };
+  auto pop_or_finish = [&]() {
+    if (sp > 0) cur = stack.at(--sp);
+    else finish();
+  };
+
+  // one node step of this lane (both children of pair `cur`, near one first, far one pushed)
+  auto node_step = [&]() {
+    const unsigned long long addr = ((kUseSmem && cur < n_top) ? base_top : base_all) + (unsigned long long)cur * 64ull;
+    // record = {lo0.xyz hi0.xyz lo1.xyz hi1.xyz desc0 desc1 - -}
+    float4 q0, q1, q2;
+    uint2 dd;
+    if (kUseSmem) {
+      q0 = ld_pair_generic(addr); q1 = ld_pair_generic(addr + 16); q2 = ld_pair_generic(addr + 32);
+      asm("ld.v2.u32 {%0,%1}, [%2];" : "=r"(dd.x), "=r"(dd.y) : "l"(addr + 48));
+    } else {
+      q0 = ld_pair_global(addr); q1 = ld_pair_global(addr + 16); q2 = ld_pair_global(addr + 32);
+      asm("ld.global.nc.v2.u32 {%0,%1}, [%2];" : "=r"(dd.x), "=r"(dd.y) : "l"(addr + 48));
+    }
+    const float4 llo = make_float4(q0.x, q0.y, q0.z, 0.f), lhi = make_float4(q0.w, q1.x, q1.y, 0.f);
+    const float4 rlo = make_float4(q1.z, q1.w, q2.x, 0.f), rhi = make_float4(q2.y, q2.z, q2.w, 0.f);
+#ifdef RTB_COUNTERS
+    ++n_pairs;
+    ++steps;
+#endif
+    float tl, tr;
+    const bool hl = slab(r, llo, lhi, b.hi, tl);
+    const bool hr = slab(r, rlo, rhi, b.hi, tr);
+    const uint32_t dl = dd.x, dr = dd.y;
+    if (hl && hr) {
+      const bool left_first = tl <= tr;
+      stack.push(sp++, left_first ? dr : dl);
+      cur = left_first ? dl : dr;
+    } else if (hl || hr) {
+      cur = hl ? dl : dr;
+    } else {
+      pop_or_finish();
+    }
+  };
+  // one primitive of the leaf this lane stands at; the descriptor itself is the loop counter
+  auto leaf_step = [&](uint32_t type) {
+#ifdef RTB_COUNTERS
+    if (type == RTB_PRIM_TRIANGLE) ++n_tri; else if (type == RTB_PRIM_SPHERE) ++n_sph; else ++n_rect;
+#endif
+    consider(s, r, type, desc_first(cur), b, cnt);
+    if (desc_more(cur)) cur += 1u - (1u << 24);  // first + 1, count - 1
+    else pop_or_finish();
+  };
+
   for (;;) {
-    // ---- refill idle lanes
-    unsigned idle = __ballot_sync(kFull, !active);
-    if (idle && !(exhausted && pool_next == pool_end) && (__popc(idle) >= kRefillLanes || idle == kFull)) {
-      for (int round = 0; round < 2 && idle; ++round) {
+    // ---- service phase: finished lanes hand their hit to the Io (store it, or shade it and maybe
+    // continue with the bounced ray), idle lanes take new work from the global cursor.  Runs when
+    // enough lanes are waiting for it to be worth a warp-wide pass, or when nobody is tracing.
+    const bool done = active && cur == kDoneMark;
+    const unsigned wait_mask = __ballot_sync(kFull, !active || done);
+    const unsigned done_mask = __ballot_sync(kFull, done);
+    const int n_trace = 32 - __popc(wait_mask);
+    const bool more = !(exhausted && pool_next == pool_end);
+    if ((done_mask != 0u || (more && wait_mask != 0u)) && (__popc(wait_mask) >= Io::kServiceLanes || n_trace == 0)) {
+      float4 o, d;
+      bool have = false;
+      if (done) {
+        have = io.finish(slot, b.ref, b.tf, r, o, d);
+        active = have;
+        cur = 0;
+      }
+      unsigned need = __ballot_sync(kFull, !active);
+      for (int round = 0; round < 2 && need; ++round) {
         if (pool_next == pool_end) {
           if (exhausted) break;
           unsigned base = 0;
@@ -96,106 +207,46 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
           pool_end = min(base + kChunk, io.n);
           exhausted = pool_end == io.n;
         }
-        const unsigned mine = pool_next + __popc(idle & lt_mask);
-        const bool take = !active && mine < pool_end;
-        if (take) {
-          float4 o, d;
+        const unsigned mine = pool_next + __popc(need & lt_mask);
+        if (!active && mine < pool_end) {
           io.load(mine, o, d);
-          prepare_ray(r, o, d);
           slot = mine;
-          b.ref = kNoHit; b.tf = d.w; b.ef = 0.f; b.hi = d.w; b.td = (double)d.w; b.exact = true;
-          cur = 0;  // pair 0 = the root's two children
-          sp = 0;
+          have = true;
           active = true;
-          if (s.n_pairs == 0) {  // empty scene: Bvh::Hit returns false (bvh.h:72-73)
-            io.store(slot, kNoHit, d.w, (double)d.w, true);
-            active = false;
-          }
-#ifdef RTB_COUNTERS
-          ++n_rays;
-          steps = 0;
-#endif
         }
-        pool_next = min(pool_next + (unsigned)__popc(idle), pool_end);
-        idle = __ballot_sync(kFull, !active);
+        pool_next = min(pool_next + (unsigned)__popc(need), pool_end);
+        need = __ballot_sync(kFull, !active);
       }
-    }
-    const int n_act = __popc(~idle);
-    if (n_act == 0) {
-      if (exhausted && pool_next == pool_end) break;
+      if (have) {
+        prepare_ray(r, o, d);
+        b.ref = kNoHit; b.tf = d.w; b.ef = 0.f; b.hi = d.w;
+        cur = 0;  // pair 0 = the root's two children
+        sp = 0;
+        ++io.rays;
+#ifdef RTB_COUNTERS
+        ++n_rays;
+        steps = 0;
+#endif
+        if (s.n_pairs == 0) finish();  // empty scene: Bvh::Hit returns false (bvh.h:72-73)
+      }
       continue;
     }
+    if (n_trace == 0) break;  // nobody tracing, nothing to hand over, nothing left to claim
+    const int n_act = n_trace;
     // ---- node phase: descend while the descending lanes are the majority
     for (;;) {
       const bool at_node = active && !(cur & kLeafBit);
       const unsigned nm = __ballot_sync(kFull, at_node);
       if (nm == 0u || 2 * __popc(nm) < n_act) break;
-      if (at_node) {
-        const unsigned long long addr = ((kUseSmem && cur < n_top) ? base_top : base_all) + (unsigned long long)cur * 64ull;
-        // record = {lo0.xyz hi0.xyz lo1.xyz hi1.xyz desc0 desc1 - -}
-        float4 q0, q1, q2;
-        uint2 dd;
-        if (kUseSmem) {
-          q0 = ld_pair_generic(addr); q1 = ld_pair_generic(addr + 16); q2 = ld_pair_generic(addr + 32);
-          asm("ld.v2.u32 {%0,%1}, [%2];" : "=r"(dd.x), "=r"(dd.y) : "l"(addr + 48));
-        } else {
-          q0 = ld_pair_global(addr); q1 = ld_pair_global(addr + 16); q2 = ld_pair_global(addr + 32);
-          asm("ld.global.nc.v2.u32 {%0,%1}, [%2];" : "=r"(dd.x), "=r"(dd.y) : "l"(addr + 48));
-        }
-        const float4 llo = make_float4(q0.x, q0.y, q0.z, 0.f), lhi = make_float4(q0.w, q1.x, q1.y, 0.f);
-        const float4 rlo = make_float4(q1.z, q1.w, q2.x, 0.f), rhi = make_float4(q2.y, q2.z, q2.w, 0.f);
-#ifdef RTB_COUNTERS
-        ++n_pairs;
-        ++steps;
-#endif
-        float tl, tr;
-        const bool hl = slab(r, llo, lhi, b.hi, tl);
-        const bool hr = slab(r, rlo, rhi, b.hi, tr);
-        const uint32_t dl = dd.x, dr = dd.y;
-        if (hl && hr) {
-          const bool left_first = tl <= tr;
-          stack[sp++] = left_first ? dr : dl;
-          cur = left_first ? dl : dr;
-        } else if (hl || hr) {
-          cur = hl ? dl : dr;
-        } else if (sp > 0) {
-          cur = stack[--sp];
-        } else {
-          io.store(slot, b.ref, b.exact ? (float)b.td : b.tf, b.exact ? b.td : (double)b.tf, b.exact);
-          active = false;
-#ifdef RTB_COUNTERS
-          if (cnt) {
-            atomicMax(&cnt->max_steps, (unsigned long long)steps);
-            if (steps > 2000u && atomicAdd(&cnt->slow_rays, 1ull) == 0ull) {
-              cnt->slow_ray[0] = r.ox; cnt->slow_ray[1] = r.oy; cnt->slow_ray[2] = r.oz; cnt->slow_ray[3] = r.tmin;
-              cnt->slow_ray[4] = r.dx; cnt->slow_ray[5] = r.dy; cnt->slow_ray[6] = r.dz; cnt->slow_ray[7] = r.tmax;
-            }
-          }
-#endif
-        }
-      }
+      if (at_node) node_step();
     }
-    // ---- leaf phase: every lane standing at a leaf works through all of its primitives
-    if (active && (cur & kLeafBit)) {
-      const uint32_t type = desc_type(cur);
-      uint32_t idx = desc_first(cur);
-      const uint32_t last = idx + ((cur >> 24) & 31u);
-      for (;;) {
-#ifdef RTB_COUNTERS
-        if (type == RTB_PRIM_TRIANGLE) ++n_tri; else if (type == RTB_PRIM_SPHERE) ++n_sph; else ++n_rect;
-#endif
-        consider(s, r, type, idx, b, cnt);
-        if (idx == last) break;
-        ++idx;
-      }
-      if (sp > 0) {
-        cur = stack[--sp];
-      } else {
-        io.store(slot, b.ref, b.exact ? (float)b.td : b.tf, b.exact ? b.td : (double)b.tf, b.exact);
-        active = false;
-#ifdef RTB_COUNTERS
-        if (cnt) atomicMax(&cnt->max_steps, (unsigned long long)steps);
-#endif
+    // ---- leaf phase, one primitive type at a time (the types are different code, SIMT would serialise
+    // them anyway); each lane works through its whole leaf, the descriptor counting down
+#pragma unroll 1
+    for (uint32_t type = 0; type < 3; ++type) {
+      const uint32_t want = 4u + type;  // leaf bit + type in the top three bits
+      while (__any_sync(kFull, active && (cur >> 29) == want)) {
+        if (active && (cur >> 29) == want) leaf_step(type);
       }
     }
   }
@@ -212,64 +263,73 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
 
 // ---- seam 2: RayIntegrator::IntersectBatch (src/integrator/cpu_ray_integrator.h:18-46) --------
 struct BatchIo {
+  static constexpr int kServiceLanes = RTB_REFILL_LANES;
   uint32_t n;
-  const float4* rays;
+  unsigned rays;
+  const float4* in;
   RtbHit* hits;
   const DevScene* s;
   __device__ __forceinline__ void load(uint32_t i, float4& o, float4& d) const {
-    o = __ldg(&rays[2 * (size_t)i]);
-    d = __ldg(&rays[2 * (size_t)i + 1]);
+    o = __ldg(&in[2 * (size_t)i]);
+    d = __ldg(&in[2 * (size_t)i + 1]);
   }
-  // inexact hits carry the filter's t and ref with bit 31 of prim_id's slot marked for the
-  // exact_t pass below (prim_id is filled there)
-  __device__ __forceinline__ void store(uint32_t i, uint32_t ref, float, double td, bool exact) const {
+  // the traversal settles WHICH primitive is hit; the reference's exact t and the global primitive
+  // id are filled in by exact_t_kernel below
+  __device__ __forceinline__ bool finish(uint32_t i, uint32_t ref, float tf, const TravRay&, float4&, float4&) const {
     RtbHit h;
     h.ref = ref;
-    h.t = ref == kNoHit ? 0.0 : td;
-    h.prim_id = ref == kNoHit ? -1 : (exact ? 0 : 1);
+    h.t = ref == kNoHit ? 0.0 : (double)tf;
+    h.prim_id = -1;
     hits[i] = h;
+    return false;
   }
 };
 
+// dynamic shared memory of the traversal kernels: [staged top pairs][per-thread stack columns]
+__device__ __forceinline__ uint32_t* smem_stack_base(const DevScene& s, float4* smem, bool use_top) {
+  return reinterpret_cast<uint32_t*>(smem + (use_top ? 4 * (size_t)s.n_top_pairs : 0));
+}
+
 template <bool kUseSmem>
-__global__ void __launch_bounds__(256, RTB_TRACE_MIN_BLOCKS) intersect_batch_kernel(DevScene s, const float4* __restrict__ rays, uint32_t n,
+__global__ void __launch_bounds__(kTraceBlock, RTB_TRACE_MIN_BLOCKS) intersect_batch_kernel(DevScene s, const float4* __restrict__ rays, uint32_t n,
                                                               RtbHit* __restrict__ hits, unsigned int* cursor, HitCounters* cnt) {
   extern __shared__ float4 smem_pairs[];
   if (kUseSmem) stage_top(s, smem_pairs);
-  trace_loop<kUseSmem>(s, smem_pairs, BatchIo{n, rays, hits, &s}, cursor, cnt);
+  BatchIo io{n, 0u, rays, hits, &s};
+  trace_loop<kUseSmem>(s, smem_pairs, smem_stack_base(s, smem_pairs, kUseSmem), io, cursor, cnt);
 }
 
-// Second pass of seam 2: HitRecord::t exactly as the reference computes it, for the hits the
-// traversal settled with the FP32 filter alone, and the global primitive id.  Fully convergent.
+// Second pass of seam 2: HitRecord::t exactly as the reference computes it (one replay of the
+// reference arithmetic for the winning primitive) and the global primitive id.  Fully convergent.
 __global__ void exact_t_kernel(DevScene s, const float4* __restrict__ rays, uint32_t n, RtbHit* __restrict__ hits, HitCounters* cnt) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   RtbHit h = hits[i];
   if (h.ref == kNoHit) return;
   const uint32_t ty = RTB_REF_TYPE(h.ref), idx = RTB_REF_INDEX(h.ref);
-  if (h.prim_id == 1) {
-    const float4 o = __ldg(&rays[2 * (size_t)i]), d = __ldg(&rays[2 * (size_t)i + 1]);
-    const double t = exact_eval(exact_table(s, ty), ty, idx, o.x, o.y, o.z, d.x, d.y, d.z, o.w, d.w);
-    const bool ok = t == t;
-    if (ok) h.t = t;
+  const float4 o = __ldg(&rays[2 * (size_t)i]), d = __ldg(&rays[2 * (size_t)i + 1]);
+  const double t = exact_eval(exact_table(s, ty), ty, idx, o.x, o.y, o.z, d.x, d.y, d.z, o.w, d.w);
+  const bool ok = t == t;
+  if (ok) h.t = t;
 #ifdef RTB_COUNTERS
-    if (!ok && cnt) atomicAdd(&cnt->filter_violations, 1ull);
+  if (!ok && cnt) atomicAdd(&cnt->filter_violations, 1ull);
 #else
-    (void)cnt;
+  (void)cnt;
 #endif
-  }
   h.prim_id = (int)(ty == RTB_PRIM_SPHERE ? s.sphere_gid[idx] : ty == RTB_PRIM_TRIANGLE ? s.triangle_gid[idx] : s.rect_gid[idx]);
   hits[i] = h;
 }
 
 // ---- generate: Camera::GetRay + SampleSquare + defocus_disk_sample (camera.h:134-144,196-203) --
-// Slot q+k of the queue receives local sample g0+k; pixel order is the host-built 8x4-tiled
-// permutation so that a warp's primary rays stay coherent.
-__global__ void generate_kernel(PathQueue q, uint32_t q_offset, uint32_t count, unsigned long long g0, RenderConsts rc,
-                                const uint32_t* __restrict__ pixel_order) {
-  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= count) return;
-  const unsigned long long g = g0 + k;
+// Local sample g of this call = (pixel pixel_order[g % n_pixels], sample spp_begin + g / n_pixels); pixel
+// order is the host-built 8x4-tiled permutation so that a warp's primary rays stay coherent.
+struct PathState {  // what a path carries besides its ray
+  float tr, tg, tb;   // throughput
+  uint32_t pixel, sample, bounce;
+};
+
+__device__ __forceinline__ void generate_sample(const RenderConsts& rc, const uint32_t* __restrict__ pixel_order, unsigned long long g,
+                                                float4& ro, float4& rd, PathState& ps) {
   const uint32_t s_local = (uint32_t)(g / rc.n_pixels), pl = (uint32_t)(g % rc.n_pixels);
   const uint32_t pixel = __ldg(&pixel_order[pl]);
   const uint32_t sample = (uint32_t)rc.spp_begin + s_local;
@@ -292,16 +352,34 @@ __global__ void generate_kernel(PathQueue q, uint32_t q_offset, uint32_t count, 
   }
   f3 dir = target - origin;
   if (c.depth_camera) dir = normalize3(dir);  // DepthCamera::GetPixel normalises first (camera.h:223)
+  ro = make_float4(origin.x, origin.y, origin.z, 0.001f);  // Interval(0.001, inf), camera.h:158
+  rd = make_float4(dir.x, dir.y, dir.z, __int_as_float(0x7f800000));
+  ps.tr = ps.tg = ps.tb = 1.0f;
+  ps.pixel = pixel;
+  ps.sample = sample;
+  ps.bounce = 0u;
+}
+
+// Slot q_offset + k of the queue receives local sample g0 + k.
+__global__ void generate_kernel(PathQueue q, uint32_t q_offset, uint32_t count, unsigned long long g0, RenderConsts rc,
+                                const uint32_t* __restrict__ pixel_order) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= count) return;
+  float4 ro, rd;
+  PathState ps;
+  generate_sample(rc, pixel_order, g0 + k, ro, rd, ps);
   const uint32_t slot = q_offset + k;
-  q.ro[slot] = make_float4(origin.x, origin.y, origin.z, 0.001f);  // Interval(0.001, inf), camera.h:158
-  q.rd[slot] = make_float4(dir.x, dir.y, dir.z, __int_as_float(0x7f800000));
-  q.thr[slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(pixel));
-  q.meta[slot] = make_uint2(sample, 0u);
+  q.ro[slot] = ro;
+  q.rd[slot] = rd;
+  q.thr[slot] = make_float4(ps.tr, ps.tg, ps.tb, __uint_as_float(ps.pixel));
+  q.meta[slot] = make_uint2(ps.sample, ps.bounce);
 }
 
 // ---- extend: Bvh::Hit for every live path (src/geom/bvh.h:71-119) ------------------------------
 struct ExtendIo {
+  static constexpr int kServiceLanes = RTB_REFILL_LANES;
   uint32_t n;
+  unsigned rays;
   const float4* ro;
   const float4* rd;
   float* hit_t;
@@ -310,20 +388,28 @@ struct ExtendIo {
     o = ro[i];
     d = rd[i];
   }
-  __device__ __forceinline__ void store(uint32_t i, uint32_t ref, float tf, double, bool) const {
+  __device__ __forceinline__ bool finish(uint32_t i, uint32_t ref, float tf, const TravRay&, float4&, float4&) const {
     hit_t[i] = tf;
     hit_ref[i] = ref;
+    return false;
   }
 };
 
 template <bool kUseSmem>
-__global__ void __launch_bounds__(256, RTB_TRACE_MIN_BLOCKS) extend_kernel(DevScene s, PathQueue q, uint32_t n, float* __restrict__ hit_t,
+__global__ void __launch_bounds__(kTraceBlock, RTB_TRACE_MIN_BLOCKS) extend_kernel(DevScene s, PathQueue q, uint32_t n, float* __restrict__ hit_t,
                                                      uint32_t* __restrict__ hit_ref, unsigned int* cursor, HitCounters* cnt) {
   extern __shared__ float4 smem_pairs[];
   if (kUseSmem) stage_top(s, smem_pairs);
-  trace_loop<kUseSmem>(s, smem_pairs, ExtendIo{n, q.ro, q.rd, hit_t, hit_ref}, cursor, cnt);
+  ExtendIo io{n, 0u, q.ro, q.rd, hit_t, hit_ref};
+  trace_loop<kUseSmem>(s, smem_pairs, smem_stack_base(s, smem_pairs, kUseSmem), io, cursor, cnt);
 }
 
+// ---- shade -------------------------------------------------------------------------------------
+// One bounce of one path.  Mode A: Camera::GetPixel (camera.h:148-174) with Material::Scatter
+// (material.cc:20-34,82-94,148-172,273-280).  Mode B: the shading loop of
+// WavefrontRenderer::Render (wavefront.cc:109-209) with Material::Sample (material.cc:57-74,
+// 117-141,194-256) and Russian roulette.  Finished radiance goes to the accumulator; returns
+// true when the path continues, with (ro, rd, ps) replaced by the next ray and path state.
 __device__ __forceinline__ void add_radiance(float* accum, uint32_t pixel, f3 L) {
   float* a = accum + 3 * (size_t)pixel;
   if (L.x != 0.0f) atomicAdd(a + 0, L.x);
@@ -331,129 +417,194 @@ __device__ __forceinline__ void add_radiance(float* accum, uint32_t pixel, f3 L)
   if (L.z != 0.0f) atomicAdd(a + 2, L.z);
 }
 
-// ---- shade + compact ---------------------------------------------------------------------------
-// Mode A: Camera::GetPixel (camera.h:148-174) with Material::Scatter (material.cc:20-34,82-94,
-// 148-172,273-280).  Mode B: the shading loop of WavefrontRenderer::Render (wavefront.cc:109-209)
-// with Material::Sample (material.cc:57-74,117-141,194-256) and Russian roulette.
-// Survivors are appended to `out` with one atomicAdd per warp (ballot + popc prefix).
+__device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts& rc, float* accum, float4& ro, float4& rd, PathState& ps,
+                                           float hit_t, uint32_t ref) {
+  bool alive = false;
+  const f3 d = mk3(rd.x, rd.y, rd.z);
+  const uint32_t pixel = ps.pixel;
+  const f3 thr = mk3(ps.tr, ps.tg, ps.tb);
+  const uint32_t bounce = ps.bounce;
+  if (rc.cam.depth_camera) {
+    // DepthCamera::GetPixel (camera.h:217-236): t of the normalised ray in red, black past max_dist 20 / on a miss
+    const float t = hit_t;
+    if (ref != kNoHit && t < 20.0f) add_radiance(accum, pixel, mk3(t, 0.0f, 0.0f));
+  } else if (ref == kNoHit || (rc.mode == RTB_MODE_B && (int)bounce >= rc.max_depth)) {
+    add_radiance(accum, pixel, thr * sky(d));  // camera.h:171-173 / wavefront.cc:122-129
+  } else {
+    const float t = hit_t;
+    const f3 p = mk3(fmaf(t, d.x, ro.x), fmaf(t, d.y, ro.y), fmaf(t, d.z, ro.z));
+    f3 n_out;
+    float u, v;
+    uint32_t mat_id;
+    surface_at(s, ref, p, n_out, u, v, mat_id);
+    const bool front = dot3(d, n_out) < 0.0f;  // HitRecord::set_face_normal, hittable.h:31-34
+    const f3 nrm = front ? n_out : -n_out;
+    const RtbMaterial m = s.materials[mat_id];
+    const uint4 rnd = philox4x32_10(make_uint4(pixel, ps.sample, bounce, 0u), rc.key);
+    f3 atten = mk3(1.0f, 1.0f, 1.0f), dir = nrm;
+    if (rc.mode == RTB_MODE_A) {
+      if (m.type == RTB_MAT_LAMBERTIAN) {  // material.cc:20-34
+        dir = nrm + unit_vector(u01(rnd.x), u01(rnd.y));
+        if (fabsf(dir.x) < 1e-8f && fabsf(dir.y) < 1e-8f && fabsf(dir.z) < 1e-8f) dir = nrm;
+        atten = texture_value(s, m.tex, u, v, p);
+        alive = true;
+      } else if (m.type == RTB_MAT_METAL) {  // material.cc:82-94: reflects the UN-normalised direction
+        dir = reflect3(d, nrm) + m.fuzz * unit_vector(u01(rnd.x), u01(rnd.y));
+        atten = mk3(m.albedo[0], m.albedo[1], m.albedo[2]);
+        alive = dot3(dir, nrm) > 0.0f;
+      } else if (m.type == RTB_MAT_DIELECTRIC) {  // material.cc:148-172
+        const float eta = front ? (1.0f / m.ior) : m.ior;
+        const f3 ud = normalize3(d);
+        const float cos_theta = fminf(dot3(-ud, nrm), 1.0f);
+        const float sin_theta = sqrtf(fmaxf(0.0f, 1.0f - cos_theta * cos_theta));
+        const bool cannot_refract = eta * sin_theta > 1.0f;
+        dir = (cannot_refract || schlick(cos_theta, eta) > u01(rnd.z)) ? reflect3(ud, nrm) : refract3(ud, nrm, eta);
+        alive = true;
+      } else {  // DiffuseLight: emits, never scatters (material.cc:273-280,312-316)
+        add_radiance(accum, pixel, thr * texture_value(s, m.tex, u, v, p));
+      }
+      ps.tr = thr.x * atten.x; ps.tg = thr.y * atten.y; ps.tb = thr.z * atten.z;
+      // the recursion bottoms out in black when depth reaches 0 (camera.h:149-151)
+      if ((int)bounce + 1 >= rc.max_depth) alive = false;
+    } else {
+      // ---- mode B (wavefront.cc:131-207)
+      f3 emitted = mk3(0, 0, 0);
+      if (m.type == RTB_MAT_DIFFUSE_LIGHT) emitted = texture_value(s, m.tex, u, v, p);
+      const bool near_zero = fabsf(emitted.x) < 1e-8f && fabsf(emitted.y) < 1e-8f && fabsf(emitted.z) < 1e-8f;
+      f3 tp = thr;
+      if (!near_zero) {
+        add_radiance(accum, pixel, thr * emitted);  // wavefront.cc:134-142
+      } else if (m.type == RTB_MAT_LAMBERTIAN) {
+        // Lambertian::Sample (material.cc:57-74): cosine direction, f = albedo/pi, pdf = cos/pi;
+        // wavefront.cc:176-186 multiplies by f*cos/pdf = albedo.  RandomCosineDirection math_utils.h:104-123.
+        const float r1 = u01(rnd.x), r2 = u01(rnd.y);
+        float sn, cs;
+        sincospif(2.0f * r1, &sn, &cs);
+        const float rr = sqrtf(r2), z = sqrtf(fmaxf(0.0f, 1.0f - r2));
+        const f3 w = normalize3(nrm);
+        const f3 a = fabsf(w.x) > 0.9f ? mk3(0, 1, 0) : mk3(1, 0, 0);
+        const f3 vv = normalize3(cross3(w, a));
+        const f3 uu = cross3(vv, w);
+        dir = normalize3((rr * cs) * uu + (rr * sn) * vv + z * w);
+        const float cosv = dot3(dir, nrm);
+        const float pdf = cosv / 3.14159265358979323846f;
+        if (cosv > 0.0f && pdf >= 1e-6f) {  // material.cc:66-68, wavefront.cc:178-183
+          tp = thr * texture_value(s, m.tex, u, v, p);
+          alive = true;
+        }
+      } else if (m.type == RTB_MAT_METAL) {  // Metal::Sample, material.cc:117-141
+        const f3 wo = -normalize3(d);
+        dir = normalize3(reflect3(-wo, nrm) + m.fuzz * unit_vector(u01(rnd.x), u01(rnd.y)));
+        if (dot3(dir, nrm) > 0.0f) {
+          tp = thr * mk3(m.albedo[0], m.albedo[1], m.albedo[2]);
+          alive = true;
+        }
+      } else if (m.type == RTB_MAT_DIELECTRIC) {  // Dielectric::Sample, material.cc:194-256
+        const float eta = front ? (1.0f / m.ior) : m.ior;
+        const f3 wi_inc = normalize3(d);
+        const float cos_i = fminf(fmaxf(dot3(wi_inc, nrm), -1.0f), 1.0f);
+        const float sin_i = sqrtf(fmaxf(0.0f, 1.0f - cos_i * cos_i));
+        const float sin_t = eta * sin_i;
+        alive = true;
+        if (sin_t >= 1.0f || u01(rnd.z) < schlick(fabsf(cos_i), m.ior)) {
+          dir = reflect3(wi_inc, nrm);
+        } else {
+          dir = refract3(wi_inc, nrm, eta);
+          tp = (eta * eta) * thr;  // material.cc:252-253
+        }
+      }
+      // Russian roulette, wavefront.cc:189-205 (child depth > 5)
+      if (alive && (int)bounce + 1 > 5) {
+        const float pr = fminf(fmaxf(fmaxf(tp.x, fmaxf(tp.y, tp.z)), 0.1f), 0.95f);
+        if (u01(rnd.w) > pr) alive = false;
+        else tp = (1.0f / pr) * tp;
+      }
+      ps.tr = tp.x; ps.tg = tp.y; ps.tb = tp.z;
+    }
+    if (alive) {
+      ro = make_float4(p.x, p.y, p.z, 0.001f);
+      rd = make_float4(dir.x, dir.y, dir.z, __int_as_float(0x7f800000));
+      ps.bounce = bounce + 1u;
+    }
+  }
+  return alive;
+}
+
+// ---- path kernel: generate / traverse / shade per lane, no queues ------------------------------
+// The same persistent traversal loop, but a finished ray is shaded in place (with the other lanes
+// that are waiting in the same service phase) and the lane carries on with the bounced ray; a dead
+// path is replaced from the global cursor.  Two sources of work:
+//   kFromQueue = true   the last live paths of a wavefront ("drain"): the bounce chain of the few
+//                       deepest paths no longer costs one latency-bound launch per bounce;
+//   kFromQueue = false  camera samples g0 .. g0+n: the whole render in one launch (the default mode).
+#ifndef RTB_PATH_MIN_BLOCKS
+#define RTB_PATH_MIN_BLOCKS 4  // 64 registers: measured faster than 3 x 80 or 2 x 128 despite the spills
+#endif
+template <bool kFromQueue>
+struct PathIo {
+  static constexpr int kServiceLanes = RTB_PATH_REFILL_LANES;
+  uint32_t n;
+  unsigned rays;
+  const DevScene& s;
+  const RenderConsts& rc;
+  float* accum;
+  PathQueue q;
+  unsigned long long g0;
+  const uint32_t* pixel_order;
+  PathState ps;
+  __device__ __forceinline__ void load(uint32_t i, float4& o, float4& d) {
+    if (kFromQueue) {
+      o = q.ro[i];
+      d = q.rd[i];
+      const float4 th = q.thr[i];
+      const uint2 meta = q.meta[i];
+      ps.tr = th.x; ps.tg = th.y; ps.tb = th.z;
+      ps.pixel = __float_as_uint(th.w);
+      ps.sample = meta.x;
+      ps.bounce = meta.y;
+    } else {
+      generate_sample(rc, pixel_order, g0 + i, o, d, ps);
+    }
+  }
+  __device__ __forceinline__ bool finish(uint32_t, uint32_t ref, float tf, const TravRay& r, float4& o, float4& d) {
+    o = make_float4(r.ox, r.oy, r.oz, r.tmin);
+    d = make_float4(r.dx, r.dy, r.dz, r.tmax);
+    return shade_path(s, rc, accum, o, d, ps, tf, ref);
+  }
+};
+
+template <bool kUseSmem, bool kFromQueue>
+__global__ void __launch_bounds__(kTraceBlock, RTB_PATH_MIN_BLOCKS) path_kernel(DevScene s, PathQueue q, uint32_t n, unsigned long long g0,
+                                                                               RenderConsts rc, const uint32_t* __restrict__ pixel_order,
+                                                                               float* accum, unsigned int* cursor,
+                                                                               unsigned long long* ray_count, HitCounters* cnt) {
+  extern __shared__ float4 smem_pairs[];
+  if (kUseSmem) stage_top(s, smem_pairs);
+  PathIo<kFromQueue> io{n, 0u, s, rc, accum, q, g0, pixel_order, PathState{}};
+  trace_loop<kUseSmem>(s, smem_pairs, smem_stack_base(s, smem_pairs, kUseSmem), io, cursor, cnt);
+  const unsigned total = __reduce_add_sync(kFull, io.rays);
+  if ((threadIdx.x & 31u) == 0u && total) atomicAdd(ray_count, (unsigned long long)total);
+}
+
+// Wavefront form: one thread per queue entry; survivors are appended to `out` with one atomicAdd
+// per warp (ballot + popc prefix).
 __global__ void __launch_bounds__(256) shade_kernel(DevScene s, PathQueue in, uint32_t n, const float* __restrict__ hit_t,
                                                     const uint32_t* __restrict__ hit_ref, PathQueue out, unsigned int* out_count,
                                                     float* accum, RenderConsts rc) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   bool alive = false;
-  float4 n_ro, n_rd, n_thr;
-  uint2 n_meta;
+  float4 ro, rd;
+  PathState ps;
   if (i < n) {
-    const float4 ro = in.ro[i], rd = in.rd[i], th = in.thr[i];
+    ro = in.ro[i];
+    rd = in.rd[i];
+    const float4 th = in.thr[i];
     const uint2 meta = in.meta[i];
-    const uint32_t ref = hit_ref[i];
-    const uint32_t pixel = __float_as_uint(th.w);
-    const f3 thr = mk3(th.x, th.y, th.z);
-    const f3 d = mk3(rd.x, rd.y, rd.z);
-    const uint32_t bounce = meta.y;
-    if (rc.cam.depth_camera) {
-      // DepthCamera::GetPixel (camera.h:217-236): t of the normalised ray in red, black past max_dist 20 / on a miss
-      const float t = hit_t[i];
-      if (ref != kNoHit && t < 20.0f) add_radiance(accum, pixel, mk3(t, 0.0f, 0.0f));
-    } else if (ref == kNoHit || (rc.mode == RTB_MODE_B && (int)bounce >= rc.max_depth)) {
-      add_radiance(accum, pixel, thr * sky(d));  // camera.h:171-173 / wavefront.cc:122-129
-    } else {
-      const float t = hit_t[i];
-      const f3 p = mk3(fmaf(t, d.x, ro.x), fmaf(t, d.y, ro.y), fmaf(t, d.z, ro.z));
-      f3 n_out;
-      float u, v;
-      uint32_t mat_id;
-      surface_at(s, ref, p, n_out, u, v, mat_id);
-      const bool front = dot3(d, n_out) < 0.0f;  // HitRecord::set_face_normal, hittable.h:31-34
-      const f3 nrm = front ? n_out : -n_out;
-      const RtbMaterial m = s.materials[mat_id];
-      const uint4 rnd = philox4x32_10(make_uint4(pixel, meta.x, bounce, 0u), rc.key);
-      f3 atten = mk3(1.0f, 1.0f, 1.0f), dir = nrm;
-      if (rc.mode == RTB_MODE_A) {
-        if (m.type == RTB_MAT_LAMBERTIAN) {  // material.cc:20-34
-          dir = nrm + unit_vector(u01(rnd.x), u01(rnd.y));
-          if (fabsf(dir.x) < 1e-8f && fabsf(dir.y) < 1e-8f && fabsf(dir.z) < 1e-8f) dir = nrm;
-          atten = texture_value(s, m.tex, u, v, p);
-          alive = true;
-        } else if (m.type == RTB_MAT_METAL) {  // material.cc:82-94: reflects the UN-normalised direction
-          dir = reflect3(d, nrm) + m.fuzz * unit_vector(u01(rnd.x), u01(rnd.y));
-          atten = mk3(m.albedo[0], m.albedo[1], m.albedo[2]);
-          alive = dot3(dir, nrm) > 0.0f;
-        } else if (m.type == RTB_MAT_DIELECTRIC) {  // material.cc:148-172
-          const float eta = front ? (1.0f / m.ior) : m.ior;
-          const f3 ud = normalize3(d);
-          const float cos_theta = fminf(dot3(-ud, nrm), 1.0f);
-          const float sin_theta = sqrtf(fmaxf(0.0f, 1.0f - cos_theta * cos_theta));
-          const bool cannot_refract = eta * sin_theta > 1.0f;
-          dir = (cannot_refract || schlick(cos_theta, eta) > u01(rnd.z)) ? reflect3(ud, nrm) : refract3(ud, nrm, eta);
-          alive = true;
-        } else {  // DiffuseLight: emits, never scatters (material.cc:273-280,312-316)
-          add_radiance(accum, pixel, thr * texture_value(s, m.tex, u, v, p));
-        }
-        n_thr = make_float4(thr.x * atten.x, thr.y * atten.y, thr.z * atten.z, th.w);
-        // the recursion bottoms out in black when depth reaches 0 (camera.h:149-151)
-        if ((int)bounce + 1 >= rc.max_depth) alive = false;
-      } else {
-        // ---- mode B (wavefront.cc:131-207)
-        f3 emitted = mk3(0, 0, 0);
-        if (m.type == RTB_MAT_DIFFUSE_LIGHT) emitted = texture_value(s, m.tex, u, v, p);
-        const bool near_zero = fabsf(emitted.x) < 1e-8f && fabsf(emitted.y) < 1e-8f && fabsf(emitted.z) < 1e-8f;
-        f3 tp = thr;
-        if (!near_zero) {
-          add_radiance(accum, pixel, thr * emitted);  // wavefront.cc:134-142
-        } else if (m.type == RTB_MAT_LAMBERTIAN) {
-          // Lambertian::Sample (material.cc:57-74): cosine direction, f = albedo/pi, pdf = cos/pi;
-          // wavefront.cc:176-186 multiplies by f*cos/pdf = albedo.  RandomCosineDirection math_utils.h:104-123.
-          const float r1 = u01(rnd.x), r2 = u01(rnd.y);
-          float sn, cs;
-          sincospif(2.0f * r1, &sn, &cs);
-          const float rr = sqrtf(r2), z = sqrtf(fmaxf(0.0f, 1.0f - r2));
-          const f3 w = normalize3(nrm);
-          const f3 a = fabsf(w.x) > 0.9f ? mk3(0, 1, 0) : mk3(1, 0, 0);
-          const f3 vv = normalize3(cross3(w, a));
-          const f3 uu = cross3(vv, w);
-          dir = normalize3((rr * cs) * uu + (rr * sn) * vv + z * w);
-          const float cosv = dot3(dir, nrm);
-          const float pdf = cosv / 3.14159265358979323846f;
-          if (cosv > 0.0f && pdf >= 1e-6f) {  // material.cc:66-68, wavefront.cc:178-183
-            tp = thr * texture_value(s, m.tex, u, v, p);
-            alive = true;
-          }
-        } else if (m.type == RTB_MAT_METAL) {  // Metal::Sample, material.cc:117-141
-          const f3 wo = -normalize3(d);
-          dir = normalize3(reflect3(-wo, nrm) + m.fuzz * unit_vector(u01(rnd.x), u01(rnd.y)));
-          if (dot3(dir, nrm) > 0.0f) {
-            tp = thr * mk3(m.albedo[0], m.albedo[1], m.albedo[2]);
-            alive = true;
-          }
-        } else if (m.type == RTB_MAT_DIELECTRIC) {  // Dielectric::Sample, material.cc:194-256
-          const float eta = front ? (1.0f / m.ior) : m.ior;
-          const f3 wi_inc = normalize3(d);
-          const float cos_i = fminf(fmaxf(dot3(wi_inc, nrm), -1.0f), 1.0f);
-          const float sin_i = sqrtf(fmaxf(0.0f, 1.0f - cos_i * cos_i));
-          const float sin_t = eta * sin_i;
-          alive = true;
-          if (sin_t >= 1.0f || u01(rnd.z) < schlick(fabsf(cos_i), m.ior)) {
-            dir = reflect3(wi_inc, nrm);
-          } else {
-            dir = refract3(wi_inc, nrm, eta);
-            tp = (eta * eta) * thr;  // material.cc:252-253
-          }
-        }
-        // Russian roulette, wavefront.cc:189-205 (child depth > 5)
-        if (alive && (int)bounce + 1 > 5) {
-          const float pr = fminf(fmaxf(fmaxf(tp.x, fmaxf(tp.y, tp.z)), 0.1f), 0.95f);
-          if (u01(rnd.w) > pr) alive = false;
-          else tp = (1.0f / pr) * tp;
-        }
-        n_thr = make_float4(tp.x, tp.y, tp.z, th.w);
-      }
-      if (alive) {
-        n_ro = make_float4(p.x, p.y, p.z, 0.001f);
-        n_rd = make_float4(dir.x, dir.y, dir.z, __int_as_float(0x7f800000));
-        n_meta = make_uint2(meta.x, bounce + 1u);
-      }
-    }
+    ps.tr = th.x; ps.tg = th.y; ps.tb = th.z;
+    ps.pixel = __float_as_uint(th.w);
+    ps.sample = meta.x;
+    ps.bounce = meta.y;
+    alive = shade_path(s, rc, accum, ro, rd, ps, hit_t[i], hit_ref[i]);
   }
   // ---- compact: ballot + prefix inside the warp, one atomic per warp
   const unsigned ballot = __ballot_sync(0xffffffffu, alive);
@@ -464,10 +615,10 @@ __global__ void __launch_bounds__(256) shade_kernel(DevScene s, PathQueue in, ui
     base = __shfl_sync(0xffffffffu, base, __ffs(ballot) - 1);
     if (alive) {
       const uint32_t slot = base + __popc(ballot & ((1u << lane) - 1u));
-      out.ro[slot] = n_ro;
-      out.rd[slot] = n_rd;
-      out.thr[slot] = n_thr;
-      out.meta[slot] = n_meta;
+      out.ro[slot] = ro;
+      out.rd[slot] = rd;
+      out.thr[slot] = make_float4(ps.tr, ps.tg, ps.tb, __uint_as_float(ps.pixel));
+      out.meta[slot] = make_uint2(ps.sample, ps.bounce);
     }
   }
 }

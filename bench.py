@@ -65,10 +65,11 @@ class ClockSampler:
 
     def __init__(self, device_index):
         self.dev, self.rows, self.proc = device_index, [], None
+        self.window = None  # (t0, t1) of the timed region; samples outside it are dropped
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50",
                                           "-i", str(self.dev)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._pump, daemon=True)
             self.thread.start()
@@ -77,7 +78,7 @@ class ClockSampler:
 
     def _pump(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
 
     def stop(self):
         if not self.proc:
@@ -88,7 +89,11 @@ class ClockSampler:
         except subprocess.TimeoutExpired:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
-        for r in self.rows:
+        rows = [r for t, r in self.rows if self.window is None or self.window[0] <= t <= self.window[1] + 0.15]
+        if not rows and self.rows:  # region shorter than the sampling period: the sample nearest to it
+            mid = 0.5 * (self.window[0] + self.window[1])
+            rows = [min(self.rows, key=lambda tr: abs(tr[0] - mid))[1]]
+        for r in rows:
             try:
                 sm.append(float(r[1])); mx.append(float(r[2]))
             except (ValueError, IndexError):
@@ -140,14 +145,16 @@ def _cpu_has(flag):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", default="bunny", choices=list(CONFIGS))
     ap.add_argument("--spp", type=int, default=0, help="override the configuration's spp (then the line says so)")
     ap.add_argument("--width", type=int, default=0)
     ap.add_argument("--pool", type=int, default=0)
     ap.add_argument("--mode", default="A", choices=["A", "B"])
+    ap.add_argument("--pipeline", default="path", choices=["path", "wavefront"],
+                    help="path = the default persistent path kernel; wavefront = generate/extend/shade kernels over queues")
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
@@ -198,35 +205,39 @@ def main():
     accum = torch.zeros(n_pix * 3, dtype=torch.float32, device="cuda")
     rgb8 = torch.zeros(n_pix * 3, dtype=torch.uint8, device="cuda")
     flush = torch.empty(384 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
-    stream = torch.cuda.current_stream().cuda_stream
+    tstream = torch.cuda.Stream()  # reduce + resolve run here, bracketed by the two events
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    base_flags = rt.RENDER_WAVEFRONT if args.pipeline == "wavefront" else 0
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step(flags=0):
+    def step(flags=None):
+        flags = base_flags if flags is None else flags
         """one render of the configuration at this rank + reduce + resolve; returns (device ms, stats)"""
         b_, e_ = rt.multigpu.weak_slice(spp, rank)
-        st = ds.render_device(cam, accum.data_ptr(), b_, e_, depth, mode=mode, pool_size=args.pool, flags=flags)
-        ev[0].record()
-        if world > 1:
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
-        if rank == 0:
-            rt.binding._check(lib, lib.rtb_resolve_device(accum.data_ptr(), n_pix, spp * world, rgb8.data_ptr(), stream))
-        ev[1].record()
+        st = ds.render_device(cam, accum.data_ptr(), b_, e_, depth, mode=mode, pool_size=args.pool, flags=flags)  # synchronous
+        with torch.cuda.stream(tstream):
+            ev[0].record(tstream)
+            if world > 1:
+                dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+            if rank == 0:
+                rt.binding._check(lib, lib.rtb_resolve_device(accum.data_ptr(), n_pix, spp * world, rgb8.data_ptr(), tstream.cuda_stream))
+            ev[1].record(tstream)
         torch.cuda.synchronize()
         return st["ms_total"] + ev[0].elapsed_time(ev[1]), st
 
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()  # nvidia-smi takes a few hundred ms to deliver its first sample: start it before the warm-up
     for _ in range(W):
         flush.fill_(1)
         barrier()
         step()
-    clocks = ClockSampler(local_rank)
-    if rank == 0:
-        clocks.start()
     dev_ms, wall_ms, stats = [], [], []
+    t_region = time.perf_counter()
     for _ in range(K):
         flush.fill_(1)  # evict the scene and the path pool from L2 between timed steps (untimed)
         barrier()
@@ -236,6 +247,7 @@ def main():
         dev_ms.append(ms)
         stats.append(st)
     barrier()
+    clocks.window = (t_region, time.perf_counter())
     clk = clocks.stop() if rank == 0 else None
     # per-kernel times: the same step with ONE wavefront in flight and an event pair around every launch
     # (RTB_RENDER_SERIAL); in the timed steps above several wavefronts overlap, so kernels cannot be timed singly
@@ -244,6 +256,15 @@ def main():
         flush.fill_(1)
         barrier()
         serial_stats.append(step(rt.RENDER_SERIAL)[1])
+    # the other pipeline, for the record (not the headline)
+    other_flags = 0 if args.pipeline == "wavefront" else rt.RENDER_WAVEFRONT
+    other_ms = []
+    for k in range(1 + min(K, 5)):
+        flush.fill_(1)
+        barrier()
+        ms_o, _ = step(other_flags)
+        if k:
+            other_ms.append(ms_o)
     # max over ranks of the K-step time
     tot = torch.tensor([sum(dev_ms), sum(wall_ms)], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -259,16 +280,17 @@ def main():
     e2e_ms = []
     import ctypes as C
     host_img = torch.empty(n_pix * 3, dtype=torch.float32).pin_memory()
-    for k in range(min(W, 1) + K):
+    KE = min(K, 10)
+    for k in range(min(W, 1) + KE):
         barrier()
         t0 = time.perf_counter()
         ds2 = rt.DeviceScene(hs, device=local_rank)  # rtb_scene_create: copies every scene array host -> device
         if world == 1:
-            prm = rt.binding.RtbRenderParams(0, spp, depth, mode, 0x3360, args.pool, 0)
+            prm = rt.binding.RtbRenderParams(0, spp, depth, mode, 0x3360, args.pool, base_flags)
             s2 = rt.binding.RtbStats()
             rt.binding._check(lib, lib.rtb_render(ds2._h, C.byref(cam), C.byref(prm), host_img.data_ptr(), C.byref(s2)))
         else:
-            ds2.render_device(cam, accum.data_ptr(), rank * spp, (rank + 1) * spp, depth, mode=mode, pool_size=args.pool)
+            ds2.render_device(cam, accum.data_ptr(), rank * spp, (rank + 1) * spp, depth, mode=mode, pool_size=args.pool, flags=base_flags)
             dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
             if rank == 0:
                 host_img.copy_(accum, non_blocking=False)
@@ -294,18 +316,23 @@ def main():
                        "image": [cam.width, cam.height], "spp_per_gpu": spp, "spp_total": spp * world, "max_depth": depth,
                        "estimator": args.mode, "parallelism": f"spp-split x{world}, scene replicated, 1 NCCL reduce(sum,f32) of {n_pix * 12} B",
                        "l2": "384 MiB buffer written between timed steps (L2 flushed); scene itself is L2-resident by design",
-                       "pool_paths": args.pool or (1 << 21), "wavefronts_in_flight": int(os.environ.get("RTB_WAVES", "4")), "scene_build_s_untimed": round(t_build, 3)},
-            "e2e": {"value": samples_per_step / (e2e_tot.item() / K * 1e-3) / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_tot.item() / K,
+                       "pipeline": "persistent path kernel (generate + traverse + shade per lane, one launch per step)" if args.pipeline == "path"
+                       else f"wavefront: generate / extend / shade+compact over queues, pool {args.pool or (1 << 21)} paths x {os.environ.get('RTB_WAVES', '4')} wavefronts in flight",
+                       "scene_build_s_untimed": round(t_build, 3)},
+            "e2e": {"value": samples_per_step / (e2e_tot.item() / KE * 1e-3) / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_tot.item() / KE, "steps": KE,
                     "what": "rtb_scene_create (all scene arrays H2D) + rtb_render with a host rgb buffer (D2H) + rtb_scene_destroy, wall clock"},
             "gpu_launches": int(sum(s["launches"] for s in stats) + K),
+            "other_pipeline": {"name": "path" if args.pipeline == "wavefront" else "wavefront", "ms_per_step": float(np.mean(other_ms)),
+                               "msamples_per_s": stats[-1]["samples"] / float(np.mean(other_ms)) / 1e3},
             "clocks": clk,
-            "kernel_ms_per_step": {**{k: float(np.mean([s[k] for s in serial_stats])) for k in ("ms_generate", "ms_extend", "ms_shade", "ms_total")},
-                                   "how": "same step re-run with one wavefront in flight (RTB_RENDER_SERIAL), CUDA events around every launch"},
-            "iterations_per_step": stats[-1]["iterations"],
+            "kernel_ms_per_step": {"path_kernel": float(np.mean([s["ms_total"] for s in stats])) if args.pipeline == "path" else None,
+                                   "wavefront_serial": {k: float(np.mean([s[k] for s in serial_stats])) for k in ("ms_generate", "ms_extend", "ms_shade", "ms_drain", "ms_total")},
+                                   "how": "path_kernel: CUDA events around the one launch of each timed step; wavefront_serial: the wavefront pipeline re-run with one "
+                                          "wavefront in flight (RTB_RENDER_SERIAL) and events around every launch"},
         }
         if not args.no_roofline and world == 1:
-            line["roofline"] = roofline(rt, hs, cam, cfg, serial_stats, mode, args.pool)
+            line["roofline"] = roofline(rt, hs, cam, cfg, stats if args.pipeline == "path" else serial_stats, mode, args.pool, args.pipeline)
         elif not args.no_roofline:
             line["roofline"] = {"note": "measured at N=1 only (one process, one GPU)"}
         if not args.no_cpu_baseline and world == 1:
@@ -332,8 +359,11 @@ def scene_bytes(d):
                + d.n_materials * 32 + d.n_textures * 32)
 
 
-def roofline(rt, hs, cam, cfg, stats, mode, pool):
-    """extend (BVH traversal) kernel: algorithmic bytes and flops per launch / its CUDA-event time."""
+def roofline(rt, hs, cam, cfg, stats, mode, pool, pipeline):
+    """The dominant kernel - path_kernel (default pipeline: one launch per step) or extend_kernel (wavefront pipeline) -
+    against the HBM roof the contract asks for and against the roof that actually binds an L2-resident scene.
+    Algorithmic bytes / flops per ray are SURVEY 8(d)'s per-unit figures with the traversal counts of this workload
+    taken from the instrumented build (librtb200_counters.so); the path kernel adds its accumulator read-modify-write."""
     peaks_file = ROOT / "MEASURED_PEAKS.json"
     hbm_peak, src = 6650.0, "fallback (B200_PROFILING.md)"
     if peaks_file.exists():
@@ -342,29 +372,43 @@ def roofline(rt, hs, cam, cfg, stats, mode, pool):
     # per-ray traversal counts from the instrumented build on the same workload at reduced spp (counts per ray are spp-invariant)
     hs_c = rt.HostScene.build(*cfg["scene"], counters=True)
     ds_c = rt.DeviceScene(hs_c)
-    _, sc = ds_c.render(cam, spp=max(1, min(4, cfg["spp"])), max_depth=cfg["depth"], mode=mode, pool_size=pool)
+    _, sc = ds_c.render(cam, spp=max(1, min(4, cfg["spp"])), max_depth=cfg["depth"], mode=mode, pool_size=pool,
+                        flags=rt.RENDER_WAVEFRONT if pipeline == "wavefront" else 0)
     ds_c.close()
     per_ray = {k: sc[k] / sc["rays"] for k in ("node_visits", "sphere_tests", "triangle_tests", "rect_tests")}
     refs = per_ray["sphere_tests"] + per_ray["triangle_tests"] + per_ray["rect_tests"]
+    io_ray = B_RAY_IO if pipeline == "wavefront" else 0  # the path kernel keeps rays and hits in registers
     bytes_ray = (B_NODE * per_ray["node_visits"] + B_SPHERE * per_ray["sphere_tests"] + B_TRI * per_ray["triangle_tests"]
-                 + B_RECT * per_ray["rect_tests"] + B_REF * refs + B_RAY_IO)
+                 + B_RECT * per_ray["rect_tests"] + B_REF * refs + io_ray)
     f32_ray = F32_NODE * per_ray["node_visits"]
     f64_ray = F64_SPHERE * per_ray["sphere_tests"] + F64_TRI * per_ray["triangle_tests"] + F64_RECT * per_ray["rect_tests"]
     rays = float(np.mean([s["rays"] for s in stats]))
-    launches = float(np.mean([s["iterations"] for s in stats]))
-    ext_ms = float(np.mean([s["ms_extend"] for s in stats]))
-    gbs = bytes_ray * rays / (ext_ms * 1e-3) / 1e9
-    t_l2 = bytes_ray * rays / (mp["l2_gbs"] * 1e9)
+    samples = float(np.mean([s["samples"] for s in stats]))
+    if pipeline == "path":
+        kernel, launches = "path_kernel (generate + closest-hit BVH traversal + shade, persistent)", float(np.mean([s["launches"] for s in stats]))
+        k_ms = float(np.mean([s["ms_total"] for s in stats]))
+        extra = 12.0 * 2 * samples  # >= one float3 read-modify-write of the accumulator per sample
+    else:
+        kernel, launches = "extend_kernel (closest-hit BVH traversal)", float(np.mean([s["iterations"] for s in stats]))
+        k_ms = float(np.mean([s["ms_extend"] for s in stats]))
+        extra = 0.0
+    total_bytes = bytes_ray * rays + extra
+    gbs = total_bytes / (k_ms * 1e-3) / 1e9
+    t_l2 = total_bytes / (mp["l2_gbs"] * 1e9)
     t_alu = f32_ray * rays / (mp["fp32_tflops"] * 1e12) + f64_ray * rays / (mp["fp64_tflops"] * 1e12)
-    return {"kernel": "extend_kernel (closest_hit BVH traversal)", "bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
-            "frac": gbs / hbm_peak, "peak_source": src, "traffic": None,
+    traffic = None
+    tf = ROOT / "profiles" / "traffic.json"  # dram bytes per launch from the committed ncu --set full capture of this kernel
+    if tf.exists():
+        traffic = json.loads(tf.read_text()).get(f"{pipeline}:{cfg['scene'][0]}")
+    return {"kernel": kernel, "bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
+            "frac": gbs / hbm_peak, "peak_source": src, "traffic": traffic,
             "note": "scene (<=10 MB) is L2-resident: HBM is not the binding roof; binding model below",
-            "binding": {"bound": "l2" if t_l2 > t_alu else "fp32+fp64 issue", "model_ms": 1e3 * max(t_l2, t_alu), "measured_ms": ext_ms,
-                        "frac": 1e3 * max(t_l2, t_alu) / ext_ms, "l2_ms": 1e3 * t_l2, "alu_ms": 1e3 * t_alu,
+            "binding": {"bound": "l2" if t_l2 > t_alu else "fp32+fp64 issue", "model_ms": 1e3 * max(t_l2, t_alu), "measured_ms": k_ms,
+                        "frac": 1e3 * max(t_l2, t_alu) / k_ms, "l2_ms": 1e3 * t_l2, "alu_ms": 1e3 * t_alu,
                         "measured_peaks": mp},
             "per_ray": {**per_ray, "bytes": bytes_ray, "fp32_flops": f32_ray, "fp64_flops": f64_ray},
-            "rays_per_step": rays, "extend_launches_per_step": launches, "extend_ms_per_step": ext_ms,
-            "avg_launch_ms": ext_ms / max(launches, 1)}
+            "rays_per_step": rays, "launches_per_step": launches, "kernel_ms_per_step": k_ms,
+            "avg_launch_ms": k_ms / max(launches, 1), "algorithmic_bytes_per_launch": total_bytes / max(launches, 1)}
 
 
 if __name__ == "__main__":

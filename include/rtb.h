@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define RTB_ABI_VERSION 1
+#define RTB_ABI_VERSION 2
 
 /* ---- status codes ------------------------------------------------------ */
 enum {
@@ -189,9 +189,12 @@ typedef struct RtbRenderParams {
   uint32_t pool_size; /* live paths in flight per wavefront, 0 = default */
   uint32_t flags;     /* RTB_RENDER_* */
 } RtbRenderParams;
-#define RTB_RENDER_NO_SMEM_TOP 1u  /* do not stage the top BVH levels in shared memory */
+#define RTB_RENDER_SMEM_TOP 1u     /* stage the BFS-ordered top of the BVH in shared memory (off by default: measured slower than L1 on B200) */
 #define RTB_RENDER_KEEP_ACCUM 2u   /* add into the accumulator instead of zeroing it first */
-#define RTB_RENDER_SERIAL 4u       /* one wavefront, each kernel timed alone (fills RtbStats.ms_generate/extend/shade) */
+#define RTB_RENDER_SERIAL 4u       /* wavefront mode with one wavefront, each kernel timed alone (fills RtbStats.ms_generate/extend/shade) */
+#define RTB_RENDER_WAVEFRONT 8u    /* generate / extend / shade+compact kernels over path queues instead of the default persistent path kernel
+                                      (generate + traverse + shade per lane, no queues; measured 13-53 % faster) */
+#define RTB_RENDER_NO_DRAIN 16u    /* wavefront mode: do not hand the last few live paths to the path kernel */
 
 typedef struct RtbStats {
   uint64_t samples;     /* camera samples started                      */
@@ -206,6 +209,8 @@ typedef struct RtbStats {
   float ms_generate;    /* per-kernel sums: only with RTB_RENDER_SERIAL (0 otherwise: wavefronts overlap) */
   float ms_extend;
   float ms_shade;
+  float ms_drain;       /* path kernel finishing the last live paths of each wavefront (RTB_RENDER_SERIAL) */
+  uint32_t drain_paths; /* paths handed to it */
 } RtbStats;
 
 typedef struct RtbScene RtbScene; /* opaque; owns all device memory of one scene on one GPU */

@@ -132,3 +132,26 @@ def test_mode_b_renders_and_is_unbiased_on_diffuse_scene(rt, scenes, golden_dir)
     a, _ = ds.render(cam, spp=GPU_SPP, max_depth=50, mode=rt.MODE_A)
     assert abs(mu.mean() - (a / GPU_SPP).mean()) < 0.01
     assert st["rays"] > st["samples"]
+
+
+@pytest.mark.parametrize("name", list(SCENES))
+@pytest.mark.parametrize("mode", ["A", "B"])
+def test_wavefront_and_path_kernel_render_the_same_paths(rt, golden_dir, scenes, name, mode):
+    """The default persistent path kernel and the wavefront pipeline (RTB_RENDER_WAVEFRONT: generate /
+    extend / shade+compact over queues, with and without the drain) follow the SAME paths - Philox keys
+    are (pixel, sample, bounce) - so ray counts are identical and images differ only by the order of the
+    float atomics."""
+    g = np.load(golden_dir / f"image_{name}.npz")
+    cfg, cam = golden_camera(rt, g)
+    m = rt.MODE_A if mode == "A" else rt.MODE_B
+    ds = scenes[name][1]
+    fused, sf = ds.render(cam, spp=32, max_depth=cfg.max_depth, mode=m)
+    wave, sw = ds.render(cam, spp=32, max_depth=cfg.max_depth, mode=m, flags=rt.RENDER_WAVEFRONT, pool_size=1 << 16)
+    nodrain, sn = ds.render(cam, spp=32, max_depth=cfg.max_depth, mode=m, flags=rt.RENDER_WAVEFRONT | rt.RENDER_NO_DRAIN, pool_size=1 << 16)
+    serial, ss = ds.render(cam, spp=32, max_depth=cfg.max_depth, mode=m, flags=rt.RENDER_SERIAL, pool_size=1 << 16)
+    assert sf["rays"] == sw["rays"] == sn["rays"] == ss["rays"] and sf["samples"] == sw["samples"] == cam.width * cam.height * 32
+    assert sf["launches"] < sw["launches"] < sn["launches"] and sw["drain_paths"] > 0 and sn["drain_paths"] == 0
+    scale = max(1.0, float(fused.max()))
+    for other in (wave, nodrain, serial):
+        assert np.abs(other - fused).max() <= 1e-5 * scale
+    assert ss["ms_extend"] > 0 and ss["ms_shade"] > 0

@@ -1,0 +1,42 @@
+"""Summarise an .ncu-rep: key raw metrics per launch + instruction share per source region.
+  python tools/ncu_summary.py gpurun_out/x.ncu-rep [--lines N]"""
+import csv, io, subprocess, sys, collections
+
+rep = sys.argv[1]
+top = int(sys.argv[sys.argv.index("--lines") + 1]) if "--lines" in sys.argv else 25
+KEYS = ["gpu__time_duration.sum", "launch__registers_per_thread", "launch__grid_size", "launch__block_size", "smsp__cycles_active.avg",
+        "sm__cycles_elapsed.max", "smsp__inst_executed.sum", "smsp__thread_inst_executed_per_inst_executed.ratio",
+        "smsp__issue_active.avg.pct_of_peak_sustained_active", "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "l1tex__t_sector_hit_rate.pct", "l1tex__t_sector_pipe_lsu_mem_global_op_ld_hit_rate.pct", "lts__t_sector_hit_rate.pct",
+        "dram__bytes_read.sum", "dram__bytes_write.sum", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
+        "l1tex__throughput.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio", "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio", "smsp__average_warp_latency_per_inst_issued.ratio",
+        "smsp__warps_eligible.avg.per_cycle_active", "smsp__sass_inst_executed_op_local_ld.sum", "smsp__sass_inst_executed_op_local_st.sum",
+        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum"]
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(io.StringIO(raw)))
+hdr, units, data = rows[0], rows[1], rows[2:]
+print("kernel:", [d[hdr.index("Kernel Name")][:60] for d in data])
+for k in KEYS:
+    if k in hdr:
+        i = hdr.index(k)
+        print(f"{k:90s} {units[i]:14s} " + " | ".join(d[i] for d in data))
+src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass", "--launch-count", "1"], capture_output=True, text=True).stdout
+cur, out = None, []
+for r in csv.reader(io.StringIO(src)):
+    if r and r[0] == "File Path":
+        cur = r[1].split("/")[-1]
+        continue
+    if len(r) < 10 or r[0] in ("Line No", "Function Name", ""):
+        continue
+    try:
+        out.append((cur, int(r[0]), r[1].strip()[:80], int(r[4]), int(r[7]), int(r[8])))
+    except ValueError:
+        pass
+ti, ts = sum(o[4] for o in out), sum(o[3] for o in out)
+print(f"\nsource lines: {ti/1e6:.1f} M warp instructions, {ts} samples (first launch)")
+for o in sorted(out, key=lambda o: -o[4])[:top]:
+    print(f"{o[0][:16]:16s}{o[1]:4d} inst {100*o[4]/ti:5.1f}% samp {100*o[3]/max(ts,1):5.1f}% lanes {o[5]/max(o[4],1):5.1f} | {o[2]}")
