@@ -233,7 +233,15 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
 #ifdef RTB_TOP_PAIRS  // tuning builds: size of the shared-memory prefix, overriding the flattener's
       dd.n_top_nodes = 2u * (uint32_t)(RTB_TOP_PAIRS);
 #endif
-      tree = rtbc::Compiler(dd).Run();
+      uint32_t leaf_max = 4;  // tuning knobs of the device tree (rtb_compile.h)
+      float cost[3];
+      const float* prim_cost = nullptr;
+      if (const char* e = std::getenv("RTB_LEAF_MAX")) leaf_max = (uint32_t)std::max(1, std::atoi(e));
+      if (const char* e = std::getenv("RTB_PRIM_COST")) {
+        cost[0] = cost[1] = cost[2] = (float)std::atof(e);
+        prim_cost = cost;
+      }
+      tree = rtbc::Compiler(dd, leaf_max, prim_cost).Run();
     } catch (const std::exception& e) {
       rtb_scene_destroy(s);
       return Fail(RTB_EINVAL, std::string("scene compile: ") + e.what());

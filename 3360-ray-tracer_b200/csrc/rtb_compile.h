@@ -74,7 +74,13 @@ struct Compiled {
 
 class Compiler {
  public:
-  explicit Compiler(const RtbSceneDesc& d) : d_(d) {}
+  // leaf_max: most primitives a device leaf may hold (1..32); prim_cost: cost of one sphere / triangle / rect test in
+  // pair steps (nullptr = the measured defaults: gpurun_out r1t sweep)
+  explicit Compiler(const RtbSceneDesc& d, uint32_t leaf_max = 4, const float* prim_cost = nullptr)
+      : d_(d), leaf_max_(std::min(std::max(leaf_max, 1u), kMaxLeafCount)) {
+    const float def[3] = {2.f, 8.f, 4.f};
+    for (int k = 0; k < 3; ++k) prim_cost_[k] = prim_cost ? prim_cost[k] : def[k];
+  }
 
   Compiled Run() {
     int root = FromNode(0, 0);
@@ -103,11 +109,13 @@ class Compiler {
 
   int NewLeaf(const Box& b, uint32_t type, uint32_t first, uint32_t count) {
     if (first + count > kMaxFirst) throw std::runtime_error("more than 2^24 primitives of one type");
-    if (count > kMaxLeafCount) {  // split long runs under tight halves
-      const uint32_t half = count / 2;
-      const int l = NewLeaf(RunBox(type, first, half), type, first, half);
-      const int r = NewLeaf(RunBox(type, first + half, count - half), type, first + half, count - half);
-      return NewInternal(l, r);
+    if (count > 1) {
+      // The reference stops at <= 4 primitives per leaf (bvh.h:204).  On the device a primitive test is an order of
+      // magnitude dearer per lane than a box test (it runs at a handful of active lanes, ncu profiles/r01_path_*),
+      // so leaves are split further wherever the surface-area heuristic with the device's costs says it pays.
+      std::vector<uint32_t> items(count);
+      for (uint32_t i = 0; i < count; ++i) items[i] = first + i;
+      return SplitRun(type, items, 0, items.size());
     }
     CNode n;
     n.box = b;
@@ -160,6 +168,90 @@ class Compiler {
     Box b = Box::Empty();
     for (uint32_t i = 0; i < count; ++i) b.Grow(PrimBox(type, first + i));
     return b;
+  }
+
+  // Tree over the primitives items[lo, hi) of one type, chosen by a surface-area heuristic with the DEVICE's
+  // costs: one pair step = 1, one primitive test = prim_cost_[type] (a primitive test runs at a handful of active lanes
+  // and is several times dearer per lane than a box test).  Small sets try every axis and split position; a set
+  // stays one leaf when no split is cheaper (e.g. large overlapping spheres).  Returns the expected cost.
+  static float Area(const Box& b) {
+    const float dx = std::max(b.hi[0] - b.lo[0], 0.f), dy = std::max(b.hi[1] - b.lo[1], 0.f), dz = std::max(b.hi[2] - b.lo[2], 0.f);
+    return 2.f * (dx * dy + dy * dz + dz * dx);
+  }
+  Box ItemsBox(uint32_t type, const std::vector<uint32_t>& items, size_t lo, size_t hi) const {
+    Box b = Box::Empty();
+    for (size_t i = lo; i < hi; ++i) b.Grow(PrimBox(type, items[i]));
+    return b;
+  }
+  int SplitRun(uint32_t type, std::vector<uint32_t>& items, size_t lo, size_t hi, float* cost_out = nullptr) {
+    const size_t n = hi - lo;
+    std::sort(items.begin() + lo, items.begin() + hi);
+    bool consecutive = true;
+    for (size_t i = lo + 1; i < hi; ++i) consecutive = consecutive && items[i] == items[i - 1] + 1;
+    const Box box = ItemsBox(type, items, lo, hi);
+    const bool may_leaf = n <= leaf_max_ && consecutive;
+    const float leaf_cost = prim_cost_[type] * static_cast<float>(n);
+    auto make_leaf = [&]() {
+      CNode c;
+      c.box = box;
+      c.desc = LeafDesc(type, items[lo], static_cast<uint32_t>(n));
+      nodes_.push_back(c);
+      if (cost_out) *cost_out = leaf_cost;
+      return static_cast<int>(nodes_.size()) - 1;
+    };
+    if (n == 1) return make_leaf();
+    auto centroid = [&](uint32_t idx, int k) {
+      const Box b = PrimBox(type, idx);
+      return 0.5f * (b.lo[k] + b.hi[k]);
+    };
+    // candidate split: (axis, position) minimising area_L * n_L + area_R * n_R; all of them for small sets,
+    // the median of the widest axis for large ones
+    int best_axis = 0;
+    size_t best_mid = lo + n / 2;
+    if (n <= 16) {
+      float best = INFINITY;
+      std::vector<uint32_t> tmp(items.begin() + lo, items.begin() + hi);
+      for (int axis = 0; axis < 3; ++axis) {
+        std::sort(tmp.begin(), tmp.end(), [&](uint32_t a, uint32_t b) {
+          const float ca = centroid(a, axis), cb = centroid(b, axis);
+          return ca < cb || (ca == cb && a < b);
+        });
+        for (size_t k = 1; k < n; ++k) {
+          const float c = Area(ItemsBox(type, tmp, 0, k)) * static_cast<float>(k) + Area(ItemsBox(type, tmp, k, n)) * static_cast<float>(n - k);
+          if (c < best) {
+            best = c;
+            best_axis = axis;
+            best_mid = lo + k;
+          }
+        }
+      }
+    } else {
+      float cmin[3] = {INFINITY, INFINITY, INFINITY}, cmax[3] = {-INFINITY, -INFINITY, -INFINITY};
+      for (size_t i = lo; i < hi; ++i)
+        for (int k = 0; k < 3; ++k) {
+          const float c = centroid(items[i], k);
+          cmin[k] = std::min(cmin[k], c);
+          cmax[k] = std::max(cmax[k], c);
+        }
+      for (int k = 1; k < 3; ++k)
+        if (cmax[k] - cmin[k] > cmax[best_axis] - cmin[best_axis]) best_axis = k;
+    }
+    std::sort(items.begin() + lo, items.begin() + hi, [&](uint32_t a, uint32_t b) {
+      const float ca = centroid(a, best_axis), cb = centroid(b, best_axis);
+      return ca < cb || (ca == cb && a < b);
+    });
+    const size_t mark = nodes_.size();
+    float cl = 0.f, cr = 0.f;
+    const int l = SplitRun(type, items, lo, best_mid, &cl), r = SplitRun(type, items, best_mid, hi, &cr);
+    const float a = std::max(Area(box), 1e-30f);
+    const float split_cost = 1.f + (Area(nodes_[l].box) * cl + Area(nodes_[r].box) * cr) / a;
+    if (may_leaf && leaf_cost <= split_cost) {
+      nodes_.resize(mark);  // drop the trial subtree
+      std::sort(items.begin() + lo, items.begin() + hi);
+      return make_leaf();
+    }
+    if (cost_out) *cost_out = split_cost;
+    return NewInternal(l, r);
   }
 
   // Balanced tree over a short list of already-built children.
@@ -270,6 +362,8 @@ class Compiler {
   }
 
   const RtbSceneDesc& d_;
+  uint32_t leaf_max_;
+  float prim_cost_[3];
   std::vector<CNode> nodes_;
   struct IntMap {  // CNode index -> pair index (dense)
     std::vector<uint32_t> v;
