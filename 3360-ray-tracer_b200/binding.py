@@ -47,7 +47,7 @@ class RtbSceneDesc(C.Structure):
         ("n_materials", C.c_uint32), ("materials", C.c_void_p),
         ("n_textures", C.c_uint32), ("textures", C.c_void_p),
         ("n_images", C.c_uint32), ("images", C.c_void_p),
-        ("n_top_nodes", C.c_uint32), ("max_depth", C.c_uint32),
+        ("n_top_nodes", C.c_uint32), ("max_depth", C.c_uint32), ("compiled", C.c_void_p),
     ]
 
 
@@ -99,7 +99,7 @@ assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 16
 
 # Every symbol include/rtb.h and include/rth.h declare (checked by tests/test_abi.py).
 RTB_SYMBOLS = [
-    "rtb_last_error", "rtb_abi_version", "rtb_device_count", "rtb_init", "rtb_shutdown", "rtb_scene_create",
+    "rtb_last_error", "rtb_abi_version", "rtb_tree_compile", "rtb_tree_destroy", "rtb_device_count", "rtb_init", "rtb_shutdown", "rtb_scene_create",
     "rtb_scene_destroy", "rtb_intersect_batch", "rtb_intersect_batch_device", "rtb_render", "rtb_render_device",
     "rtb_resolve_device", "rtb_resolve", "rtb_measure_l2_gbs", "rtb_measure_fp32_tflops", "rtb_measure_fp64_tflops",
 ]

@@ -98,6 +98,35 @@ void FreeFused(RenderCtx* s) {
 // shared memory of the traversal kernels besides the staged top of the tree: the stack columns
 constexpr size_t kStackSmem = (size_t)rtb::kSmemStack * rtb::kTraceBlock * sizeof(uint32_t);
 
+struct RtbCompiledTree {
+  rtbc::Compiled tree;
+};
+
+static int CompileTree(const RtbSceneDesc& d, rtbc::Compiled* out) {
+  try {
+    RtbSceneDesc dd = d;
+#ifdef RTB_TOP_PAIRS  // tuning builds: size of the shared-memory prefix, overriding the flattener's
+    dd.n_top_nodes = 2u * (uint32_t)(RTB_TOP_PAIRS);
+#endif
+    uint32_t leaf_max = 4;  // tuning knobs of the device tree (rtb_compile.h)
+    float cost[3];
+    const float* prim_cost = nullptr;
+    if (const char* e = std::getenv("RTB_LEAF_MAX")) leaf_max = (uint32_t)std::max(1, std::atoi(e));
+    if (const char* e = std::getenv("RTB_PRIM_COST")) {
+      cost[0] = cost[1] = cost[2] = (float)std::atof(e);
+      prim_cost = cost;
+    }
+    *out = rtbc::Compiler(dd, leaf_max, prim_cost).Run();
+  } catch (const std::exception& e) {
+    return Fail(RTB_EINVAL, std::string("scene compile: ") + e.what());
+  }
+  if (out->pairs.size() >= (1u << 29)) return Fail(RTB_EINVAL, "more than 2^29 BVH pairs");
+  if (out->depth + 2 > (uint32_t)rtb::kStackSize) return Fail(RTB_EINVAL, "BVH deeper than the 64-entry traversal stack (bvh.h:80)");
+  return RTB_OK;
+}
+
+static int ValidateDesc(const RtbSceneDesc* d);
+
 struct RtbScene {
   rtb::DevScene dev{};
   std::vector<void*> allocs;
@@ -123,6 +152,22 @@ extern "C" {
 
 const char* rtb_last_error(void) { return g_error.c_str(); }
 int rtb_abi_version(void) { return RTB_ABI_VERSION; }
+
+int rtb_tree_compile(const RtbSceneDesc* d, RtbCompiledTree** out) {
+  if (!d || !out) return Fail(RTB_EINVAL, "null argument");
+  *out = nullptr;
+  int rc = ValidateDesc(d);
+  if (rc != RTB_OK) return rc;
+  RtbCompiledTree* t = new RtbCompiledTree();
+  rc = CompileTree(*d, &t->tree);
+  if (rc != RTB_OK) {
+    delete t;
+    return rc;
+  }
+  *out = t;
+  return RTB_OK;
+}
+void rtb_tree_destroy(RtbCompiledTree* t) { delete t; }
 
 int rtb_device_count(void) {
   int n = 0;
@@ -178,41 +223,9 @@ int rtb_scene_destroy(RtbScene* s) {
 int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
   if (!d || !out) return Fail(RTB_EINVAL, "null argument");
   *out = nullptr;
-  if (d->abi_version != RTB_ABI_VERSION) return Fail(RTB_EINVAL, "RtbSceneDesc.abi_version mismatch");
-  if (d->n_nodes < 2 || (d->n_nodes & 1u) || !d->nodes) return Fail(RTB_EINVAL, "scene needs an even, non-zero node count");
-  if (d->n_prim_refs >= (1u << 25)) return Fail(RTB_EINVAL, "more than 2^25 leaf entries");
-  if (d->n_top_nodes > d->n_nodes || (d->n_top_nodes & 1u)) return Fail(RTB_EINVAL, "bad n_top_nodes");
-  // structural validation: every index the kernels will follow must be in range
-  for (uint32_t i = 0; i < d->n_nodes; ++i) {
-    const RtbNode& n = d->nodes[i];
-    if (n.b == 0) {
-      if (!(n.lo[0] <= n.hi[0])) continue;  // padding slot (inverted box), never entered
-      if (n.a + 1 >= d->n_nodes || (n.a & 1u) || n.a == 0) return Fail(RTB_EINVAL, "node child index out of range");
-    } else if (n.b > RTB_MAX_LEAF || (uint64_t)n.a + n.b > d->n_prim_refs) {
-      return Fail(RTB_EINVAL, "leaf range out of bounds");
-    }
-  }
-  for (uint32_t i = 0; i < d->n_prim_refs; ++i) {
-    const uint32_t ty = RTB_REF_TYPE(d->prim_refs[i]), idx = RTB_REF_INDEX(d->prim_refs[i]);
-    const uint32_t lim = ty == RTB_PRIM_SPHERE ? d->n_spheres : ty == RTB_PRIM_TRIANGLE ? d->n_triangles : ty == RTB_PRIM_RECT ? d->n_rects : d->n_nodes;
-    if (idx >= lim || (ty == RTB_PRIM_SUBTREE && (idx & 1u))) return Fail(RTB_EINVAL, "leaf entry out of range");
-  }
-  auto mat_ok = [&](uint32_t m) { return m < d->n_materials; };
-  for (uint32_t i = 0; i < d->n_spheres; ++i) if (!mat_ok(d->sphere_mat[i])) return Fail(RTB_EINVAL, "sphere material out of range");
-  for (uint32_t i = 0; i < d->n_triangles; ++i) if (!mat_ok(d->triangles[i].mat)) return Fail(RTB_EINVAL, "triangle material out of range");
-  for (uint32_t i = 0; i < d->n_rects; ++i) if (!mat_ok(d->rects[i].mat) || d->rects[i].axis < 0 || d->rects[i].axis > 2) return Fail(RTB_EINVAL, "bad rect");
-  for (uint32_t i = 0; i < d->n_materials; ++i) {
-    const RtbMaterial& m = d->materials[i];
-    if ((m.type == RTB_MAT_LAMBERTIAN || m.type == RTB_MAT_DIFFUSE_LIGHT) && (m.tex < 0 || (uint32_t)m.tex >= d->n_textures))
-      return Fail(RTB_EINVAL, "material texture out of range");
-  }
-  for (uint32_t i = 0; i < d->n_textures; ++i) {
-    const RtbTexture& t = d->textures[i];
-    if (t.type == RTB_TEX_CHECKER && (t.even < 0 || t.odd < 0 || (uint32_t)t.even >= d->n_textures || (uint32_t)t.odd >= d->n_textures))
-      return Fail(RTB_EINVAL, "checker child out of range");
-    if (t.type == RTB_TEX_IMAGE && (t.image < 0 || (uint32_t)t.image >= d->n_images)) return Fail(RTB_EINVAL, "image out of range");
-  }
-  int rc = EnsureInit();
+  int rc = ValidateDesc(d);
+  if (rc != RTB_OK) return rc;
+  rc = EnsureInit();
   if (rc != RTB_OK) return rc;
 
   RtbScene* s = new RtbScene();
@@ -226,37 +239,19 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
       return rc;             \
     }                        \
   } while (0)
-  {  // interchange tree -> device-native sibling pairs (rtb_compile.h)
-    rtbc::Compiled tree;
-    try {
-      RtbSceneDesc dd = *d;
-#ifdef RTB_TOP_PAIRS  // tuning builds: size of the shared-memory prefix, overriding the flattener's
-      dd.n_top_nodes = 2u * (uint32_t)(RTB_TOP_PAIRS);
-#endif
-      uint32_t leaf_max = 4;  // tuning knobs of the device tree (rtb_compile.h)
-      float cost[3];
-      const float* prim_cost = nullptr;
-      if (const char* e = std::getenv("RTB_LEAF_MAX")) leaf_max = (uint32_t)std::max(1, std::atoi(e));
-      if (const char* e = std::getenv("RTB_PRIM_COST")) {
-        cost[0] = cost[1] = cost[2] = (float)std::atof(e);
-        prim_cost = cost;
+  {  // interchange tree -> device-native sibling pairs (rtb_compile.h), unless the caller already did it
+    rtbc::Compiled local;
+    const rtbc::Compiled* tree = d->compiled ? &d->compiled->tree : &local;
+    if (!d->compiled) {
+      rc = CompileTree(*d, &local);
+      if (rc != RTB_OK) {
+        rtb_scene_destroy(s);
+        return rc;
       }
-      tree = rtbc::Compiler(dd, leaf_max, prim_cost).Run();
-    } catch (const std::exception& e) {
-      rtb_scene_destroy(s);
-      return Fail(RTB_EINVAL, std::string("scene compile: ") + e.what());
     }
-    if (tree.pairs.size() >= (1u << 29)) {
-      rtb_scene_destroy(s);
-      return Fail(RTB_EINVAL, "more than 2^29 BVH pairs");
-    }
-    if (tree.depth + 2 > (uint32_t)rtb::kStackSize) {
-      rtb_scene_destroy(s);
-      return Fail(RTB_EINVAL, "BVH deeper than the 64-entry traversal stack (bvh.h:80)");
-    }
-    PUT(s->Put(reinterpret_cast<const float4*>(tree.pairs.data()), 4 * tree.pairs.size(), &v.pairs));
-    v.n_pairs = (uint32_t)tree.pairs.size();
-    v.n_top_pairs = tree.top_pairs;
+    PUT(s->Put(reinterpret_cast<const float4*>(tree->pairs.data()), 4 * tree->pairs.size(), &v.pairs));
+    v.n_pairs = (uint32_t)tree->pairs.size();
+    v.n_top_pairs = tree->top_pairs;
   }
   PUT(s->Put(reinterpret_cast<const double2*>(d->spheres), 2 * (size_t)d->n_spheres, &v.spheres));
   PUT(s->Put(reinterpret_cast<const double2*>(d->triangles), 5 * (size_t)d->n_triangles, &v.triangles));
@@ -376,6 +371,44 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
 }
 
 }  // extern "C"
+
+// structural validation: every index the kernels will follow must be in range
+static int ValidateDesc(const RtbSceneDesc* d) {
+  if (d->abi_version != RTB_ABI_VERSION) return Fail(RTB_EINVAL, "RtbSceneDesc.abi_version mismatch");
+  if (d->n_nodes < 2 || (d->n_nodes & 1u) || !d->nodes) return Fail(RTB_EINVAL, "scene needs an even, non-zero node count");
+  if (d->n_prim_refs >= (1u << 25)) return Fail(RTB_EINVAL, "more than 2^25 leaf entries");
+  if (d->n_top_nodes > d->n_nodes || (d->n_top_nodes & 1u)) return Fail(RTB_EINVAL, "bad n_top_nodes");
+  for (uint32_t i = 0; i < d->n_nodes; ++i) {
+    const RtbNode& n = d->nodes[i];
+    if (n.b == 0) {
+      if (!(n.lo[0] <= n.hi[0])) continue;  // padding slot (inverted box), never entered
+      if (n.a + 1 >= d->n_nodes || (n.a & 1u) || n.a == 0) return Fail(RTB_EINVAL, "node child index out of range");
+    } else if (n.b > RTB_MAX_LEAF || (uint64_t)n.a + n.b > d->n_prim_refs) {
+      return Fail(RTB_EINVAL, "leaf range out of bounds");
+    }
+  }
+  for (uint32_t i = 0; i < d->n_prim_refs; ++i) {
+    const uint32_t ty = RTB_REF_TYPE(d->prim_refs[i]), idx = RTB_REF_INDEX(d->prim_refs[i]);
+    const uint32_t lim = ty == RTB_PRIM_SPHERE ? d->n_spheres : ty == RTB_PRIM_TRIANGLE ? d->n_triangles : ty == RTB_PRIM_RECT ? d->n_rects : d->n_nodes;
+    if (idx >= lim || (ty == RTB_PRIM_SUBTREE && (idx & 1u))) return Fail(RTB_EINVAL, "leaf entry out of range");
+  }
+  auto mat_ok = [&](uint32_t m) { return m < d->n_materials; };
+  for (uint32_t i = 0; i < d->n_spheres; ++i) if (!mat_ok(d->sphere_mat[i])) return Fail(RTB_EINVAL, "sphere material out of range");
+  for (uint32_t i = 0; i < d->n_triangles; ++i) if (!mat_ok(d->triangles[i].mat)) return Fail(RTB_EINVAL, "triangle material out of range");
+  for (uint32_t i = 0; i < d->n_rects; ++i) if (!mat_ok(d->rects[i].mat) || d->rects[i].axis < 0 || d->rects[i].axis > 2) return Fail(RTB_EINVAL, "bad rect");
+  for (uint32_t i = 0; i < d->n_materials; ++i) {
+    const RtbMaterial& m = d->materials[i];
+    if ((m.type == RTB_MAT_LAMBERTIAN || m.type == RTB_MAT_DIFFUSE_LIGHT) && (m.tex < 0 || (uint32_t)m.tex >= d->n_textures))
+      return Fail(RTB_EINVAL, "material texture out of range");
+  }
+  for (uint32_t i = 0; i < d->n_textures; ++i) {
+    const RtbTexture& t = d->textures[i];
+    if (t.type == RTB_TEX_CHECKER && (t.even < 0 || t.odd < 0 || (uint32_t)t.even >= d->n_textures || (uint32_t)t.odd >= d->n_textures))
+      return Fail(RTB_EINVAL, "checker child out of range");
+    if (t.type == RTB_TEX_IMAGE && (t.image < 0 || (uint32_t)t.image >= d->n_images)) return Fail(RTB_EINVAL, "image out of range");
+  }
+  return RTB_OK;
+}
 
 // Traversal CTAs are large so that one shared-memory copy of the top of the tree serves many warps
 // and most of the 228 KB stays L1 for the rest of the tree.

@@ -47,14 +47,25 @@ struct Box {
   static Box Empty() { return Box{{INFINITY, INFINITY, INFINITY}, {-INFINITY, -INFINITY, -INFINITY}}; }
 };
 
+// one float towards -inf / +inf (finite, non-NaN input; bit arithmetic instead of nextafterf: this runs per primitive)
+inline float StepDown(float f) {
+  uint32_t u;
+  std::memcpy(&u, &f, 4);
+  if (f > 0.f) --u;
+  else if (f < 0.f) ++u;
+  else u = 0x80000001u;  // below +-0: the smallest negative denormal
+  std::memcpy(&f, &u, 4);
+  return f;
+}
+inline float StepUp(float f) { return -StepDown(-f); }
 inline float Down(double v) {
   float f = static_cast<float>(v);
-  if (static_cast<double>(f) > v) f = std::nextafterf(f, -INFINITY);
+  if (static_cast<double>(f) > v && std::isfinite(f)) f = StepDown(f);
   return f;
 }
 inline float Up(double v) {
   float f = static_cast<float>(v);
-  if (static_cast<double>(f) < v) f = std::nextafterf(f, INFINITY);
+  if (static_cast<double>(f) < v && std::isfinite(f)) f = StepUp(f);
   return f;
 }
 
@@ -113,9 +124,7 @@ class Compiler {
       // The reference stops at <= 4 primitives per leaf (bvh.h:204).  On the device a primitive test is an order of
       // magnitude dearer per lane than a box test (it runs at a handful of active lanes, ncu profiles/r01_path_*),
       // so leaves are split further wherever the surface-area heuristic with the device's costs says it pays.
-      std::vector<uint32_t> items(count);
-      for (uint32_t i = 0; i < count; ++i) items[i] = first + i;
-      return SplitRun(type, items, 0, items.size());
+      return SplitRun(type, first, count);
     }
     CNode n;
     n.box = b;
@@ -178,46 +187,76 @@ class Compiler {
     const float dx = std::max(b.hi[0] - b.lo[0], 0.f), dy = std::max(b.hi[1] - b.lo[1], 0.f), dz = std::max(b.hi[2] - b.lo[2], 0.f);
     return 2.f * (dx * dy + dy * dz + dz * dx);
   }
-  Box ItemsBox(uint32_t type, const std::vector<uint32_t>& items, size_t lo, size_t hi) const {
+  struct Item {  // one primitive of a run being split: its index in the type's table, box and centroid
+    uint32_t idx;
+    Box box;
+    float c[3];
+  };
+  static Box ItemsBox(const Item* it, size_t lo, size_t hi) {
     Box b = Box::Empty();
-    for (size_t i = lo; i < hi; ++i) b.Grow(PrimBox(type, items[i]));
+    for (size_t i = lo; i < hi; ++i) b.Grow(it[i].box);
     return b;
   }
-  int SplitRun(uint32_t type, std::vector<uint32_t>& items, size_t lo, size_t hi, float* cost_out = nullptr) {
+  template <class Less>
+  static void SmallSort(Item* it, size_t lo, size_t hi, Less less) {  // insertion sort: runs are short (<= 4 almost always)
+    if (hi - lo > 32) {
+      std::sort(it + lo, it + hi, less);
+      return;
+    }
+    for (size_t i = lo + 1; i < hi; ++i) {
+      Item v = it[i];
+      size_t k = i;
+      for (; k > lo && less(v, it[k - 1]); --k) it[k] = it[k - 1];
+      it[k] = v;
+    }
+  }
+  int SplitRun(uint32_t type, uint32_t first, uint32_t count) {
+    Item small[kMaxLeafCount];
+    std::vector<Item> big;
+    Item* items = small;
+    if (count > kMaxLeafCount) {
+      big.resize(count);
+      items = big.data();
+    }
+    for (uint32_t i = 0; i < count; ++i) {
+      Item& t = items[i];
+      t.idx = first + i;
+      t.box = PrimBox(type, t.idx);
+      for (int k = 0; k < 3; ++k) t.c[k] = 0.5f * (t.box.lo[k] + t.box.hi[k]);
+    }
+    return SplitItems(type, items, 0, count, nullptr);
+  }
+  int SplitItems(uint32_t type, Item* items, size_t lo, size_t hi, float* cost_out) {
     const size_t n = hi - lo;
-    std::sort(items.begin() + lo, items.begin() + hi);
+    auto by_index = [](const Item& a, const Item& b) { return a.idx < b.idx; };
+    SmallSort(items, lo, hi, by_index);
     bool consecutive = true;
-    for (size_t i = lo + 1; i < hi; ++i) consecutive = consecutive && items[i] == items[i - 1] + 1;
-    const Box box = ItemsBox(type, items, lo, hi);
+    for (size_t i = lo + 1; i < hi; ++i) consecutive = consecutive && items[i].idx == items[i - 1].idx + 1;
+    const Box box = ItemsBox(items, lo, hi);
     const bool may_leaf = n <= leaf_max_ && consecutive;
     const float leaf_cost = prim_cost_[type] * static_cast<float>(n);
     auto make_leaf = [&]() {
       CNode c;
       c.box = box;
-      c.desc = LeafDesc(type, items[lo], static_cast<uint32_t>(n));
+      c.desc = LeafDesc(type, items[lo].idx, static_cast<uint32_t>(n));
       nodes_.push_back(c);
       if (cost_out) *cost_out = leaf_cost;
       return static_cast<int>(nodes_.size()) - 1;
     };
     if (n == 1) return make_leaf();
-    auto centroid = [&](uint32_t idx, int k) {
-      const Box b = PrimBox(type, idx);
-      return 0.5f * (b.lo[k] + b.hi[k]);
-    };
     // candidate split: (axis, position) minimising area_L * n_L + area_R * n_R; all of them for small sets,
     // the median of the widest axis for large ones
     int best_axis = 0;
     size_t best_mid = lo + n / 2;
+    auto by_axis = [](int axis) {
+      return [axis](const Item& a, const Item& b) { return a.c[axis] < b.c[axis] || (a.c[axis] == b.c[axis] && a.idx < b.idx); };
+    };
     if (n <= 16) {
       float best = INFINITY;
-      std::vector<uint32_t> tmp(items.begin() + lo, items.begin() + hi);
       for (int axis = 0; axis < 3; ++axis) {
-        std::sort(tmp.begin(), tmp.end(), [&](uint32_t a, uint32_t b) {
-          const float ca = centroid(a, axis), cb = centroid(b, axis);
-          return ca < cb || (ca == cb && a < b);
-        });
+        SmallSort(items, lo, hi, by_axis(axis));
         for (size_t k = 1; k < n; ++k) {
-          const float c = Area(ItemsBox(type, tmp, 0, k)) * static_cast<float>(k) + Area(ItemsBox(type, tmp, k, n)) * static_cast<float>(n - k);
+          const float c = Area(ItemsBox(items, lo, lo + k)) * static_cast<float>(k) + Area(ItemsBox(items, lo + k, hi)) * static_cast<float>(n - k);
           if (c < best) {
             best = c;
             best_axis = axis;
@@ -229,25 +268,21 @@ class Compiler {
       float cmin[3] = {INFINITY, INFINITY, INFINITY}, cmax[3] = {-INFINITY, -INFINITY, -INFINITY};
       for (size_t i = lo; i < hi; ++i)
         for (int k = 0; k < 3; ++k) {
-          const float c = centroid(items[i], k);
-          cmin[k] = std::min(cmin[k], c);
-          cmax[k] = std::max(cmax[k], c);
+          cmin[k] = std::min(cmin[k], items[i].c[k]);
+          cmax[k] = std::max(cmax[k], items[i].c[k]);
         }
       for (int k = 1; k < 3; ++k)
         if (cmax[k] - cmin[k] > cmax[best_axis] - cmin[best_axis]) best_axis = k;
     }
-    std::sort(items.begin() + lo, items.begin() + hi, [&](uint32_t a, uint32_t b) {
-      const float ca = centroid(a, best_axis), cb = centroid(b, best_axis);
-      return ca < cb || (ca == cb && a < b);
-    });
+    SmallSort(items, lo, hi, by_axis(best_axis));
     const size_t mark = nodes_.size();
     float cl = 0.f, cr = 0.f;
-    const int l = SplitRun(type, items, lo, best_mid, &cl), r = SplitRun(type, items, best_mid, hi, &cr);
+    const int l = SplitItems(type, items, lo, best_mid, &cl), r = SplitItems(type, items, best_mid, hi, &cr);
     const float a = std::max(Area(box), 1e-30f);
     const float split_cost = 1.f + (Area(nodes_[l].box) * cl + Area(nodes_[r].box) * cr) / a;
     if (may_leaf && leaf_cost <= split_cost) {
       nodes_.resize(mark);  // drop the trial subtree
-      std::sort(items.begin() + lo, items.begin() + hi);
+      SmallSort(items, lo, hi, by_index);
       return make_leaf();
     }
     if (cost_out) *cost_out = split_cost;

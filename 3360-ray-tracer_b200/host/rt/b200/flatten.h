@@ -89,6 +89,7 @@ struct FlatScene {
     d.images = images.data();
     d.n_top_nodes = n_top_nodes;
     d.max_depth = max_depth;
+    d.compiled = nullptr;  // rtb_tree_compile's result, set by whoever owns it (rth_capi.cc, B200Renderer)
     return d;
   }
 };

@@ -18,7 +18,9 @@ struct RthScene {
   b200::BuiltScene built;
   b200::FlatScene flat;
   RtbSceneDesc desc;
+  RtbCompiledTree* tree = nullptr;  // device-native traversal tree, built once with the scene (host work)
   std::string image_paths;  // '\n'-joined
+  ~RthScene() { rtb_tree_destroy(tree); }
 };
 
 namespace {
@@ -32,6 +34,8 @@ double Param(const double* p, int n, int i, double dflt) { return (p && i < n) ?
 void Finish(RthScene& s, uint32_t top_budget) {
   s.flat = b200::Flattener(top_budget).Run(s.built.world);
   s.desc = s.flat.desc();
+  if (rtb_tree_compile(&s.desc, &s.tree) != RTB_OK) throw std::runtime_error(rtb_last_error());
+  s.desc.compiled = s.tree;
   s.image_paths.clear();
   for (const auto& p : s.flat.image_paths) {
     if (!s.image_paths.empty()) s.image_paths += '\n';

@@ -148,7 +148,12 @@ typedef struct RtbSceneDesc {
   const RtbImage* images;
   uint32_t n_top_nodes; /* nodes[0..n_top_nodes) are the BFS-ordered top levels (shared-memory stage) */
   uint32_t max_depth;   /* deepest root-to-leaf path, for the traversal stack bound */
+  /* optional: the device-native traversal tree built ahead of time with rtb_tree_compile() - host work that belongs
+   * to scene construction, like the reference's Bvh constructor (bvh.h:39-68), not to the render call.  NULL:
+   * rtb_scene_create builds it itself. */
+  const struct RtbCompiledTree* compiled;
 } RtbSceneDesc;
+typedef struct RtbCompiledTree RtbCompiledTree; /* opaque, host memory only */
 
 /* ---- rays and hits (seam 2) -------------------------------------------- */
 /* core::Ray (src/core/ray.h:7-26) + the core::Interval passed to Hit.
@@ -222,6 +227,10 @@ int rtb_device_count(void);
 /* Bind the calling thread to `device` and create the library's stream on it. */
 int rtb_init(int device);
 int rtb_shutdown(void);
+
+/* Host only (works without a GPU): interchange nodes -> the sibling-pair tree the kernels walk. */
+int rtb_tree_compile(const RtbSceneDesc* desc, RtbCompiledTree** out);
+void rtb_tree_destroy(RtbCompiledTree* tree);
 
 int rtb_scene_create(const RtbSceneDesc* desc, RtbScene** out);
 int rtb_scene_destroy(RtbScene* scene);
