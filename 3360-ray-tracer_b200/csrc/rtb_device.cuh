@@ -83,9 +83,12 @@ __device__ __forceinline__ float u01(uint32_t x) { return (x >> 8) * (1.0f / 167
 struct TravRay {
   float ox, oy, oz, dx, dy, dz;
   float tmin, tmax;
-  // FP32 slab constants: t_plane = fma(plane, inv, b) with b = -o*inv; eabs bounds the absolute
-  // error of that form (|o*inv| * few ulp), the relative part is applied in slab_pair()
-  float ix, iy, iz, bx, by, bz, eabs;
+  // FP32 slab constants: t_plane = fma(plane, inv, b) with b = -o*inv.  The only ABSOLUTE error of that form is
+  // the rounding of b (<= u |o*inv|; it can be large: |o| ~ 500 and |d_k| ~ 1e-3 give ~0.03 in t), so each axis
+  // carries two copies of b, pushed outward by its own bound: bl* is added to the box's lo plane, bh* to its hi
+  // plane, ordered by the sign of inv so that min() lands on (near - e) and max() on (far + e).  An axis with a
+  // tiny direction component therefore loosens only its own slab, never the other two.
+  float ix, iy, iz, blx, bly, blz, bhx, bhy, bhz;
 };
 // max |d_i|: the filters' error bounds scale with it (one FMNMX3, cheaper than a live register)
 __device__ __forceinline__ float ray_dmax(const TravRay& r) { return fmaxf(fabsf(r.dx), fmaxf(fabsf(r.dy), fabsf(r.dz))); }
@@ -95,31 +98,36 @@ __device__ __forceinline__ float safe_dir(float d) {
   return fabsf(d) < 1e-20f ? copysignf(1e-20f, d) : d;
 }
 
+__device__ __forceinline__ void slab_axis(float o, float d, float& inv, float& bl, float& bh) {
+  inv = __frcp_rn(safe_dir(d));
+  // computed t = fma(p, inv, b), b = fl(-o*inv):  t_true = t (1 +- 2u) +- u |o*inv|.  4u covers b's rounding and
+  // the rounding of the two sums below; the relative part is applied in slab().
+  const float oi = o * inv, e = (4.0f * kU) * fabsf(oi);
+  const float near_b = -oi - e, far_b = -oi + e;
+  bl = inv >= 0.0f ? near_b : far_b;
+  bh = inv >= 0.0f ? far_b : near_b;
+}
+
 __device__ __forceinline__ void prepare_ray(TravRay& r, float4 o, float4 d) {
   r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tmin = o.w;
   r.dx = d.x; r.dy = d.y; r.dz = d.z; r.tmax = d.w;
-  r.ix = __frcp_rn(safe_dir(d.x));
-  r.iy = __frcp_rn(safe_dir(d.y));
-  r.iz = __frcp_rn(safe_dir(d.z));
-  // computed t = fma(p, inv, -o*inv): |error| <= ~2^-23 (|o*inv| + |t|)
-  const float ox = o.x * r.ix, oy = o.y * r.iy, oz = o.z * r.iz;
-  r.bx = -ox; r.by = -oy; r.bz = -oz;
-  // absolute slack of the comparison tn <= tf: twice the |o*inv| rounding term, plus the relative
-  // term of a negative tmin (tn, tf >= 0 otherwise, where the (1 + 2^-18) factor in slab() covers it)
-  r.eabs = 16.0f * kU * fmaxf(fabsf(ox), fmaxf(fabsf(oy), fabsf(oz))) + (o.w < 0.0f ? -1.6e-5f * o.w : 0.0f);
+  slab_axis(o.x, d.x, r.ix, r.blx, r.bhx);
+  slab_axis(o.y, d.y, r.iy, r.bly, r.bhy);
+  slab_axis(o.z, d.z, r.iz, r.blz, r.bhz);
 }
 
 // Conservative slab test of one box against [tmin, thi].  Returns the entry distance in tn.
-// Computed plane distances carry <= 2^-22 relative + eabs/2 absolute error; the test widens the
-// far side by 2^-18 relative + eabs, so a box the exact test enters is never culled.
+// Per axis min() is a lower bound of the true entry and max() an upper bound of the true exit up to 2^-22
+// relative; the comparison widens the exit by 2^-18 relative, so a box the exact (double) test of the reference
+// enters is never culled.
 __device__ __forceinline__ bool slab(const TravRay& r, float4 lo, float4 hi, float thi, float& tn) {
-  const float ax = fmaf(lo.x, r.ix, r.bx), bx = fmaf(hi.x, r.ix, r.bx);
-  const float ay = fmaf(lo.y, r.iy, r.by), by = fmaf(hi.y, r.iy, r.by);
-  const float az = fmaf(lo.z, r.iz, r.bz), bz = fmaf(hi.z, r.iz, r.bz);
+  const float ax = fmaf(lo.x, r.ix, r.blx), bx = fmaf(hi.x, r.ix, r.bhx);
+  const float ay = fmaf(lo.y, r.iy, r.bly), by = fmaf(hi.y, r.iy, r.bhy);
+  const float az = fmaf(lo.z, r.iz, r.blz), bz = fmaf(hi.z, r.iz, r.bhz);
   // fminf/fmaxf drop a NaN operand, which is the conservative side
   tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), r.tmin));
   const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), thi));
-  return tn <= fmaf(tf, 1.0000038f, r.eabs);
+  return tn <= fmaf(fabsf(tf), 3.8e-6f, tf);  // 2^-18 >> the 4u a borderline pair (|tn| ~ |tf|) needs, any signs
 }
 
 // ---------------------------------------------------------------------------------------------
