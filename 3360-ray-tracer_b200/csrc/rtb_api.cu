@@ -540,7 +540,8 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   if (rc != RTB_OK) return rc;
   const uint32_t n_pixels = (uint32_t)cam->width * (uint32_t)cam->height;
   uint32_t pool = prm->pool_size ? prm->pool_size : (1u << 21);
-  pool = std::max(pool, 1u << 10);
+  pool = std::min(std::max(pool, 1u << 10), 1u << 28);
+  if ((unsigned long long)cam->width * (unsigned long long)cam->height > (1ull << 30)) return Fail(RTB_EINVAL, "image larger than 2^30 pixels");
   // RTB_RENDER_SERIAL: one wave, every kernel timed alone with events (the roofline measurement);
   // otherwise several waves in flight and only the whole render is timed.
   const bool serial = (prm->flags & RTB_RENDER_SERIAL) != 0;
@@ -608,13 +609,14 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
     Wave& w = *waves[0];
     while (generated < total) {
       const uint32_t chunk = (uint32_t)std::min<unsigned long long>(total - generated, 1ull << 30);
+      const uint32_t s0 = (uint32_t)(generated / n_pixels), p0 = (uint32_t)(generated % n_pixels);
       RTB_CUDA(cudaMemsetAsync(w.counts, 0, 4, w.stream));
       auto* rc64 = reinterpret_cast<unsigned long long*>(w.counts + 2);
       if (use_smem)
-        rtb::path_kernel<true, false><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, generated, rcst, ctx->pixel_order,
+        rtb::path_kernel<true, false><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, ctx->pixel_order,
                                                                                   d_rgb_sum, w.counts, rc64, s->counters);
       else
-        rtb::path_kernel<false, false><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, generated, rcst, ctx->pixel_order,
+        rtb::path_kernel<false, false><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, ctx->pixel_order,
                                                                                    d_rgb_sum, w.counts, rc64, s->counters);
       generated += chunk;
       ++launches;
@@ -654,10 +656,10 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
           if (serial) RTB_CUDA(cudaEventRecord(d0, ws));
           auto* rc64 = reinterpret_cast<unsigned long long*>(w.counts + 2);
           if (use_smem)
-            rtb::path_kernel<true, true><<<path_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, 0ull, rcst, ctx->pixel_order, d_rgb_sum,
+            rtb::path_kernel<true, true><<<path_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, 0u, 0u, rcst, ctx->pixel_order, d_rgb_sum,
                                                                                w.counts, rc64, s->counters);
           else
-            rtb::path_kernel<false, true><<<path_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, 0ull, rcst, ctx->pixel_order, d_rgb_sum,
+            rtb::path_kernel<false, true><<<path_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, 0u, 0u, rcst, ctx->pixel_order, d_rgb_sum,
                                                                                 w.counts, rc64, s->counters);
           if (serial) RTB_CUDA(cudaEventRecord(d1, ws));
           if (trace_iters) std::fprintf(stderr, "[rtb drain] %u paths\n", w.live);
@@ -672,7 +674,8 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
       cudaStream_t ws = w.stream;
       if (serial) RTB_CUDA(cudaEventRecord(ek[0], ws));
       if (gen) {
-        rtb::generate_kernel<<<(gen + 255) / 256, 256, 0, ws>>>(w.q[w.cur], w.live, gen, generated, rcst, ctx->pixel_order);
+        rtb::generate_kernel<<<(gen + 255) / 256, 256, 0, ws>>>(w.q[w.cur], w.live, gen, (uint32_t)(generated / n_pixels), (uint32_t)(generated % n_pixels), rcst,
+                                                                ctx->pixel_order);
         generated += gen;
         w.live += gen;
         ++launches;

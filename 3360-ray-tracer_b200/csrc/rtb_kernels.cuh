@@ -53,6 +53,13 @@ __device__ __forceinline__ void stage_top(const DevScene& s, float4* smem_pairs)
 #ifndef RTB_PATH_REFILL_LANES  // ... of the path kernel, whose service phase also shades: worth waiting for more lanes
 #define RTB_PATH_REFILL_LANES 16
 #endif
+#ifndef RTB_NODE_EXIT_NUM  // the node phase ends when fewer than NUM/DEN of the tracing lanes stand at an internal pair
+#define RTB_NODE_EXIT_NUM 1
+#define RTB_NODE_EXIT_DEN 4
+#endif
+#ifndef RTB_NODE_STEPS_PER_VOTE
+#define RTB_NODE_STEPS_PER_VOTE 2
+#endif
 #ifndef RTB_SMEM_STACK  // traversal-stack entries per thread kept in shared memory (the rest: local memory)
 #define RTB_SMEM_STACK 0
 #endif
@@ -237,8 +244,11 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
     for (;;) {
       const bool at_node = active && !(cur & kLeafBit);
       const unsigned nm = __ballot_sync(kFull, at_node);
-      if (nm == 0u || 2 * __popc(nm) < n_act) break;
+      if (nm == 0u || RTB_NODE_EXIT_DEN * __popc(nm) < RTB_NODE_EXIT_NUM * n_act) break;
       if (at_node) node_step();
+#pragma unroll
+      for (int extra = 1; extra < RTB_NODE_STEPS_PER_VOTE; ++extra)  // more steps on the same vote: less vote overhead
+        if (active && !(cur & kLeafBit)) node_step();
     }
     // ---- leaf phase, one primitive type at a time (the types are different code, SIMT would serialise
     // them anyway); each lane works through its whole leaf, the descriptor counting down
@@ -328,9 +338,12 @@ struct PathState {  // what a path carries besides its ray
   uint32_t pixel, sample, bounce;
 };
 
-__device__ __forceinline__ void generate_sample(const RenderConsts& rc, const uint32_t* __restrict__ pixel_order, unsigned long long g,
-                                                float4& ro, float4& rd, PathState& ps) {
-  const uint32_t s_local = (uint32_t)(g / rc.n_pixels), pl = (uint32_t)(g % rc.n_pixels);
+// A call's samples are numbered g = s_local * n_pixels + pl; callers pass (s0, p0) = divmod(g0, n_pixels) of their first
+// sample and a 32-bit offset i, so the device never divides 64-bit numbers.
+__device__ __forceinline__ void generate_sample(const RenderConsts& rc, const uint32_t* __restrict__ pixel_order, uint32_t s0, uint32_t p0,
+                                                uint32_t i, float4& ro, float4& rd, PathState& ps) {
+  const uint32_t t = p0 + i;  // < 2^31: p0 < n_pixels <= 2^30 and i < 2^30 (host-side chunking)
+  const uint32_t s_local = s0 + t / rc.n_pixels, pl = t % rc.n_pixels;
   const uint32_t pixel = __ldg(&pixel_order[pl]);
   const uint32_t sample = (uint32_t)rc.spp_begin + s_local;
   const int px = (int)(pixel % (uint32_t)rc.cam.width), py = (int)(pixel / (uint32_t)rc.cam.width);
@@ -360,14 +373,14 @@ __device__ __forceinline__ void generate_sample(const RenderConsts& rc, const ui
   ps.bounce = 0u;
 }
 
-// Slot q_offset + k of the queue receives local sample g0 + k.
-__global__ void generate_kernel(PathQueue q, uint32_t q_offset, uint32_t count, unsigned long long g0, RenderConsts rc,
+// Slot q_offset + k of the queue receives local sample g0 + k, g0 = s0 * n_pixels + p0.
+__global__ void generate_kernel(PathQueue q, uint32_t q_offset, uint32_t count, uint32_t s0, uint32_t p0, RenderConsts rc,
                                 const uint32_t* __restrict__ pixel_order) {
   const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= count) return;
   float4 ro, rd;
   PathState ps;
-  generate_sample(rc, pixel_order, g0 + k, ro, rd, ps);
+  generate_sample(rc, pixel_order, s0, p0, k, ro, rd, ps);
   const uint32_t slot = q_offset + k;
   q.ro[slot] = ro;
   q.rd[slot] = rd;
@@ -437,6 +450,7 @@ __device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts
     float u, v;
     uint32_t mat_id;
     surface_at(s, ref, p, n_out, u, v, mat_id);
+    const bool on_sphere = RTB_REF_TYPE(ref) == RTB_PRIM_SPHERE;
     const bool front = dot3(d, n_out) < 0.0f;  // HitRecord::set_face_normal, hittable.h:31-34
     const f3 nrm = front ? n_out : -n_out;
     const RtbMaterial m = s.materials[mat_id];
@@ -446,7 +460,7 @@ __device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts
       if (m.type == RTB_MAT_LAMBERTIAN) {  // material.cc:20-34
         dir = nrm + unit_vector(u01(rnd.x), u01(rnd.y));
         if (fabsf(dir.x) < 1e-8f && fabsf(dir.y) < 1e-8f && fabsf(dir.z) < 1e-8f) dir = nrm;
-        atten = texture_value(s, m.tex, u, v, p);
+        atten = texture_value(s, m.tex, u, v, p, on_sphere, n_out);
         alive = true;
       } else if (m.type == RTB_MAT_METAL) {  // material.cc:82-94: reflects the UN-normalised direction
         dir = reflect3(d, nrm) + m.fuzz * unit_vector(u01(rnd.x), u01(rnd.y));
@@ -461,7 +475,7 @@ __device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts
         dir = (cannot_refract || schlick(cos_theta, eta) > u01(rnd.z)) ? reflect3(ud, nrm) : refract3(ud, nrm, eta);
         alive = true;
       } else {  // DiffuseLight: emits, never scatters (material.cc:273-280,312-316)
-        add_radiance(accum, pixel, thr * texture_value(s, m.tex, u, v, p));
+        add_radiance(accum, pixel, thr * texture_value(s, m.tex, u, v, p, on_sphere, n_out));
       }
       ps.tr = thr.x * atten.x; ps.tg = thr.y * atten.y; ps.tb = thr.z * atten.z;
       // the recursion bottoms out in black when depth reaches 0 (camera.h:149-151)
@@ -469,7 +483,7 @@ __device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts
     } else {
       // ---- mode B (wavefront.cc:131-207)
       f3 emitted = mk3(0, 0, 0);
-      if (m.type == RTB_MAT_DIFFUSE_LIGHT) emitted = texture_value(s, m.tex, u, v, p);
+      if (m.type == RTB_MAT_DIFFUSE_LIGHT) emitted = texture_value(s, m.tex, u, v, p, on_sphere, n_out);
       const bool near_zero = fabsf(emitted.x) < 1e-8f && fabsf(emitted.y) < 1e-8f && fabsf(emitted.z) < 1e-8f;
       f3 tp = thr;
       if (!near_zero) {
@@ -489,7 +503,7 @@ __device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts
         const float cosv = dot3(dir, nrm);
         const float pdf = cosv / 3.14159265358979323846f;
         if (cosv > 0.0f && pdf >= 1e-6f) {  // material.cc:66-68, wavefront.cc:178-183
-          tp = thr * texture_value(s, m.tex, u, v, p);
+          tp = thr * texture_value(s, m.tex, u, v, p, on_sphere, n_out);
           alive = true;
         }
       } else if (m.type == RTB_MAT_METAL) {  // Metal::Sample, material.cc:117-141
@@ -549,7 +563,7 @@ struct PathIo {
   const RenderConsts& rc;
   float* accum;
   PathQueue q;
-  unsigned long long g0;
+  uint32_t s0, p0;  // divmod(first sample of this launch, n_pixels)
   const uint32_t* pixel_order;
   PathState ps;
   __device__ __forceinline__ void load(uint32_t i, float4& o, float4& d) {
@@ -563,7 +577,7 @@ struct PathIo {
       ps.sample = meta.x;
       ps.bounce = meta.y;
     } else {
-      generate_sample(rc, pixel_order, g0 + i, o, d, ps);
+      generate_sample(rc, pixel_order, s0, p0, i, o, d, ps);
     }
   }
   __device__ __forceinline__ bool finish(uint32_t, uint32_t ref, float tf, const TravRay& r, float4& o, float4& d) {
@@ -574,13 +588,13 @@ struct PathIo {
 };
 
 template <bool kUseSmem, bool kFromQueue>
-__global__ void __launch_bounds__(kTraceBlock, RTB_PATH_MIN_BLOCKS) path_kernel(DevScene s, PathQueue q, uint32_t n, unsigned long long g0,
+__global__ void __launch_bounds__(kTraceBlock, RTB_PATH_MIN_BLOCKS) path_kernel(DevScene s, PathQueue q, uint32_t n, uint32_t s0, uint32_t p0,
                                                                                RenderConsts rc, const uint32_t* __restrict__ pixel_order,
                                                                                float* accum, unsigned int* cursor,
                                                                                unsigned long long* ray_count, HitCounters* cnt) {
   extern __shared__ float4 smem_pairs[];
   if (kUseSmem) stage_top(s, smem_pairs);
-  PathIo<kFromQueue> io{n, 0u, s, rc, accum, q, g0, pixel_order, PathState{}};
+  PathIo<kFromQueue> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathState{}};
   trace_loop<kUseSmem>(s, smem_pairs, smem_stack_base(s, smem_pairs, kUseSmem), io, cursor, cnt);
   const unsigned total = __reduce_add_sync(kFull, io.rays);
   if ((threadIdx.x & 31u) == 0u && total) atomicAdd(ray_count, (unsigned long long)total);

@@ -59,7 +59,9 @@ __device__ __forceinline__ void sphere_uv(f3 n, float& u, float& v) {
 
 // Texture::Value: SolidColor (texture.h:24-26), CheckerTexture (texture.h:39-47, nesting followed
 // iteratively), ImageTexture (texture.h:59-73 + Image::PixelData clamp image.cc:50-67).
-__device__ __forceinline__ f3 texture_value(const DevScene& s, int tex, float u, float v, f3 p) {
+// (u, v) of a sphere are only needed by image textures: they are computed here, on demand, from the outward
+// normal (sphere_n, valid when on_sphere) instead of for every sphere hit as the reference does (sphere.h:50).
+__device__ __forceinline__ f3 texture_value(const DevScene& s, int tex, float u, float v, f3 p, bool on_sphere, f3 sphere_n) {
   for (int guard = 0; guard < 8; ++guard) {
     const RtbTexture t = s.textures[tex];
     if (t.type == RTB_TEX_SOLID) return mk3(t.color[0], t.color[1], t.color[2]);
@@ -71,6 +73,7 @@ __device__ __forceinline__ f3 texture_value(const DevScene& s, int tex, float u,
     // image
     const int2 dim = s.image_dim[t.image];
     if (dim.y <= 0) return mk3(0.0f, 1.0f, 1.0f);  // texture.h:61
+    if (on_sphere) sphere_uv(sphere_n, u, v);
     u = fminf(fmaxf(u, 0.0f), 1.0f);
     v = 1.0f - fminf(fmaxf(v, 0.0f), 1.0f);
     int i = (int)(u * dim.x), j = (int)(v * dim.y);
@@ -94,7 +97,6 @@ __device__ __forceinline__ void surface_at(const DevScene& s, uint32_t ref, f3 p
     const float4 c = __ldg(&s.sphere_f[idx]);
     const float inv_r = 1.0f / c.w;
     n_out = inv_r * mk3(p.x - c.x, p.y - c.y, p.z - c.z);
-    sphere_uv(n_out, u, v);
     mat = __ldg(&s.sphere_mat[idx]);
   } else if (ty == RTB_PRIM_TRIANGLE) {
     const float4 a = __ldg(&s.triangle_f[3 * (size_t)idx]), e1 = __ldg(&s.triangle_f[3 * (size_t)idx + 1]), e2 = __ldg(&s.triangle_f[3 * (size_t)idx + 2]);
