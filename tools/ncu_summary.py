@@ -40,3 +40,47 @@ ti, ts = sum(o[4] for o in out), sum(o[3] for o in out)
 print(f"\nsource lines: {ti/1e6:.1f} M warp instructions, {ts} samples (first launch)")
 for o in sorted(out, key=lambda o: -o[4])[:top]:
     print(f"{o[0][:16]:16s}{o[1]:4d} inst {100*o[4]/ti:5.1f}% samp {100*o[3]/max(ts,1):5.1f}% lanes {o[5]/max(o[4],1):5.1f} | {o[2]}")
+
+# ---- instruction share per phase of the traversal / path kernels (source line ranges found by marker text)
+if "--phases" in sys.argv:
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent / "3360-ray-tracer_b200" / "csrc"
+    K = (root / "rtb_kernels.cuh").read_text().split("\n")
+    D = (root / "rtb_device.cuh").read_text().split("\n")
+    def find(lines, pat):
+        for i, l in enumerate(lines):
+            if pat in l:
+                return i + 1
+        return 10 ** 9
+    kr = {"node_step": (find(K, "auto node_step = [&]()"), find(K, "auto leaf_step = [&]")),
+          "leaf_step": (find(K, "auto leaf_step = [&]"), find(K, "// ---- service phase")),
+          "service phase (store/refill control)": (find(K, "// ---- service phase"), find(K, "if (n_trace == 0) break;")),
+          "node loop vote": (find(K, "// ---- node phase: descend"), find(K, "// ---- leaf phase, one primitive type")),
+          "leaf loop vote": (find(K, "// ---- leaf phase, one primitive type"), find(K, "// ---- leaf phase, one primitive type") + 12),
+          "generate_sample": (find(K, "__device__ __forceinline__ void generate_sample"), find(K, "// Slot q_offset + k")),
+          "shade_path": (find(K, "__device__ __forceinline__ bool shade_path"), find(K, "// ---- path kernel")),
+          "stack / pop / finish": (find(K, "struct TravStack"), find(K, "auto node_step = [&]()"))}
+    dr = {"philox": (find(D, "// Philox4x32-10"), find(D, "// Per-lane ray state")),
+          "slab + prepare_ray": (find(D, "// Per-lane ray state"), find(D, "// Exact replays.")),
+          "exact replays": (find(D, "// Exact replays."), find(D, "// Filters.  Result classes")),
+          "triangle_filter": (find(D, "__device__ __forceinline__ int triangle_filter"), find(D, "// Sphere: the cancellation-prone")),
+          "sphere_filter": (find(D, "__device__ __forceinline__ int sphere_filter"), find(D, "// Rect: FP32 throughout")),
+          "rect_filter": (find(D, "__device__ __forceinline__ int rect_filter"), find(D, "__device__ __forceinline__ uint32_t rank_of")),
+          "consider / tie rule": (find(D, "__device__ __forceinline__ uint32_t rank_of"), 10 ** 9)}
+    def cat(f, l):
+        table = kr if f.startswith("rtb_kernels") else dr if f.startswith("rtb_device") else None
+        if f.startswith("rtb_shade"):
+            return "shade_path"
+        if table:
+            for k, (a, b) in table.items():
+                if a <= l < b:
+                    return k
+            return "other " + f
+        return "intrinsic headers"
+    S = collections.defaultdict(lambda: [0, 0, 0])
+    for f, l, _, samp, inst, thr in out:
+        c = cat(f, l)
+        S[c][0] += samp; S[c][1] += inst; S[c][2] += thr
+    print("\nphase                                  warp-inst  samples  active lanes")
+    for k, v in sorted(S.items(), key=lambda kv: -kv[1][1]):
+        print(f"{k:38s} {100*v[1]/ti:7.1f}% {100*v[0]/max(ts,1):7.1f}% {v[2]/max(v[1],1):8.1f}")
