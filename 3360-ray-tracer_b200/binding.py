@@ -20,6 +20,7 @@ RTB_OK, RTB_EINVAL, RTB_ENODEVICE, RTB_ECUDA, RTB_ENOMEM = 0, -1, -2, -3, -4
 PRIM_SPHERE, PRIM_TRIANGLE, PRIM_RECT, PRIM_SUBTREE = 0, 1, 2, 3
 MODE_A, MODE_B = 0, 1
 RENDER_SMEM_TOP, RENDER_KEEP_ACCUM, RENDER_SERIAL, RENDER_WAVEFRONT, RENDER_NO_DRAIN = 1, 2, 4, 8, 16
+ADAPT_PIXEL_STATE, ADAPT_LUMINANCE = 0, 1
 EX_SPHERE, EX_TRIANGLE, EX_RECT, EX_BVH_BEGIN, EX_BVH_END, EX_LIST_BEGIN, EX_LIST_END = 0, 1, 2, 10, 11, 12, 13
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_DIFFUSE_LIGHT = 0, 1, 2, 3
 TEX_SOLID, TEX_CHECKER, TEX_IMAGE = 0, 1, 2
@@ -67,6 +68,10 @@ class RtbRenderParams(C.Structure):
     ]
 
 
+class RtbAdaptive(C.Structure):
+    _fields_ = [("rel_threshold", C.c_float), ("min_samples", C.c_int32), ("criterion", C.c_int32), ("pad", C.c_int32)]
+
+
 class RtbStats(C.Structure):
     _fields_ = [
         ("samples", C.c_uint64), ("rays", C.c_uint64), ("node_visits", C.c_uint64), ("sphere_tests", C.c_uint64),
@@ -101,6 +106,7 @@ assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 16
 RTB_SYMBOLS = [
     "rtb_last_error", "rtb_abi_version", "rtb_tree_compile", "rtb_tree_destroy", "rtb_device_count", "rtb_init", "rtb_shutdown", "rtb_scene_create",
     "rtb_scene_destroy", "rtb_intersect_batch", "rtb_intersect_batch_device", "rtb_render", "rtb_render_device",
+    "rtb_render_adaptive", "rtb_render_adaptive_device", "rtb_resolve_counts", "rtb_resolve_counts_device",
     "rtb_resolve_device", "rtb_resolve", "rtb_measure_l2_gbs", "rtb_measure_fp32_tflops", "rtb_measure_fp64_tflops",
 ]
 RTH_SYMBOLS = [
@@ -152,6 +158,11 @@ def load(counters: bool = False) -> C.CDLL:
     lib.rtb_intersect_batch_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
     lib.rtb_render.argtypes = [C.c_void_p, C.POINTER(RtbCamera), C.POINTER(RtbRenderParams), C.c_void_p, C.POINTER(RtbStats)]
     lib.rtb_render_device.argtypes = [C.c_void_p, C.POINTER(RtbCamera), C.POINTER(RtbRenderParams), C.c_void_p, C.POINTER(RtbStats)]
+    lib.rtb_render_adaptive.argtypes = [C.c_void_p, C.POINTER(RtbCamera), C.POINTER(RtbRenderParams), C.POINTER(RtbAdaptive), C.c_void_p,
+                                        C.c_void_p, C.c_void_p, C.POINTER(RtbStats)]
+    lib.rtb_render_adaptive_device.argtypes = lib.rtb_render_adaptive.argtypes
+    lib.rtb_resolve_counts.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.rtb_resolve_counts_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
     lib.rtb_resolve.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]
     lib.rtb_resolve_device.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p]
     lib.rtb_measure_l2_gbs.argtypes = [C.c_size_t, C.c_int, C.POINTER(C.c_float)]
@@ -328,12 +339,48 @@ class DeviceScene:
         _check(self._lib, self._lib.rtb_render(self._h, C.byref(cam), C.byref(prm), _ptr(out), C.byref(st)))
         return out, st.as_dict()
 
+    def render_adaptive(self, cam: RtbCamera, max_spp: int, max_depth: int, rel_threshold: float = 0.05, min_samples: int = 16,
+                        criterion: int = ADAPT_PIXEL_STATE, mode: int = MODE_B, seed: int = 0x3360, spp_begin: int = 0, flags: int = 0,
+                        state=None):
+        """seam 1 with the per-pixel adaptive stop; host buffers.  Returns (rgb_sum[h,w,3], rgb_sumsq[h,w,3], count[h,w], stats).
+        `state` = (rgb_sum, rgb_sumsq, count) of an earlier call to continue (sets RENDER_KEEP_ACCUM)."""
+        prm = RtbRenderParams(spp_begin, spp_begin + max_spp, max_depth, mode, seed, 0, flags | (RENDER_KEEP_ACCUM if state is not None else 0))
+        ad = RtbAdaptive(rel_threshold, min_samples, criterion, 0)
+        shape = (cam.height, cam.width)
+        if state is not None:
+            out, sq, cnt = (np.array(state[0], np.float32, order="C"), np.array(state[1], np.float32, order="C"), np.array(state[2], np.uint32, order="C"))
+        else:
+            out, sq, cnt = np.zeros(shape + (3,), np.float32), np.zeros(shape + (3,), np.float32), np.zeros(shape, np.uint32)
+        st = RtbStats()
+        _check(self._lib, self._lib.rtb_render_adaptive(self._h, C.byref(cam), C.byref(prm), C.byref(ad), _ptr(out), _ptr(sq), _ptr(cnt), C.byref(st)))
+        return out, sq, cnt, st.as_dict()
+
+    def render_adaptive_device(self, cam: RtbCamera, d_sum_ptr: int, d_sumsq_ptr: int, d_count_ptr: int, spp_begin: int, spp_end: int, max_depth: int,
+                               rel_threshold: float = 0.05, min_samples: int = 16, criterion: int = ADAPT_PIXEL_STATE, mode: int = MODE_B,
+                               seed: int = 0x3360, flags: int = 0):
+        prm = RtbRenderParams(spp_begin, spp_end, max_depth, mode, seed, 0, flags)
+        ad = RtbAdaptive(rel_threshold, min_samples, criterion, 0)
+        st = RtbStats()
+        _check(self._lib, self._lib.rtb_render_adaptive_device(self._h, C.byref(cam), C.byref(prm), C.byref(ad), d_sum_ptr, d_sumsq_ptr, d_count_ptr,
+                                                               C.byref(st)))
+        return st.as_dict()
+
     def render_device(self, cam: RtbCamera, d_accum_ptr: int, spp_begin: int, spp_end: int, max_depth: int, mode: int = MODE_A,
                       seed: int = 0x3360, pool_size: int = 0, flags: int = 0):
         prm = RtbRenderParams(spp_begin, spp_end, max_depth, mode, seed, pool_size, flags)
         st = RtbStats()
         _check(self._lib, self._lib.rtb_render_device(self._h, C.byref(cam), C.byref(prm), d_accum_ptr, C.byref(st)))
         return st.as_dict()
+
+
+def resolve_counts(rgb_sum: np.ndarray, count: np.ndarray, counters: bool = False) -> np.ndarray:
+    """write_color of rgb_sum / count per pixel (wavefront.cc:229-241)."""
+    lib = load(counters)
+    a = np.ascontiguousarray(rgb_sum, dtype=np.float32)
+    c = np.ascontiguousarray(count, dtype=np.uint32)
+    out = np.zeros(a.shape, np.uint8)
+    _check(lib, lib.rtb_resolve_counts(_ptr(a), _ptr(c), c.size, _ptr(out)))
+    return out
 
 
 def resolve(rgb_sum: np.ndarray, spp: int, counters: bool = False) -> np.ndarray:

@@ -37,15 +37,6 @@ int EnsureInit() {
   return rtb_init(0);
 }
 
-template <class T>
-int Upload(const T* host, size_t n, T** dev) {
-  *dev = nullptr;
-  if (n == 0) return RTB_OK;
-  RTB_CUDA(cudaMalloc(reinterpret_cast<void**>(dev), n * sizeof(T)));
-  RTB_CUDA(cudaMemcpy(*dev, host, n * sizeof(T), cudaMemcpyHostToDevice));
-  return RTB_OK;
-}
-
 // Wavefront state, per host thread (= per device), allocated lazily by rtb_render* and kept across
 // scenes and calls.  A Wave is one independent wavefront: its own path pool (two queues), hit
 // arrays, counters and stream.  Several waves are kept in flight so that the drain tail of one
@@ -55,7 +46,7 @@ struct Wave {
   rtb::PathQueue q[2]{};
   float* hit_t = nullptr;
   uint32_t* hit_ref = nullptr;
-  unsigned int* counts = nullptr;      // device: [0] traversal cursor, [1] shade survivor count, [2..3] 64-bit ray counter of the path kernel
+  unsigned int* counts = nullptr;      // device: [0] traversal cursor, [1] shade survivor count, [2..3] 64-bit ray counter of the path kernel, [4..5] camera samples started (adaptive)
   unsigned int* host_count = nullptr;  // pinned
   cudaStream_t stream = nullptr;
   cudaEvent_t done = nullptr;
@@ -70,6 +61,8 @@ struct RenderCtx {
   uint32_t pool = 0;
   uint32_t* pixel_order = nullptr;
   int order_w = 0, order_h = 0;
+  float* accum = nullptr;  // rtb_render's device accumulator (host-buffer entry), grow-only
+  size_t accum_bytes = 0;
 };
 thread_local RenderCtx g_ctx;
 
@@ -127,23 +120,74 @@ static int CompileTree(const RtbSceneDesc& d, rtbc::Compiled* out) {
 
 static int ValidateDesc(const RtbSceneDesc* d);
 
+// Pinned staging for scene uploads, per host thread, grow-only: rtb_scene_create copies every array into it and
+// issues one asynchronous H2D copy per array into ONE device arena (one cudaMalloc / cudaFree per scene).
+struct Staging {
+  char* host = nullptr;
+  size_t bytes = 0;
+};
+thread_local Staging g_staging;
+
 struct RtbScene {
   rtb::DevScene dev{};
-  std::vector<void*> allocs;
+  char* arena = nullptr;  // every table of the scene, 256-byte aligned sub-ranges
+  size_t arena_bytes = 0;
+  struct Pending {
+    const void* src;
+    size_t bytes, off;
+    const void** out;
+  };
+  std::vector<Pending> pending;
   std::vector<cudaArray_t> arrays;
   std::vector<cudaTextureObject_t> textures;
   rtb::HitCounters* counters = nullptr;
   unsigned int* cursor = nullptr;  // persistent-thread work cursor + shade output counter (2 words)
-  unsigned int* host_count = nullptr;  // pinned
   size_t smem_bytes = 0;
   int device = 0;
+  size_t Reserve(size_t bytes) {
+    const size_t off = (arena_bytes + 255) & ~(size_t)255;
+    arena_bytes = off + bytes;
+    return off;
+  }
+  // queue `n` elements for upload; *out is set by Commit.  `host` must stay valid until then.
   template <class T>
   int Put(const T* host, size_t n, const T** out) {
-    T* d = nullptr;
-    int rc = Upload(host, n, &d);
-    if (rc != RTB_OK) return rc;
-    if (d) allocs.push_back(d);
-    *out = d;
+    *out = nullptr;
+    if (n == 0) return RTB_OK;
+    pending.push_back(Pending{host, n * sizeof(T), Reserve(n * sizeof(T)), reinterpret_cast<const void**>(out)});
+    return RTB_OK;
+  }
+  int Commit(cudaStream_t st) {
+    const size_t ctr_off = Reserve(sizeof(rtb::HitCounters) + 16);
+    // tables above 32 MB (the stress scene) go straight from the caller's memory; pinning gigabytes costs more than it saves
+    constexpr size_t kDirect = 32u << 20;
+    size_t staged = 0;
+    for (const Pending& p : pending)
+      if (p.bytes <= kDirect) staged += (p.bytes + 255) & ~(size_t)255;
+    if (g_staging.bytes < staged) {
+      if (g_staging.host) cudaFreeHost(g_staging.host);
+      g_staging = Staging{};
+      const size_t want = staged + staged / 4;
+      RTB_CUDA(cudaMallocHost(reinterpret_cast<void**>(&g_staging.host), want));
+      g_staging.bytes = want;
+    }
+    RTB_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&arena), arena_bytes, st));  // pool-backed: re-creating a scene reuses the block
+    size_t so = 0;
+    for (const Pending& p : pending) {  // the DMA of one table overlaps the host copy of the next
+      if (p.bytes <= kDirect) {
+        std::memcpy(g_staging.host + so, p.src, p.bytes);
+        RTB_CUDA(cudaMemcpyAsync(arena + p.off, g_staging.host + so, p.bytes, cudaMemcpyHostToDevice, st));
+        so += (p.bytes + 255) & ~(size_t)255;
+      } else {
+        RTB_CUDA(cudaMemcpyAsync(arena + p.off, p.src, p.bytes, cudaMemcpyHostToDevice, st));
+      }
+      *p.out = arena + p.off;
+    }
+    RTB_CUDA(cudaMemsetAsync(arena + ctr_off, 0, sizeof(rtb::HitCounters) + 16, st));
+    counters = reinterpret_cast<rtb::HitCounters*>(arena + ctr_off);
+    cursor = reinterpret_cast<unsigned int*>(arena + ctr_off + sizeof(rtb::HitCounters));
+    RTB_CUDA(cudaStreamSynchronize(st));  // the staging buffer and the caller's arrays are free again
+    pending.clear();
     return RTB_OK;
   }
 };
@@ -190,6 +234,15 @@ int rtb_init(int device) {
   RTB_CUDA(cudaGetDeviceProperties(&prop, device));
   g_sm_count = prop.multiProcessorCount;
   g_device = device;
+  {  // keep freed scene arenas in the device's default pool instead of returning them to the driver
+    cudaMemPool_t pool = nullptr;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+      unsigned long long keep = ~0ull;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    } else {
+      cudaGetLastError();
+    }
+  }
   return RTB_OK;
 }
 
@@ -201,6 +254,11 @@ int rtb_shutdown(void) {
     if (g_ctx.pixel_order) cudaFree(g_ctx.pixel_order);
     g_ctx.pixel_order = nullptr;
     g_ctx.order_w = g_ctx.order_h = 0;
+    if (g_ctx.accum) cudaFree(g_ctx.accum);
+    g_ctx.accum = nullptr;
+    g_ctx.accum_bytes = 0;
+    if (g_staging.host) cudaFreeHost(g_staging.host);
+    g_staging = Staging{};
     cudaStreamDestroy(g_stream);
     g_stream = nullptr;
     g_device = -1;
@@ -214,8 +272,11 @@ int rtb_scene_destroy(RtbScene* s) {
   for (auto t : s->textures)
     if (t) cudaDestroyTextureObject(t);
   for (auto a : s->arrays) cudaFreeArray(a);
-  for (void* p : s->allocs) cudaFree(p);
-  if (s->host_count) cudaFreeHost(s->host_count);
+  if (s->arena) {
+    cudaDeviceSynchronize();  // work on caller streams (rtb_intersect_batch_device) may still read the arena
+    if (g_stream && g_device == s->device) cudaFreeAsync(s->arena, g_stream);
+    else cudaFree(s->arena);
+  }
   delete s;
   return RTB_OK;
 }
@@ -239,8 +300,12 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
       return rc;             \
     }                        \
   } while (0)
+  // host temporaries queued by Put must outlive Commit
+  rtbc::Compiled local;
+  std::vector<float4> sf, tf, rf;
+  std::vector<cudaTextureObject_t> objs;
+  std::vector<int2> dims;
   {  // interchange tree -> device-native sibling pairs (rtb_compile.h), unless the caller already did it
-    rtbc::Compiled local;
     const rtbc::Compiled* tree = d->compiled ? &d->compiled->tree : &local;
     if (!d->compiled) {
       rc = CompileTree(*d, &local);
@@ -257,11 +322,11 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
   PUT(s->Put(reinterpret_cast<const double2*>(d->triangles), 5 * (size_t)d->n_triangles, &v.triangles));
   PUT(s->Put(reinterpret_cast<const double2*>(d->rects), 3 * (size_t)d->n_rects, &v.rects));
   {  // float shadows of the double tables (shading frame + pre-filter)
-    std::vector<float4> sf(d->n_spheres);
+    sf.resize(d->n_spheres);
     for (uint32_t i = 0; i < d->n_spheres; ++i)
       sf[i] = make_float4((float)d->spheres[i].c[0], (float)d->spheres[i].c[1], (float)d->spheres[i].c[2], (float)d->spheres[i].r);
     PUT(s->Put(sf.data(), sf.size(), &v.sphere_f));
-    std::vector<float4> tf(3 * (size_t)d->n_triangles);
+    tf.resize(3 * (size_t)d->n_triangles);
     for (uint32_t i = 0; i < d->n_triangles; ++i) {
       const RtbTriangle& t = d->triangles[i];
       float4 a = make_float4((float)t.a[0], (float)t.a[1], (float)t.a[2], 0.f);
@@ -273,7 +338,7 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
       tf[3 * (size_t)i + 2] = make_float4((float)t.e2[0], (float)t.e2[1], (float)t.e2[2], mx(t.e2));
     }
     PUT(s->Put(tf.data(), tf.size(), &v.triangle_f));
-    std::vector<float4> rf(2 * (size_t)d->n_rects);
+    rf.resize(2 * (size_t)d->n_rects);
     for (uint32_t i = 0; i < d->n_rects; ++i) {
       const RtbRect& r = d->rects[i];
       rf[2 * (size_t)i] = make_float4((float)r.k, (float)r.a0, (float)r.a1, (float)r.b0);
@@ -294,8 +359,8 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
   PUT(s->Put(d->materials, d->n_materials, &v.materials));
   PUT(s->Put(d->textures, d->n_textures, &v.textures));
   {  // images -> point-sampled texture objects over RGBA8 arrays
-    std::vector<cudaTextureObject_t> objs(d->n_images, 0);
-    std::vector<int2> dims(d->n_images, make_int2(0, 0));
+    objs.assign(d->n_images, 0);
+    dims.assign(d->n_images, make_int2(0, 0));
     for (uint32_t i = 0; i < d->n_images; ++i) {
       const RtbImage& im = d->images[i];
       if (im.width <= 0 || im.height <= 0 || !im.rgb) continue;
@@ -336,19 +401,7 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
     rtb_scene_destroy(s);
     return Fail(RTB_EINVAL, "n_top_nodes does not fit shared memory");
   }
-  {
-    void* p = nullptr;
-    cudaError_t e = cudaMalloc(&p, sizeof(rtb::HitCounters) + 16);
-    if (e == cudaSuccess) e = cudaMemset(p, 0, sizeof(rtb::HitCounters) + 16);
-    if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&s->host_count), 64);
-    if (e != cudaSuccess) {
-      rtb_scene_destroy(s);
-      return Fail(RTB_ECUDA, std::string("counter alloc: ") + cudaGetErrorString(e));
-    }
-    s->allocs.push_back(p);
-    s->counters = reinterpret_cast<rtb::HitCounters*>(p);
-    s->cursor = reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(p) + sizeof(rtb::HitCounters));
-  }
+  PUT(s->Commit(g_stream));
   // opt in to large dynamic shared memory for the two traversal kernels
   {
     const int with_top = (int)(s->smem_bytes + kStackSmem), without = (int)kStackSmem;
@@ -357,12 +410,14 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
       cudaFuncSetAttribute(rtb::extend_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, with_top);
       cudaFuncSetAttribute(rtb::path_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, with_top);
       cudaFuncSetAttribute(rtb::path_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, with_top);
+      cudaFuncSetAttribute(rtb::path_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, with_top);
     }
     if (without > 48 * 1024) {
       cudaFuncSetAttribute(rtb::intersect_batch_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, without);
       cudaFuncSetAttribute(rtb::extend_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, without);
       cudaFuncSetAttribute(rtb::path_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, without);
       cudaFuncSetAttribute(rtb::path_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, without);
+      cudaFuncSetAttribute(rtb::path_kernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, without);
     }
   }
 #undef PUT
@@ -489,7 +544,7 @@ static int EnsurePool(RenderCtx* s, uint32_t pool, size_t n_waves) {
       }
       RTB_CUDA(alloc(reinterpret_cast<void**>(&wv.hit_t), (size_t)pool * 4));
       RTB_CUDA(alloc(reinterpret_cast<void**>(&wv.hit_ref), (size_t)pool * 4));
-      RTB_CUDA(alloc(reinterpret_cast<void**>(&wv.counts), 16));  // see Wave::counts
+      RTB_CUDA(alloc(reinterpret_cast<void**>(&wv.counts), 32));  // see Wave::counts
       RTB_CUDA(cudaMallocHost(reinterpret_cast<void**>(&wv.host_count), 64));
       RTB_CUDA(cudaStreamCreateWithFlags(&wv.stream, cudaStreamNonBlocking));
       RTB_CUDA(cudaEventCreateWithFlags(&wv.done, cudaEventDisableTiming));
@@ -503,7 +558,7 @@ static int EnsureFused(RenderCtx* s) {
   Wave& wv = s->fused;
   if (wv.stream) return RTB_OK;
   void* p = nullptr;
-  RTB_CUDA(cudaMalloc(&p, 16));
+  RTB_CUDA(cudaMalloc(&p, 32));
   wv.mem.push_back(p);
   wv.counts = static_cast<unsigned int*>(p);
   RTB_CUDA(cudaStreamCreateWithFlags(&wv.stream, cudaStreamNonBlocking));
@@ -532,8 +587,18 @@ static int EnsureOrder(RenderCtx* s, int w, int h) {
   return RTB_OK;
 }
 
-int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* prm, float* d_rgb_sum, RtbStats* stats) {
+}  // extern "C"
+
+// Both render entries.  `ad` != nullptr: adaptive per-pixel stop, path kernel with one work item per pixel.
+static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* prm, float* d_rgb_sum, const RtbAdaptive* ad, float* d_sumsq,
+                      uint32_t* d_count, RtbStats* stats) {
   if (!s || !cam || !prm || !d_rgb_sum) return Fail(RTB_EINVAL, "null argument");
+  if (ad) {
+    if (!d_sumsq || !d_count) return Fail(RTB_EINVAL, "adaptive render needs the sumsq and count planes");
+    if (prm->flags & (RTB_RENDER_WAVEFRONT | RTB_RENDER_SERIAL)) return Fail(RTB_EINVAL, "adaptive render runs on the path kernel only");
+    if (ad->criterion != RTB_ADAPT_PIXEL_STATE && ad->criterion != RTB_ADAPT_LUMINANCE) return Fail(RTB_EINVAL, "unknown adaptive criterion");
+    if (!(ad->rel_threshold >= 0.0f) || ad->min_samples < 1) return Fail(RTB_EINVAL, "bad adaptive parameters");
+  }
   if (cam->width <= 0 || cam->height <= 0 || prm->spp_end < prm->spp_begin || prm->max_depth < 0) return Fail(RTB_EINVAL, "bad camera / params");
   if (prm->mode != RTB_MODE_A && prm->mode != RTB_MODE_B) return Fail(RTB_EINVAL, "unknown estimator mode");
   int rc = EnsureInit();
@@ -567,6 +632,11 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   rcst.mode = prm->mode;
   rcst.spp_begin = prm->spp_begin;
   rcst.n_pixels = n_pixels;
+  rcst.spp_max = prm->spp_end - prm->spp_begin;
+  rcst.min_samples = ad ? ad->min_samples : 0;
+  rcst.criterion = ad ? ad->criterion : 0;
+  rcst.rel_threshold = ad ? ad->rel_threshold : 0.0f;
+  const rtb::AdaptivePlanes planes{d_sumsq, d_count};
   const bool use_smem = s->dev.n_top_pairs > 0 && ((prm->flags & RTB_RENDER_SMEM_TOP) || std::getenv("RTB_SMEM_TOP") != nullptr);
   const size_t ext_smem = (use_smem ? s->smem_bytes : 0) + kStackSmem;
   const int ext_grid = use_smem ? PersistentGrid(rtb::extend_kernel<true>, kTraceBlock, ext_smem) : PersistentGrid(rtb::extend_kernel<false>, kTraceBlock, ext_smem);
@@ -582,7 +652,13 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   RTB_CUDA(cudaEventCreate(&ev1));
   RTB_CUDA(cudaEventCreateWithFlags(&ev_ready, cudaEventDisableTiming));
   RTB_CUDA(cudaEventRecord(ev0, st));
-  if (!(prm->flags & RTB_RENDER_KEEP_ACCUM)) RTB_CUDA(cudaMemsetAsync(d_rgb_sum, 0, (size_t)n_pixels * 3 * sizeof(float), st));
+  if (!(prm->flags & RTB_RENDER_KEEP_ACCUM)) {
+    RTB_CUDA(cudaMemsetAsync(d_rgb_sum, 0, (size_t)n_pixels * 3 * sizeof(float), st));
+    if (ad) {
+      RTB_CUDA(cudaMemsetAsync(d_sumsq, 0, (size_t)n_pixels * 3 * sizeof(float), st));
+      RTB_CUDA(cudaMemsetAsync(d_count, 0, (size_t)n_pixels * sizeof(uint32_t), st));
+    }
+  }
 #ifdef RTB_COUNTERS
   RTB_CUDA(cudaMemsetAsync(s->counters, 0, sizeof(rtb::HitCounters), st));
 #endif
@@ -593,7 +669,7 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
     w.live = 0;
     w.cur = 0;
     w.pending = false;
-    RTB_CUDA(cudaMemsetAsync(w.counts, 0, 16, w.stream));
+    RTB_CUDA(cudaMemsetAsync(w.counts, 0, 32, w.stream));
   }
   unsigned long long generated = 0, rays = 0;
   uint32_t iterations = 0, launches = 0, drain_paths = 0;
@@ -605,7 +681,21 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   // max_depth == 0: GetPixel returns black without tracing (camera.h:149-151)
   const bool trace = prm->max_depth > 0 || prm->mode == RTB_MODE_B || cam->depth_camera;
   bool any = trace && !fused;
-  if (trace && fused) {
+  if (trace && fused && ad && total > 0) {
+    // one work item per pixel; the lane that takes a pixel runs its samples until the stop rule holds
+    Wave& w = *waves[0];
+    auto* rc64 = reinterpret_cast<unsigned long long*>(w.counts + 2);
+    const int grid = use_smem ? PersistentGrid(rtb::path_kernel<true, false, true>, kTraceBlock, ext_smem)
+                              : PersistentGrid(rtb::path_kernel<false, false, true>, kTraceBlock, ext_smem);
+    if (use_smem)
+      rtb::path_kernel<true, false, true><<<grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, n_pixels, 0u, 0u, rcst, ctx->pixel_order,
+                                                                                 d_rgb_sum, w.counts, rc64, s->counters, planes);
+    else
+      rtb::path_kernel<false, false, true><<<grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, n_pixels, 0u, 0u, rcst, ctx->pixel_order,
+                                                                                  d_rgb_sum, w.counts, rc64, s->counters, planes);
+    ++launches;
+    ++iterations;
+  } else if (trace && fused) {
     Wave& w = *waves[0];
     while (generated < total) {
       const uint32_t chunk = (uint32_t)std::min<unsigned long long>(total - generated, 1ull << 30);
@@ -614,10 +704,10 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
       auto* rc64 = reinterpret_cast<unsigned long long*>(w.counts + 2);
       if (use_smem)
         rtb::path_kernel<true, false><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, ctx->pixel_order,
-                                                                                  d_rgb_sum, w.counts, rc64, s->counters);
+                                                                                  d_rgb_sum, w.counts, rc64, s->counters, planes);
       else
         rtb::path_kernel<false, false><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, ctx->pixel_order,
-                                                                                   d_rgb_sum, w.counts, rc64, s->counters);
+                                                                                   d_rgb_sum, w.counts, rc64, s->counters, planes);
       generated += chunk;
       ++launches;
       ++iterations;
@@ -657,10 +747,10 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
           auto* rc64 = reinterpret_cast<unsigned long long*>(w.counts + 2);
           if (use_smem)
             rtb::path_kernel<true, true><<<path_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, 0u, 0u, rcst, ctx->pixel_order, d_rgb_sum,
-                                                                               w.counts, rc64, s->counters);
+                                                                               w.counts, rc64, s->counters, planes);
           else
             rtb::path_kernel<false, true><<<path_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, 0u, 0u, rcst, ctx->pixel_order, d_rgb_sum,
-                                                                                w.counts, rc64, s->counters);
+                                                                                w.counts, rc64, s->counters, planes);
           if (serial) RTB_CUDA(cudaEventRecord(d1, ws));
           if (trace_iters) std::fprintf(stderr, "[rtb drain] %u paths\n", w.live);
           drain_paths += w.live;
@@ -709,9 +799,10 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   RTB_CUDA(cudaEventSynchronize(ev1));
   RTB_CUDA(cudaGetLastError());
   for (Wave* wp : waves) {  // rays traced inside the path kernel (it bounces on the device)
-    unsigned long long c = 0;
-    RTB_CUDA(cudaMemcpy(&c, wp->counts + 2, 8, cudaMemcpyDeviceToHost));
-    rays += c;
+    unsigned long long c[2] = {0, 0};
+    RTB_CUDA(cudaMemcpy(c, wp->counts + 2, 16, cudaMemcpyDeviceToHost));
+    rays += c[0];
+    if (ad) generated += c[1];
   }
   for (auto& de : drain_events) {
     float d = 0.f;
@@ -758,20 +849,104 @@ int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   return RTB_OK;
 }
 
+extern "C" {
+
+int rtb_render_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* prm, float* d_rgb_sum, RtbStats* stats) {
+  return RenderImpl(s, cam, prm, d_rgb_sum, nullptr, nullptr, nullptr, stats);
+}
+
+int rtb_render_adaptive_device(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* prm, const RtbAdaptive* ad, float* d_rgb_sum,
+                               float* d_rgb_sumsq, uint32_t* d_count, RtbStats* stats) {
+  if (!ad) return Fail(RTB_EINVAL, "null argument");
+  return RenderImpl(s, cam, prm, d_rgb_sum, ad, d_rgb_sumsq, d_count, stats);
+}
+
 int rtb_render(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* prm, float* rgb_sum, RtbStats* stats) {
   if (!s || !cam || !prm || !rgb_sum) return Fail(RTB_EINVAL, "null argument");
   int rc = EnsureInit();
   if (rc != RTB_OK) return rc;
   const size_t bytes = (size_t)cam->width * cam->height * 3 * sizeof(float);
-  float* d = nullptr;
-  RTB_CUDA(cudaMalloc(reinterpret_cast<void**>(&d), bytes));
-  if (prm->flags & RTB_RENDER_KEEP_ACCUM) cudaMemcpy(d, rgb_sum, bytes, cudaMemcpyHostToDevice);
+  if (g_ctx.accum_bytes < bytes) {
+    if (g_ctx.accum) cudaFree(g_ctx.accum);
+    g_ctx.accum = nullptr;
+    g_ctx.accum_bytes = 0;
+    RTB_CUDA(cudaMalloc(reinterpret_cast<void**>(&g_ctx.accum), bytes));
+    g_ctx.accum_bytes = bytes;
+  }
+  float* d = g_ctx.accum;
+  if (prm->flags & RTB_RENDER_KEEP_ACCUM) RTB_CUDA(cudaMemcpy(d, rgb_sum, bytes, cudaMemcpyHostToDevice));
   rc = rtb_render_device(s, cam, prm, d, stats);
+  if (rc != RTB_OK) return rc;
+  RTB_CUDA(cudaMemcpy(rgb_sum, d, bytes, cudaMemcpyDeviceToHost));
+  return RTB_OK;
+}
+
+int rtb_render_adaptive(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* prm, const RtbAdaptive* ad, float* rgb_sum, float* rgb_sumsq,
+                        uint32_t* count, RtbStats* stats) {
+  if (!s || !cam || !prm || !ad || !rgb_sum || !count) return Fail(RTB_EINVAL, "null argument");
+  if (cam->width <= 0 || cam->height <= 0) return Fail(RTB_EINVAL, "bad camera / params");
+  int rc = EnsureInit();
+  if (rc != RTB_OK) return rc;
+  const size_t n_pix = (size_t)cam->width * cam->height, fb = n_pix * 3 * sizeof(float);
+  char* d = nullptr;  // [sum | sumsq | count]
+  RTB_CUDA(cudaMalloc(reinterpret_cast<void**>(&d), 2 * fb + n_pix * 4));
+  float* d_sum = reinterpret_cast<float*>(d);
+  float* d_sq = reinterpret_cast<float*>(d + fb);
+  uint32_t* d_cnt = reinterpret_cast<uint32_t*>(d + 2 * fb);
   cudaError_t e = cudaSuccess;
-  if (rc == RTB_OK) e = cudaMemcpy(rgb_sum, d, bytes, cudaMemcpyDeviceToHost);
+  if (prm->flags & RTB_RENDER_KEEP_ACCUM) {
+    if (!rgb_sumsq) {
+      cudaFree(d);
+      return Fail(RTB_EINVAL, "continuing an adaptive render needs its sumsq plane");
+    }
+    e = cudaMemcpy(d_sum, rgb_sum, fb, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_sq, rgb_sumsq, fb, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_cnt, count, n_pix * 4, cudaMemcpyHostToDevice);
+  }
+  if (e == cudaSuccess) {
+    rc = RenderImpl(s, cam, prm, d_sum, ad, d_sq, d_cnt, stats);
+    if (rc == RTB_OK) e = cudaMemcpy(rgb_sum, d_sum, fb, cudaMemcpyDeviceToHost);
+    if (rc == RTB_OK && e == cudaSuccess && rgb_sumsq) e = cudaMemcpy(rgb_sumsq, d_sq, fb, cudaMemcpyDeviceToHost);
+    if (rc == RTB_OK && e == cudaSuccess) e = cudaMemcpy(count, d_cnt, n_pix * 4, cudaMemcpyDeviceToHost);
+  }
   cudaFree(d);
   if (rc != RTB_OK) return rc;
-  if (e != cudaSuccess) return Fail(RTB_ECUDA, std::string("render readback: ") + cudaGetErrorString(e));
+  if (e != cudaSuccess) return Fail(RTB_ECUDA, std::string("adaptive render copies: ") + cudaGetErrorString(e));
+  return RTB_OK;
+}
+
+int rtb_resolve_counts_device(const float* d_rgb_sum, const uint32_t* d_count, size_t n_pixels, uint8_t* d_rgb8, void* stream) {
+  if (!d_rgb_sum || !d_count || !d_rgb8) return Fail(RTB_EINVAL, "bad argument");
+  int rc = EnsureInit();
+  if (rc != RTB_OK) return rc;
+  cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : g_stream;
+  const size_t n = n_pixels * 3;
+  if (n) rtb::resolve_counts_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d_rgb_sum, d_count, n, d_rgb8);
+  RTB_CUDA(cudaGetLastError());
+  return RTB_OK;
+}
+
+int rtb_resolve_counts(const float* rgb_sum, const uint32_t* count, size_t n_pixels, uint8_t* rgb8) {
+  if (!rgb_sum || !count || !rgb8) return Fail(RTB_EINVAL, "bad argument");
+  int rc = EnsureInit();
+  if (rc != RTB_OK) return rc;
+  const size_t n = n_pixels * 3;
+  if (n == 0) return RTB_OK;
+  char* d = nullptr;  // [sum | count | bytes]
+  RTB_CUDA(cudaMalloc(reinterpret_cast<void**>(&d), n * 4 + n_pixels * 4 + n));
+  float* d_sum = reinterpret_cast<float*>(d);
+  uint32_t* d_cnt = reinterpret_cast<uint32_t*>(d + n * 4);
+  uint8_t* d_out = reinterpret_cast<uint8_t*>(d + n * 4 + n_pixels * 4);
+  cudaError_t e = cudaMemcpyAsync(d_sum, rgb_sum, n * 4, cudaMemcpyHostToDevice, g_stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(d_cnt, count, n_pixels * 4, cudaMemcpyHostToDevice, g_stream);
+  if (e == cudaSuccess) {
+    rc = rtb_resolve_counts_device(d_sum, d_cnt, n_pixels, d_out, g_stream);
+    if (rc == RTB_OK) e = cudaMemcpyAsync(rgb8, d_out, n, cudaMemcpyDeviceToHost, g_stream);
+    if (rc == RTB_OK && e == cudaSuccess) e = cudaStreamSynchronize(g_stream);
+  }
+  cudaFree(d);
+  if (rc != RTB_OK) return rc;
+  if (e != cudaSuccess) return Fail(RTB_ECUDA, std::string("resolve_counts: ") + cudaGetErrorString(e));
   return RTB_OK;
 }
 

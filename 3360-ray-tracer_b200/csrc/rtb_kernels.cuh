@@ -21,6 +21,12 @@ struct RenderConsts {
   int mode;
   int spp_begin;
   uint32_t n_pixels;
+  // adaptive rendering (path_kernel<.., kAdaptive = true>): the per-pixel stop of PixelState::IsConverged
+  // (pixel_state.h:53-72) or of a repaired AdaptiveSampler (sampler.h:46-76)
+  int spp_max;        // samples per pixel this call may add at most
+  int min_samples;
+  int criterion;      // RTB_ADAPT_*
+  float rel_threshold;
 };
 
 // Stage the breadth-first top of the tree in shared memory (one copy per CTA per launch).
@@ -340,12 +346,8 @@ struct PathState {  // what a path carries besides its ray
 
 // A call's samples are numbered g = s_local * n_pixels + pl; callers pass (s0, p0) = divmod(g0, n_pixels) of their first
 // sample and a 32-bit offset i, so the device never divides 64-bit numbers.
-__device__ __forceinline__ void generate_sample(const RenderConsts& rc, const uint32_t* __restrict__ pixel_order, uint32_t s0, uint32_t p0,
-                                                uint32_t i, float4& ro, float4& rd, PathState& ps) {
-  const uint32_t t = p0 + i;  // < 2^31: p0 < n_pixels <= 2^30 and i < 2^30 (host-side chunking)
-  const uint32_t s_local = s0 + t / rc.n_pixels, pl = t % rc.n_pixels;
-  const uint32_t pixel = __ldg(&pixel_order[pl]);
-  const uint32_t sample = (uint32_t)rc.spp_begin + s_local;
+// Camera::GetRay for global sample `sample` of `pixel`: Philox(pixel, sample, stream -1) -> jitter + lens point.
+__device__ __forceinline__ void camera_ray(const RenderConsts& rc, uint32_t pixel, uint32_t sample, float4& ro, float4& rd, PathState& ps) {
   const int px = (int)(pixel % (uint32_t)rc.cam.width), py = (int)(pixel / (uint32_t)rc.cam.width);
   const uint4 rnd = philox4x32_10(make_uint4(pixel, sample, 0xffffffffu, 0u), rc.key);
   const RtbCamera& c = rc.cam;
@@ -371,6 +373,13 @@ __device__ __forceinline__ void generate_sample(const RenderConsts& rc, const ui
   ps.pixel = pixel;
   ps.sample = sample;
   ps.bounce = 0u;
+}
+
+__device__ __forceinline__ void generate_sample(const RenderConsts& rc, const uint32_t* __restrict__ pixel_order, uint32_t s0, uint32_t p0,
+                                                uint32_t i, float4& ro, float4& rd, PathState& ps) {
+  const uint32_t t = p0 + i;  // < 2^31: p0 < n_pixels <= 2^30 and i < 2^30 (host-side chunking)
+  const uint32_t s_local = s0 + t / rc.n_pixels, pl = t % rc.n_pixels;
+  camera_ray(rc, __ldg(&pixel_order[pl]), (uint32_t)rc.spp_begin + s_local, ro, rd, ps);
 }
 
 // Slot q_offset + k of the queue receives local sample g0 + k, g0 = s0 * n_pixels + p0.
@@ -430,7 +439,18 @@ __device__ __forceinline__ void add_radiance(float* accum, uint32_t pixel, f3 L)
   if (L.z != 0.0f) atomicAdd(a + 2, L.z);
 }
 
-__device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts& rc, float* accum, float4& ro, float4& rd, PathState& ps,
+// Where a finished path's radiance goes.  A path contributes at most once, when it terminates.
+struct AtomicSink {  // shared accumulator: samples of one pixel finish on different lanes
+  float* accum;
+  __device__ __forceinline__ void add(uint32_t pixel, f3 L) { add_radiance(accum, pixel, L); }
+};
+struct LocalSink {  // adaptive mode: the lane owns its pixel and records the sample itself
+  f3 L;
+  __device__ __forceinline__ void add(uint32_t, f3 v) { L = v; }
+};
+
+template <class Sink>
+__device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts& rc, Sink& sink, float4& ro, float4& rd, PathState& ps,
                                            float hit_t, uint32_t ref) {
   bool alive = false;
   const f3 d = mk3(rd.x, rd.y, rd.z);
@@ -440,9 +460,9 @@ __device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts
   if (rc.cam.depth_camera) {
     // DepthCamera::GetPixel (camera.h:217-236): t of the normalised ray in red, black past max_dist 20 / on a miss
     const float t = hit_t;
-    if (ref != kNoHit && t < 20.0f) add_radiance(accum, pixel, mk3(t, 0.0f, 0.0f));
+    if (ref != kNoHit && t < 20.0f) sink.add(pixel, mk3(t, 0.0f, 0.0f));
   } else if (ref == kNoHit || (rc.mode == RTB_MODE_B && (int)bounce >= rc.max_depth)) {
-    add_radiance(accum, pixel, thr * sky(d));  // camera.h:171-173 / wavefront.cc:122-129
+    sink.add(pixel, thr * sky(d));  // camera.h:171-173 / wavefront.cc:122-129
   } else {
     const float t = hit_t;
     const f3 p = mk3(fmaf(t, d.x, ro.x), fmaf(t, d.y, ro.y), fmaf(t, d.z, ro.z));
@@ -475,7 +495,7 @@ __device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts
         dir = (cannot_refract || schlick(cos_theta, eta) > u01(rnd.z)) ? reflect3(ud, nrm) : refract3(ud, nrm, eta);
         alive = true;
       } else {  // DiffuseLight: emits, never scatters (material.cc:273-280,312-316)
-        add_radiance(accum, pixel, thr * texture_value(s, m.tex, u, v, p, on_sphere, n_out));
+        sink.add(pixel, thr * texture_value(s, m.tex, u, v, p, on_sphere, n_out));
       }
       ps.tr = thr.x * atten.x; ps.tg = thr.y * atten.y; ps.tb = thr.z * atten.z;
       // the recursion bottoms out in black when depth reaches 0 (camera.h:149-151)
@@ -487,7 +507,7 @@ __device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts
       const bool near_zero = fabsf(emitted.x) < 1e-8f && fabsf(emitted.y) < 1e-8f && fabsf(emitted.z) < 1e-8f;
       f3 tp = thr;
       if (!near_zero) {
-        add_radiance(accum, pixel, thr * emitted);  // wavefront.cc:134-142
+        sink.add(pixel, thr * emitted);  // wavefront.cc:134-142
       } else if (m.type == RTB_MAT_LAMBERTIAN) {
         // Lambertian::Sample (material.cc:57-74): cosine direction, f = albedo/pi, pdf = cos/pi;
         // wavefront.cc:176-186 multiplies by f*cos/pdf = albedo.  RandomCosineDirection math_utils.h:104-123.
@@ -554,7 +574,14 @@ __device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts
 #ifndef RTB_PATH_MIN_BLOCKS
 #define RTB_PATH_MIN_BLOCKS 4  // 64 registers: measured faster than 3 x 80 or 2 x 128 despite the spills
 #endif
-template <bool kFromQueue>
+// Adaptive state of a render (kAdaptive): per-pixel planes owned by the caller.  The lane that takes a pixel is
+// its only writer, so the planes are updated with plain loads and stores.
+struct AdaptivePlanes {
+  float* sumsq;      // W*H*3: sum of squared sample radiance (PixelState::m2 in its sum-of-squares form)
+  uint32_t* count;   // W*H: samples recorded (PixelState::samples)
+};
+
+template <bool kFromQueue, bool kAdaptive>
 struct PathIo {
   static constexpr int kServiceLanes = RTB_PATH_REFILL_LANES;
   uint32_t n;
@@ -566,6 +593,8 @@ struct PathIo {
   uint32_t s0, p0;  // divmod(first sample of this launch, n_pixels)
   const uint32_t* pixel_order;
   PathState ps;
+  AdaptivePlanes ad;
+  unsigned samples;  // adaptive: camera samples started by this lane
   __device__ __forceinline__ void load(uint32_t i, float4& o, float4& d) {
     if (kFromQueue) {
       o = q.ro[i];
@@ -576,6 +605,11 @@ struct PathIo {
       ps.pixel = __float_as_uint(th.w);
       ps.sample = meta.x;
       ps.bounce = meta.y;
+    } else if (kAdaptive) {
+      // work item = a pixel; its samples run one after the other on this lane
+      const uint32_t pixel = __ldg(&pixel_order[i]);
+      camera_ray(rc, pixel, (uint32_t)rc.spp_begin, o, d, ps);
+      ++samples;
     } else {
       generate_sample(rc, pixel_order, s0, p0, i, o, d, ps);
     }
@@ -583,21 +617,68 @@ struct PathIo {
   __device__ __forceinline__ bool finish(uint32_t, uint32_t ref, float tf, const TravRay& r, float4& o, float4& d) {
     o = make_float4(r.ox, r.oy, r.oz, r.tmin);
     d = make_float4(r.dx, r.dy, r.dz, r.tmax);
-    return shade_path(s, rc, accum, o, d, ps, tf, ref);
+    if (!kAdaptive) {
+      AtomicSink sink{accum};
+      return shade_path(s, rc, sink, o, d, ps, tf, ref);
+    }
+    LocalSink sink{mk3(0.0f, 0.0f, 0.0f)};
+    if (shade_path(s, rc, sink, o, d, ps, tf, ref)) return true;
+    // ---- RecordSample + IsConverged (pixel_state.h:22-72) for the pixel this lane owns
+    const uint32_t pixel = ps.pixel;
+    float* a = accum + 3 * (size_t)pixel;
+    float* q2 = ad.sumsq + 3 * (size_t)pixel;
+    const uint32_t prev = ad.count[pixel];
+    const uint32_t k = ps.sample - (uint32_t)rc.spp_begin + 1u;  // samples of this call, this one included
+    const float n = (float)(prev + k);
+    const float sx = a[0] + sink.L.x, sy = a[1] + sink.L.y, sz = a[2] + sink.L.z;
+    const float qx = q2[0] + sink.L.x * sink.L.x, qy = q2[1] + sink.L.y * sink.L.y, qz = q2[2] + sink.L.z * sink.L.z;
+    a[0] = sx; a[1] = sy; a[2] = sz;
+    q2[0] = qx; q2[1] = qy; q2[2] = qz;
+    bool stop = (int)k >= rc.spp_max;
+    if (!stop && (int)(prev + k) >= rc.min_samples) {
+      const float inv_n = 1.0f / n;
+      const float mx = sx * inv_n, my = sy * inv_n, mz = sz * inv_n;
+      if (rc.criterion == RTB_ADAPT_PIXEL_STATE) {
+        // per channel: sqrt(s^2 / n) / max(|mean|, 1e-3) <= threshold, s^2 the sample variance m2 / (n - 1)
+        const float inv_n1 = 1.0f / fmaxf(n - 1.0f, 1.0f);
+        const float vx = fmaxf(qx - sx * mx, 0.0f) * inv_n1, vy = fmaxf(qy - sy * my, 0.0f) * inv_n1, vz = fmaxf(qz - sz * mz, 0.0f) * inv_n1;
+        const float tx = rc.rel_threshold * fmaxf(fabsf(mx), 1e-3f), ty = rc.rel_threshold * fmaxf(fabsf(my), 1e-3f),
+                    tz = rc.rel_threshold * fmaxf(fabsf(mz), 1e-3f);
+        stop = vx * inv_n <= tx * tx && vy * inv_n <= ty * ty && vz * inv_n <= tz * tz;
+      } else {
+        // AdaptiveSampler (sampler.h:61-71) with the running-total slip repaired: luminance of the population
+        // variance against the mean luminance
+        const float vx = qx * inv_n - mx * mx, vy = qy * inv_n - my * my, vz = qz * inv_n - mz * mz;
+        const float lum_v = fmaxf(0.2126f * vx + 0.7152f * vy + 0.0722f * vz, 0.0f);
+        const float lum_m = 0.2126f * mx + 0.7152f * my + 0.0722f * mz;
+        stop = sqrtf(lum_v * inv_n) < rc.rel_threshold * (lum_m + 1e-3f);
+      }
+    }
+    if (stop) {
+      ad.count[pixel] = prev + k;
+      return false;
+    }
+    camera_ray(rc, pixel, ps.sample + 1u, o, d, ps);
+    ++samples;
+    return true;
   }
 };
 
-template <bool kUseSmem, bool kFromQueue>
+template <bool kUseSmem, bool kFromQueue, bool kAdaptive = false>
 __global__ void __launch_bounds__(kTraceBlock, RTB_PATH_MIN_BLOCKS) path_kernel(DevScene s, PathQueue q, uint32_t n, uint32_t s0, uint32_t p0,
                                                                                RenderConsts rc, const uint32_t* __restrict__ pixel_order,
                                                                                float* accum, unsigned int* cursor,
-                                                                               unsigned long long* ray_count, HitCounters* cnt) {
+                                                                               unsigned long long* ray_count, HitCounters* cnt, AdaptivePlanes ad) {
   extern __shared__ float4 smem_pairs[];
   if (kUseSmem) stage_top(s, smem_pairs);
-  PathIo<kFromQueue> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathState{}};
+  PathIo<kFromQueue, kAdaptive> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathState{}, ad, 0u};
   trace_loop<kUseSmem>(s, smem_pairs, smem_stack_base(s, smem_pairs, kUseSmem), io, cursor, cnt);
   const unsigned total = __reduce_add_sync(kFull, io.rays);
   if ((threadIdx.x & 31u) == 0u && total) atomicAdd(ray_count, (unsigned long long)total);
+  if (kAdaptive) {
+    const unsigned started = __reduce_add_sync(kFull, io.samples);
+    if ((threadIdx.x & 31u) == 0u && started) atomicAdd(ray_count + 1, (unsigned long long)started);
+  }
 }
 
 // Wavefront form: one thread per queue entry; survivors are appended to `out` with one atomicAdd
@@ -618,7 +699,8 @@ __global__ void __launch_bounds__(256) shade_kernel(DevScene s, PathQueue in, ui
     ps.pixel = __float_as_uint(th.w);
     ps.sample = meta.x;
     ps.bounce = meta.y;
-    alive = shade_path(s, rc, accum, ro, rd, ps, hit_t[i], hit_ref[i]);
+    AtomicSink sink{accum};
+    alive = shade_path(s, rc, sink, ro, rd, ps, hit_t[i], hit_ref[i]);
   }
   // ---- compact: ballot + prefix inside the warp, one atomic per warp
   const unsigned ballot = __ballot_sync(0xffffffffu, alive);
@@ -642,6 +724,19 @@ __global__ void resolve_kernel(const float* __restrict__ rgb_sum, size_t n_value
   const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   if (i >= n_values) return;
   const double lin = (double)rgb_sum[i] * inv_spp;
+  double g = lin > 0 ? sqrt(lin) : 0.0;
+  g = g < 0.0 ? 0.0 : (g > 0.999 ? 0.999 : g);
+  rgb8[i] = (uint8_t)(int)(256 * g);
+}
+
+// adaptive form: mean = sum / count of the pixel, black where nothing was recorded (wavefront.cc:229-234)
+__global__ void resolve_counts_kernel(const float* __restrict__ rgb_sum, const uint32_t* __restrict__ count, size_t n_values,
+                                      uint8_t* __restrict__ rgb8) {
+  const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i >= n_values) return;
+  const uint32_t c = count[i / 3];
+  // PixelState::sum is double and is divided by (float)samples: the quotient is a double division
+  const double lin = c ? (double)rgb_sum[i] / (double)(float)c : 0.0;
   double g = lin > 0 ? sqrt(lin) : 0.0;
   g = g < 0.0 ? 0.0 : (g > 0.999 ? 0.999 : g);
   rgb8[i] = (uint8_t)(int)(256 * g);

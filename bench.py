@@ -281,10 +281,12 @@ def main():
     import ctypes as C
     host_img = torch.empty(n_pix * 3, dtype=torch.float32).pin_memory()
     KE = min(K, 10)
+    e2e_parts = []
     for k in range(min(W, 1) + KE):
         barrier()
         t0 = time.perf_counter()
         ds2 = rt.DeviceScene(hs, device=local_rank)  # rtb_scene_create: copies every scene array host -> device
+        t_created = time.perf_counter()
         if world == 1:
             prm = rt.binding.RtbRenderParams(0, spp, depth, mode, 0x3360, args.pool, base_flags)
             s2 = rt.binding.RtbStats()
@@ -294,10 +296,13 @@ def main():
             dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
             if rank == 0:
                 host_img.copy_(accum, non_blocking=False)
+        t_rendered = time.perf_counter()
         ds2.close()
         torch.cuda.synchronize()
         if k >= min(W, 1):
-            e2e_ms.append(1e3 * (time.perf_counter() - t0))
+            t_end = time.perf_counter()
+            e2e_ms.append(1e3 * (t_end - t0))
+            e2e_parts.append((1e3 * (t_created - t0), 1e3 * (t_rendered - t_created), 1e3 * (t_end - t_rendered)))
     e2e_tot = torch.tensor([sum(e2e_ms)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(e2e_tot, op=dist.ReduceOp.MAX)
@@ -321,6 +326,7 @@ def main():
                        "scene_build_s_untimed": round(t_build, 3)},
             "e2e": {"value": samples_per_step / (e2e_tot.item() / KE * 1e-3) / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_tot.item() / KE, "steps": KE,
+                    "ms_parts_rank0": dict(zip(("scene_create", "render_and_readback", "scene_destroy"), (float(x) for x in np.mean(e2e_parts, axis=0)))),
                     "what": "rtb_scene_create (all scene arrays H2D) + rtb_render with a host rgb buffer (D2H) + rtb_scene_destroy, wall clock"},
             "gpu_launches": int(sum(s["launches"] for s in stats) + K),
             "other_pipeline": {"name": "path" if args.pipeline == "wavefront" else "wavefront", "ms_per_step": float(np.mean(other_ms)),

@@ -218,6 +218,23 @@ typedef struct RtbStats {
   uint32_t drain_paths; /* paths handed to it */
 } RtbStats;
 
+/* Adaptive sampling.  Every pixel takes samples spp_begin, spp_begin+1, ... until its stop rule
+ * holds or spp_end is reached; the rule is evaluated after every recorded sample once min_samples are in.
+ *   RTB_ADAPT_PIXEL_STATE  integrator::IsConverged (src/integrator/pixel_state.h:53-72), what
+ *                          WavefrontRenderer::Render applies with kRelThresh 0.05 / kMinSamples 16
+ *                          (src/renderer/wavefront.cc:42-43): per channel, standard error of the mean
+ *                          sqrt(s^2/n) over max(|mean|, 1e-3) <= rel_threshold, s^2 = m2/(n-1).
+ *   RTB_ADAPT_LUMINANCE    integrator::AdaptiveSampler (src/integrator/sampler.h:46-76) as it was meant (its
+ *                          `sum += pixel` adds the running total; here the sample): sqrt(lum(E[x^2]-mean^2)/n)
+ *                          / (lum(mean) + 1e-3) < rel_threshold, lum = core::luminance (src/core/color.h:35-37). */
+enum { RTB_ADAPT_PIXEL_STATE = 0, RTB_ADAPT_LUMINANCE = 1 };
+typedef struct RtbAdaptive {
+  float rel_threshold;
+  int32_t min_samples;
+  int32_t criterion; /* RTB_ADAPT_* */
+  int32_t pad;
+} RtbAdaptive;
+
 typedef struct RtbScene RtbScene; /* opaque; owns all device memory of one scene on one GPU */
 
 const char* rtb_last_error(void);
@@ -249,6 +266,19 @@ int rtb_render(RtbScene* scene, const RtbCamera* cam, const RtbRenderParams* par
  * following ncclReduce sums across GPUs). Synchronous on return. */
 int rtb_render_device(RtbScene* scene, const RtbCamera* cam, const RtbRenderParams* params,
                       float* d_rgb_sum, RtbStats* stats);
+
+/* seam 1, adaptive: as rtb_render, plus the per-pixel state of integrator::PixelState (pixel_state.h:13-19) in
+ * planes: rgb_sum (W*H*3, PixelState::sum), rgb_sumsq (W*H*3, sum of squares: m2 = sumsq - sum^2/n) and count
+ * (W*H, PixelState::samples).  The image is rgb_sum / count (wavefront.cc:229-234) - rtb_resolve_counts.
+ * Without RTB_RENDER_KEEP_ACCUM the three planes are zeroed first; with it the call continues them (every pixel
+ * takes at least one more sample).  RtbStats.samples = camera samples actually started.  Path kernel only. */
+int rtb_render_adaptive(RtbScene* scene, const RtbCamera* cam, const RtbRenderParams* params, const RtbAdaptive* adaptive,
+                        float* rgb_sum, float* rgb_sumsq, uint32_t* count, RtbStats* stats);
+int rtb_render_adaptive_device(RtbScene* scene, const RtbCamera* cam, const RtbRenderParams* params, const RtbAdaptive* adaptive,
+                               float* d_rgb_sum, float* d_rgb_sumsq, uint32_t* d_count, RtbStats* stats);
+/* write_color of rgb_sum / count per pixel (black where count is 0, wavefront.cc:229-234). */
+int rtb_resolve_counts_device(const float* d_rgb_sum, const uint32_t* d_count, size_t n_pixels, uint8_t* d_rgb8, void* stream);
+int rtb_resolve_counts(const float* rgb_sum, const uint32_t* count, size_t n_pixels, uint8_t* rgb8);
 
 /* core::write_color (src/core/color.h:18-33): mean -> sqrt gamma -> clamp
  * [0,0.999] -> int(256 x); done in double like the reference.  Device in/out. */

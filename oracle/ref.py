@@ -36,6 +36,8 @@ def _load(fast: bool):
     lib.ora_render_a.restype = C.c_double
     lib.ora_render_a.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                  C.c_void_p, C.c_void_p, C.c_int]
+    lib.ora_render_b.restype = C.c_double
+    lib.ora_render_b.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
     lib.ora_texture_value.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]
     _LIBS[fast] = lib
     return lib
@@ -105,6 +107,19 @@ class RefScene:
         rays = C.c_uint64()
         secs = self.lib.ora_render_a(self.h, _p(cfg), spp, max_depth, seed, threads, y0, y1, _p(mean), _p(m2), C.byref(rays), int(depth_camera))
         return mean, m2, secs, rays.value
+
+    def render_b(self, cfg16: np.ndarray, max_depth: int, max_samples: int, seed: int = 1, threads: int = 0):
+        """Path B as shipped (WavefrontRenderer::Render over CPURayIntegrator, adaptive stop 0.05 / 16):
+        rgb8[h,w,3] parsed from its P3 output, active[s] = pixels still sampling in pass s, seconds."""
+        cfg = np.ascontiguousarray(cfg16, np.float64)
+        w, h = C.c_int(), C.c_int()
+        self.lib.ora_camera_dims(_p(cfg), C.byref(w), C.byref(h))
+        rgb8 = np.zeros((h.value, w.value, 3), np.uint8)
+        active = np.zeros(max_samples, np.int32)
+        secs = self.lib.ora_render_b(self.h, _p(cfg), max_depth, max_samples, seed, threads, _p(rgb8), _p(active), max_samples)
+        if secs < 0:
+            raise RuntimeError("oracle: could not parse the reference's P3 output")
+        return rgb8, active, secs
 
     def texture_value(self, tex_id: int, uvp: np.ndarray) -> np.ndarray:
         q = np.ascontiguousarray(uvp, np.float64).reshape(-1, 5)

@@ -12,7 +12,10 @@
 //       Bvh::Hit itself by ora_intersect_world(),
 //   (3) the MegaKernel/DefaultSampler pixel loop (src/renderer/mega_kernel.h:15-54,
 //       src/integrator/sampler.h:26-34) with float outputs (mean and M2) instead of 8-bit PPM,
-//       seeded per thread with core::SeedRng (src/core/random.h:46-48), and timed.
+//       seeded per thread with core::SeedRng (src/core/random.h:46-48), and timed,
+//   (4) ora_render_b: the reference's WavefrontRenderer::Render (src/renderer/wavefront.cc:40-242) run AS IS with
+//       its CPURayIntegrator; std::cout / std::clog are captured, the P3 bytes and the per-pass "queue=" sizes
+//       (= pixels not yet converged, wavefront.cc:62-82) are returned.
 #include <omp.h>
 
 #include <chrono>
@@ -23,7 +26,12 @@
 #include <unordered_map>
 #include <vector>
 
+#include <iostream>
+#include <sstream>
+
 #include "core/random.h"
+#include "integrator/cpu_ray_integrator.h"
+#include "renderer/wavefront.h"
 #include "geom/bvh.h"
 #include "geom/rect.h"
 #include "geom/sphere.h"
@@ -354,6 +362,49 @@ double ora_render_a(void* h, const double* cfg, int spp, int max_depth, unsigned
   }
   const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   if (rays_out) *rays_out = rays;
+  return secs;
+}
+
+// Path B exactly as the reference's main() runs it (main.cc:188-194): WavefrontRenderer over CPURayIntegrator.
+// rgb8: W*H*3 bytes parsed from the P3 text it writes; queue_sizes[s] = rays generated in pass s (one per
+// pixel that has not converged), up to n_queue entries.  Returns seconds, < 0 on a parse failure.
+double ora_render_b(void* h, const double* cfg, int max_depth, int max_samples, unsigned seed, int threads, uint8_t* rgb8,
+                    int32_t* queue_sizes, int n_queue) {
+  const OraScene& s = *static_cast<OraScene*>(h);
+  scene::ColorCamera cam;
+  SetupCamera(cam, cfg);
+  if (threads > 0) omp_set_num_threads(threads);
+#pragma omp parallel
+  core::SeedRng(seed * 7919u + 104729u * unsigned(omp_get_thread_num()) + 1u);
+  integrator::CPURayIntegrator integ(&s.world);
+  renderer::WavefrontRenderer wf(s.world, cam, integ, max_depth, max_samples, 8192);
+  std::ostringstream out, log;
+  std::streambuf* old_out = std::cout.rdbuf(out.rdbuf());
+  std::streambuf* old_log = std::clog.rdbuf(log.rdbuf());
+  const auto t0 = std::chrono::steady_clock::now();
+  wf.Render();
+  const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  std::cout.rdbuf(old_out);
+  std::clog.rdbuf(old_log);
+  std::istringstream in(out.str());
+  std::string magic;
+  int w = 0, hh = 0, maxv = 0;
+  in >> magic >> w >> hh >> maxv;
+  if (magic != "P3" || w != cam.get_image_width() || hh != cam.get_image_height()) return -1.0;
+  for (size_t i = 0; i < size_t(w) * hh * 3; ++i) {
+    int v = -1;
+    in >> v;
+    if (v < 0 || v > 255) return -2.0;
+    rgb8[i] = uint8_t(v);
+  }
+  const std::string text = log.str();
+  size_t pos = 0;
+  for (int k = 0; k < n_queue; ++k) {
+    pos = text.find("queue=", pos);
+    if (pos == std::string::npos) { queue_sizes[k] = -1; continue; }
+    pos += 6;
+    queue_sizes[k] = int32_t(std::strtol(text.c_str() + pos, nullptr, 10));
+  }
   return secs;
 }
 
