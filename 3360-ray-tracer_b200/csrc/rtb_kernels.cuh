@@ -89,6 +89,18 @@ __device__ __forceinline__ float4 ld_pair_global(unsigned long long addr) {
   return v;
 }
 
+// 256-bit global load (sm_100: LDG.E.256).  The L1 of an SM retires about one wavefront (instruction x distinct
+// 128-byte line) per cycle, and a traversal step of 32 diverged lanes touches 32 lines PER LOAD INSTRUCTION: the
+// 64-byte pair record costs 4 x 32 wavefronts as 3 x LD.128 + LD.64, 2 x 32 as 2 x LD.256.
+#ifndef RTB_LD256
+#define RTB_LD256 1
+#endif
+__device__ __forceinline__ void ld256_global(unsigned long long addr, float (&v)[8]) {
+  asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+      : "l"(addr));
+}
+
 // Per-thread traversal stack: the first kSmemStack entries in shared memory, laid out [entry][thread]
 // so that any mix of stack depths across a warp is bank-conflict free; deeper entries in local memory.
 struct TravStack {
@@ -151,7 +163,13 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
     // record = {lo0.xyz hi0.xyz lo1.xyz hi1.xyz desc0 desc1 - -}
     float4 q0, q1, q2;
     uint2 dd;
-    if (kUseSmem) {
+    if (!kUseSmem && RTB_LD256) {
+      float a[8], c[8];
+      ld256_global(addr, a);
+      ld256_global(addr + 32, c);
+      q0 = make_float4(a[0], a[1], a[2], a[3]); q1 = make_float4(a[4], a[5], a[6], a[7]); q2 = make_float4(c[0], c[1], c[2], c[3]);
+      dd = make_uint2(__float_as_uint(c[4]), __float_as_uint(c[5]));
+    } else if (kUseSmem) {
       q0 = ld_pair_generic(addr); q1 = ld_pair_generic(addr + 16); q2 = ld_pair_generic(addr + 32);
       asm("ld.v2.u32 {%0,%1}, [%2];" : "=r"(dd.x), "=r"(dd.y) : "l"(addr + 48));
     } else {

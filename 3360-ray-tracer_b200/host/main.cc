@@ -4,6 +4,8 @@
 // switch (main.cc:178); here it is --scene (default: cornell, the reference's case 4).
 //   rt_b200 [preset] [--scene cornell|rtiow|rtiow110|checkered|earth|earth_bubbles|bunny|stress]
 //           [--cameras file.json] [--mode A|B] [--spp N] [--depth N] [--seed N] [--assets dir]
+//           [--adaptive [threshold [min_samples]]]   per-pixel stop of the reference's WavefrontRenderer
+//           [--width N] [--p6]  binary PPM   [--dump file] [--resume file]  progressive accumulator
 #include <cstdlib>
 #include <cstring>
 #include <iomanip>
@@ -23,6 +25,7 @@ int main(int argc, char** argv) {
   std::string active = "default", scene_name = "cornell", cameras_file = "cameras.json", assets = "assets";
   renderer::B200Options opt;
   bool preset_given = false;
+  int width = 0;  // --width overrides the preset's image_width (tests)
   for (int i = 1; i < argc; ++i) {
     const std::string a = argv[i];
     auto next = [&]() -> std::string { return i + 1 < argc ? argv[++i] : std::string(); };
@@ -33,6 +36,15 @@ int main(int argc, char** argv) {
     else if (a == "--spp") opt.samples_per_pixel = std::atoi(next().c_str());
     else if (a == "--depth") opt.max_depth = std::atoi(next().c_str());
     else if (a == "--seed") opt.seed = std::strtoull(next().c_str(), nullptr, 0);
+    else if (a == "--width") width = std::atoi(next().c_str());
+    else if (a == "--p6") opt.binary_ppm = true;
+    else if (a == "--dump") opt.dump_to = next();
+    else if (a == "--resume") opt.resume_from = next();
+    else if (a == "--adaptive") {
+      opt.adaptive = true;
+      if (i + 1 < argc && std::atof(argv[i + 1]) > 0.0) opt.rel_threshold = static_cast<float>(std::atof(argv[++i]));
+      if (i + 1 < argc && std::atoi(argv[i + 1]) > 0) opt.min_samples = std::atoi(argv[++i]);
+    }
     else if (!preset_given) { active = a; preset_given = true; }
   }
   try {
@@ -47,6 +59,7 @@ int main(int argc, char** argv) {
       active = "default";
     }
     scene::ColorCamera cam;
+    if (width > 0) cameras[active].image_width = width;
     cam.SetFromConfig(cameras[active]);
     cam.Initialize();
 

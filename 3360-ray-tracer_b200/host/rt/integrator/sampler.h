@@ -20,8 +20,8 @@ class DefaultSampler : public Sampler {
   int num_samples_;
 };
 // sampler.h:43-82.  The reference's version accumulates the running total into `sum`
-// (sampler.h:56-59) and is not used by its main(); the policy parameters are carried so that the
-// device can apply the per-pixel stop once the adaptive mode lands.
+// (sampler.h:56-59) and is not used by its main(); here the test it describes - luminance of the
+// variance over luminance of the mean - runs per pixel on the device (RTB_ADAPT_LUMINANCE).
 class AdaptiveSampler : public Sampler {
  public:
   AdaptiveSampler(int min_samples, int max_samples, float threshold) : min_(min_samples), max_(max_samples), thr_(threshold) {}

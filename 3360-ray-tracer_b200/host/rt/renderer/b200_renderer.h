@@ -8,6 +8,7 @@
 #include <rtb.h>
 
 #include <cstdint>
+#include <fstream>
 #include <iostream>
 #include <stdexcept>
 #include <string>
@@ -29,7 +30,16 @@ struct B200Options {
   uint64_t seed = 0x3360;
   int device = 0;
   uint32_t pool_size = 0;
-  bool emit_ppm = true;       // write P3 to `out`
+  // adaptive per-pixel stop (rtb_render_adaptive): samples_per_pixel is then the per-pixel maximum
+  bool adaptive = false;
+  float rel_threshold = 0.05f;  // wavefront.cc:42
+  int min_samples = 16;         // wavefront.cc:43
+  int criterion = RTB_ADAPT_PIXEL_STATE;
+  bool emit_ppm = true;       // write the image to `out`
+  bool binary_ppm = false;    // "P6" (3 bytes per pixel) instead of the reference's ASCII "P3": same bytes, 1/4 of the text
+  // progressive accumulator: `resume_from` continues a dumped render with its next global sample
+  // indices, `dump_to` writes the accumulator after this call.  File: "RTBACC1\n" w h spp | float32 sums.
+  std::string resume_from, dump_to;
   std::ostream* out = &std::cout;
   std::ostream* log = &std::clog;
 };
@@ -60,20 +70,47 @@ class B200Renderer {
     prm.seed = opt_.seed;
     prm.pool_size = opt_.pool_size;
     sum_.assign(static_cast<size_t>(w) * h * 3, 0.0f);
-    const int rc = rtb_render(scene, &dc, &prm, sum_.data(), &stats_);
+    int spp_done = 0;
+    if (!opt_.resume_from.empty()) {
+      if (opt_.adaptive) throw std::runtime_error("B200Renderer: resume is for fixed-spp renders");
+      spp_done = LoadAccumulator(opt_.resume_from, w, h, sum_);
+      prm.spp_begin = spp_done;  // Philox is keyed on the global sample index: the continuation adds NEW samples
+      prm.spp_end = spp_done + spp;
+      prm.flags |= RTB_RENDER_KEEP_ACCUM;
+    }
+    const int spp_total = spp_done + spp;
     std::vector<uint8_t> rgb8(sum_.size());
-    const int rc2 = rc == RTB_OK ? rtb_resolve(sum_.data(), static_cast<size_t>(w) * h, spp, rgb8.data()) : rc;
+    int rc2;
+    if (opt_.adaptive) {
+      // integrator::PixelState per pixel (pixel_state.h:13-19): sum, sum of squares, samples; image = sum / samples
+      RtbAdaptive ad{};
+      ad.rel_threshold = opt_.rel_threshold;
+      ad.min_samples = opt_.min_samples;
+      ad.criterion = opt_.criterion;
+      sumsq_.assign(sum_.size(), 0.0f);
+      count_.assign(static_cast<size_t>(w) * h, 0u);
+      const int rc = rtb_render_adaptive(scene, &dc, &prm, &ad, sum_.data(), sumsq_.data(), count_.data(), &stats_);
+      rc2 = rc == RTB_OK ? rtb_resolve_counts(sum_.data(), count_.data(), count_.size(), rgb8.data()) : rc;
+    } else {
+      const int rc = rtb_render(scene, &dc, &prm, sum_.data(), &stats_);
+      rc2 = rc == RTB_OK ? rtb_resolve(sum_.data(), static_cast<size_t>(w) * h, spp_total, rgb8.data()) : rc;
+    }
     rtb_scene_destroy(scene);
     if (rc2 != RTB_OK) throw std::runtime_error(std::string("B200Renderer: ") + rtb_last_error());
     width_ = w;
     height_ = h;
-    spp_ = spp;
+    spp_ = spp_total;
+    if (!opt_.dump_to.empty()) SaveAccumulator(opt_.dump_to, w, h, spp_total, sum_);
     if (opt_.log) {
       *opt_.log << "B200: " << w << "x" << h << " spp=" << spp << " depth=" << depth << " mode=" << (opt_.mode == RTB_MODE_A ? 'A' : 'B')
                 << "  flatten+upload " << t_upload << "s  render " << stats_.ms_total * 1e-3 << "s  "
                 << stats_.samples / (stats_.ms_total * 1e3) << " Msamples/s  " << stats_.rays / (stats_.ms_total * 1e3) << " Mrays/s\n";
     }
-    if (opt_.emit_ppm && opt_.out) {
+    if (opt_.emit_ppm && opt_.out && opt_.binary_ppm) {
+      const std::string head = "P6\n" + std::to_string(w) + ' ' + std::to_string(h) + "\n255\n";
+      opt_.out->write(head.data(), static_cast<std::streamsize>(head.size()));
+      opt_.out->write(reinterpret_cast<const char*>(rgb8.data()), static_cast<std::streamsize>(rgb8.size()));
+    } else if (opt_.emit_ppm && opt_.out) {
       std::string text;
       text.reserve(rgb8.size() * 4 + 32);
       text += "P3\n" + std::to_string(w) + ' ' + std::to_string(h) + "\n255\n";
@@ -90,7 +127,29 @@ class B200Renderer {
     if (opt_.log) *opt_.log << "\rDone. Total samples: " << stats_.samples << "Per pixel: " << stats_.samples / (static_cast<uint64_t>(w) * h) << "\n";
   }
 
+  static void SaveAccumulator(const std::string& path, int w, int h, int spp, const std::vector<float>& sum) {
+    std::ofstream f(path, std::ios::binary);
+    if (!f) throw std::runtime_error("B200Renderer: cannot write '" + path + "'");
+    f << "RTBACC1\n" << w << ' ' << h << ' ' << spp << '\n';
+    f.write(reinterpret_cast<const char*>(sum.data()), static_cast<std::streamsize>(sum.size() * sizeof(float)));
+  }
+  // returns the samples per pixel already in the file
+  static int LoadAccumulator(const std::string& path, int w, int h, std::vector<float>& sum) {
+    std::ifstream f(path, std::ios::binary);
+    std::string magic;
+    int fw = 0, fh = 0, spp = 0;
+    if (!f || !(f >> magic >> fw >> fh >> spp) || magic != "RTBACC1") throw std::runtime_error("B200Renderer: '" + path + "' is not an accumulator dump");
+    if (fw != w || fh != h || spp < 0) throw std::runtime_error("B200Renderer: accumulator dump is " + std::to_string(fw) + "x" + std::to_string(fh) + ", camera is " + std::to_string(w) + "x" + std::to_string(h));
+    f.get();  // the newline after the header
+    sum.assign(static_cast<size_t>(w) * h * 3, 0.0f);
+    f.read(reinterpret_cast<char*>(sum.data()), static_cast<std::streamsize>(sum.size() * sizeof(float)));
+    if (f.gcount() != static_cast<std::streamsize>(sum.size() * sizeof(float))) throw std::runtime_error("B200Renderer: accumulator dump is truncated");
+    return spp;
+  }
+
   const std::vector<float>& radiance_sum() const { return sum_; }
+  const std::vector<float>& radiance_sumsq() const { return sumsq_; }   // adaptive renders only
+  const std::vector<uint32_t>& sample_counts() const { return count_; }  // adaptive renders only
   const RtbStats& stats() const { return stats_; }
   int width() const { return width_; }
   int height() const { return height_; }
@@ -100,7 +159,8 @@ class B200Renderer {
   const scene::Scene& world_;
   const scene::Camera& cam_;
   B200Options opt_;
-  std::vector<float> sum_;
+  std::vector<float> sum_, sumsq_;
+  std::vector<uint32_t> count_;
   RtbStats stats_{};
   int width_ = 0, height_ = 0, spp_ = 0;
 };
@@ -113,7 +173,12 @@ class MegaKernel {
     B200Options o;
     o.mode = RTB_MODE_A;
     o.samples_per_pixel = sampler_.max_samples();
-    if (sampler_.adaptive()) std::clog << "note: AdaptiveSampler runs at its max_samples on the device (adaptive stop: SURVEY 8f-2)\n";
+    if (sampler_.adaptive()) {  // AdaptiveSampler(min, max, threshold): its luminance test, per pixel, on the device
+      o.adaptive = true;
+      o.criterion = RTB_ADAPT_LUMINANCE;
+      o.min_samples = sampler_.min_samples();
+      o.rel_threshold = sampler_.threshold();
+    }
     B200Renderer(world_, cam_, o).Render();
   }
  private:
@@ -123,7 +188,7 @@ class MegaKernel {
 };
 
 // renderer::WavefrontRenderer(world, cam, integrator, max_depth, max_samples, batch).Render()
-// — estimator B (wavefront.cc:40-242).  `integrator` and `batch_size` are accepted for source
+// — estimator B with its adaptive per-pixel stop (wavefront.cc:40-242).  `integrator` and `batch_size` are accepted for source
 // compatibility; intersection runs inside the device wavefront, whose batch is the path pool.
 class WavefrontRenderer {
  public:
@@ -135,6 +200,7 @@ class WavefrontRenderer {
     o.mode = RTB_MODE_B;
     o.samples_per_pixel = max_ssp_;
     o.max_depth = max_depth_;
+    o.adaptive = true;  // kRelThresh 0.05, kMinSamples 16, PixelState::IsConverged (wavefront.cc:42-43)
     B200Renderer(world_, cam_, o).Render();
   }
  private:

@@ -37,3 +37,29 @@ def render_sharded(device_scene, cam, spp_total: int, max_depth: int, accum, dis
     stats = device_scene.render_device(cam, accum.data_ptr(), b, e, max_depth, mode=mode, seed=seed, pool_size=pool_size)
     reduce_accumulator(accum, dist)
     return stats
+
+
+def reduce_adaptive(accum, count, dist=None, dst: int = 0, sumsq=None):
+    """Adaptive renders (rtb_render_adaptive_device) exchange one more plane: the per-pixel sample counts
+    (SURVEY 8e).  Every rank runs the stop rule on its own slice of the global sample indices; the image is
+    sum over ranks of rgb_sum / sum over ranks of count.  `count` travels as int32 (NCCL and gloo both sum it)."""
+    if dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.reduce(accum, dst=dst, op=dist.ReduceOp.SUM)
+        dist.reduce(count, dst=dst, op=dist.ReduceOp.SUM)
+        if sumsq is not None:
+            dist.reduce(sumsq, dst=dst, op=dist.ReduceOp.SUM)
+    return accum, count
+
+
+def render_sharded_adaptive(device_scene, cam, max_spp_total: int, max_depth: int, accum, sumsq, count, dist=None, rel_threshold: float = 0.05,
+                            min_samples: int = 16, criterion: int = 0, mode: int = 1, seed: int = 0x3360):
+    """Rank k takes the global sample indices of its slice of [0, max_spp_total) and stops each pixel by the rule
+    evaluated on its own samples (min_samples applies per rank); then sums and counts are reduced onto rank 0.
+    accum / sumsq: CUDA float32 W*H*3; count: CUDA int32 W*H (the device writes uint32 values < 2^31)."""
+    rank = dist.get_rank() if dist is not None and dist.is_initialized() else 0
+    world = dist.get_world_size() if dist is not None and dist.is_initialized() else 1
+    b, e = spp_slice(max_spp_total, rank, world)
+    stats = device_scene.render_adaptive_device(cam, accum.data_ptr(), sumsq.data_ptr(), count.data_ptr(), b, e, max_depth,
+                                                rel_threshold=rel_threshold, min_samples=min_samples, criterion=criterion, mode=mode, seed=seed)
+    reduce_adaptive(accum, count, dist, sumsq=sumsq)
+    return stats

@@ -59,3 +59,42 @@ def test_reduce_of_sharded_accumulators_equals_single_rank(rt, tmp_path, world):
     got = np.load(out)
     want = _fake_radiance(n_pix, 0, spp)
     assert np.allclose(got, want, rtol=1e-5, atol=1e-4)
+
+
+def _worker_adaptive(rank, world, port, n_pix, out_path):
+    import sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parents[1]
+    sys.path.insert(0, str(root))
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as g
+    rt = g.load_package()
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    # stand-in for a rank's adaptive render: pixel p stopped after (p + rank) % 5 + 1 samples of value (rank + 1)
+    cnt = torch.tensor([(p + rank) % 5 + 1 for p in range(n_pix)], dtype=torch.int32)
+    accum = (cnt.to(torch.float32) * (rank + 1)).repeat_interleave(3)
+    rt.multigpu.reduce_adaptive(accum, cnt, dist)
+    if rank == 0:
+        np.savez(out_path, sum=accum.numpy(), count=cnt.numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_adaptive_reduce_sums_radiance_and_counts(rt, tmp_path):
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    world, n_pix = 2, 64
+    out = tmp_path / "adaptive.npz"
+    mp.spawn(_worker_adaptive, args=(world, port, n_pix, str(out)), nprocs=world, join=True)
+    got = np.load(out)
+    cnts = np.array([[(p + r) % 5 + 1 for p in range(n_pix)] for r in range(world)])
+    assert np.array_equal(got["count"], cnts.sum(0))
+    want = (cnts * np.arange(1, world + 1)[:, None]).sum(0).repeat(3).astype(np.float32)
+    assert np.allclose(got["sum"], want)
+    # the image is sum / count: a count-weighted mean of the per-rank means
+    mean = got["sum"].reshape(-1, 3)[:, 0] / got["count"]
+    assert np.all((mean >= 1.0) & (mean <= world))
