@@ -48,7 +48,7 @@ class RtbSceneDesc(C.Structure):
         ("n_materials", C.c_uint32), ("materials", C.c_void_p),
         ("n_textures", C.c_uint32), ("textures", C.c_void_p),
         ("n_images", C.c_uint32), ("images", C.c_void_p),
-        ("n_top_nodes", C.c_uint32), ("max_depth", C.c_uint32), ("compiled", C.c_void_p),
+        ("n_top_nodes", C.c_uint32), ("max_depth", C.c_uint32), ("compiled", C.c_void_p), ("flags", C.c_uint32),
     ]
 
 
@@ -110,7 +110,7 @@ RTB_SYMBOLS = [
     "rtb_resolve_device", "rtb_resolve", "rtb_measure_l2_gbs", "rtb_measure_fp32_tflops", "rtb_measure_fp64_tflops",
 ]
 RTH_SYMBOLS = [
-    "rth_last_error", "rth_scene_build", "rth_scene_from_records", "rth_scene_desc", "rth_scene_export",
+    "rth_last_error", "rth_scene_build", "rth_scene_build_ex", "rth_scene_from_records", "rth_scene_desc", "rth_scene_export",
     "rth_scene_gid_map", "rth_scene_bvh_count", "rth_scene_bvh_size", "rth_scene_bvh_dump", "rth_scene_free",
     "rth_camera_init", "rth_camera_preset",
 ]
@@ -141,6 +141,7 @@ def load(counters: bool = False) -> C.CDLL:
     lib.rth_scene_desc.restype = C.POINTER(RtbSceneDesc)
     lib.rth_scene_desc.argtypes = [C.c_void_p]
     lib.rth_scene_build.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_char_p, C.c_uint32, C.POINTER(C.c_void_p)]
+    lib.rth_scene_build_ex.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_char_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_void_p)]
     lib.rth_scene_from_records.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t,
                                            C.c_char_p, C.c_uint32, C.POINTER(C.c_void_p)]
     lib.rth_scene_export.argtypes = [C.c_void_p] + [C.c_void_p] * 7
@@ -190,12 +191,13 @@ class HostScene:
         self._h, self._lib = handle, lib
 
     @classmethod
-    def build(cls, name: str, params=(), top_budget: int = 0, counters: bool = False, asset_dir=None) -> "HostScene":
+    def build(cls, name: str, params=(), top_budget: int = 0, counters: bool = False, asset_dir=None, device_tree: bool = False) -> "HostScene":
+        """device_tree: no host SAH build; rtb_scene_create builds a linear BVH on the GPU (RTB_SCENE_DEVICE_BUILD)."""
         lib = load(counters)
         p = np.asarray(params, dtype=np.float64)
         h = C.c_void_p()
-        rc = lib.rth_scene_build(name.encode(), _ptr(p) if p.size else None, int(p.size),
-                                 str(asset_dir or ASSET_DIR).encode(), top_budget, C.byref(h))
+        rc = lib.rth_scene_build_ex(name.encode(), _ptr(p) if p.size else None, int(p.size),
+                                    str(asset_dir or ASSET_DIR).encode(), top_budget, 1 if device_tree else 0, C.byref(h))
         _check(lib, rc, host=True)
         return cls(h, lib)
 

@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "rtb_compile.h"
+#include "rtb_build.cuh"
 #include "rtb_kernels.cuh"
 
 namespace {
@@ -192,6 +193,66 @@ struct RtbScene {
   }
 };
 
+// RTB_SCENE_DEVICE_BUILD: the pair records of a linear BVH over every primitive, written straight into the scene's
+// arena by the kernels of rtb_build.cuh.  Scratch lives in the stream-ordered pool for the duration of the build.
+__global__ void build_single_kernel(rtb::DevScene s, uint32_t n_s, uint32_t n_t, float* pairs) {
+  uint32_t type, idx;
+  rtb::split_index(0u, n_s, n_t, type, idx);
+  const rtb::BuildBox b = rtb::prim_box(s, type, idx);
+  const uint32_t desc = rtb::kLeafBit | (type << 29) | idx;
+  rtb::store_half(pairs, 0u, b, desc);  // one primitive: both children hold it (a self-tie never replaces)
+  rtb::store_half(pairs, 1u, b, desc);
+}
+
+static int BuildTreeOnDevice(RtbScene* s, uint32_t n_s, uint32_t n_t, uint32_t n, float* d_pairs) {
+  cudaStream_t st = g_stream;
+  if (n == 1) {
+    build_single_kernel<<<1, 1, 0, st>>>(s->dev, n_s, n_t, d_pairs);
+    RTB_CUDA(cudaStreamSynchronize(st));
+    return RTB_OK;
+  }
+  auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
+  size_t cub_bytes = 0;
+  RTB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, (const unsigned long long*)nullptr, (unsigned long long*)nullptr,
+                                           (const uint32_t*)nullptr, (uint32_t*)nullptr, (int)n, 0, 63, st));
+  const size_t o_boxes = 0, o_keys0 = o_boxes + up((size_t)n * sizeof(rtb::BuildBox)), o_keys1 = o_keys0 + up((size_t)n * 8),
+               o_ord0 = o_keys1 + up((size_t)n * 8), o_ord1 = o_ord0 + up((size_t)n * 4), o_pint = o_ord1 + up((size_t)n * 4),
+               o_pleaf = o_pint + up((size_t)n * 4), o_flags = o_pleaf + up((size_t)n * 4), o_misc = o_flags + up((size_t)n * 4),
+               o_cub = o_misc + 256, total = o_cub + up(cub_bytes);
+  char* w = nullptr;
+  RTB_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&w), total, st));
+  auto* boxes = reinterpret_cast<rtb::BuildBox*>(w + o_boxes);
+  auto* keys0 = reinterpret_cast<unsigned long long*>(w + o_keys0);
+  auto* keys1 = reinterpret_cast<unsigned long long*>(w + o_keys1);
+  auto* ord0 = reinterpret_cast<uint32_t*>(w + o_ord0);
+  auto* ord1 = reinterpret_cast<uint32_t*>(w + o_ord1);
+  auto* pint = reinterpret_cast<uint32_t*>(w + o_pint);
+  auto* pleaf = reinterpret_cast<uint32_t*>(w + o_pleaf);
+  auto* flags = reinterpret_cast<unsigned*>(w + o_flags);
+  auto* misc = reinterpret_cast<unsigned*>(w + o_misc);  // [0..2] min, [3..5] max of the centres (ordered bits), [6] depth
+  cudaError_t e = cudaMemsetAsync(misc, 0xff, 12, st);
+  if (e == cudaSuccess) e = cudaMemsetAsync(misc + 3, 0, 16, st);
+  if (e == cudaSuccess) e = cudaMemsetAsync(flags, 0, (size_t)n * 4, st);
+  const unsigned grid = (n + 255) / 256;
+  if (e == cudaSuccess) {
+    rtb::build_bounds_kernel<<<grid, 256, 0, st>>>(s->dev, n_s, n_t, n, boxes, misc);
+    rtb::build_morton_kernel<<<grid, 256, 0, st>>>(boxes, n, misc, keys0, ord0);
+    e = cub::DeviceRadixSort::SortPairs(w + o_cub, cub_bytes, keys0, keys1, ord0, ord1, (int)n, 0, 63, st);
+  }
+  unsigned depth = 0;
+  if (e == cudaSuccess) {
+    rtb::build_hierarchy_kernel<<<grid, 256, 0, st>>>(keys1, (int)n, pint, pleaf);
+    rtb::build_emit_kernel<<<grid, 256, 0, st>>>(boxes, ord1, n, n_s, n_t, pint, pleaf, d_pairs, flags, misc + 6);
+    e = cudaMemcpyAsync(&depth, misc + 6, 4, cudaMemcpyDeviceToHost, st);
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e == cudaSuccess) e = cudaGetLastError();
+  cudaFreeAsync(w, st);
+  if (e != cudaSuccess) return Fail(RTB_ECUDA, std::string("device tree build: ") + cudaGetErrorString(e));
+  if (depth + 2 > (unsigned)rtb::kStackSize) return Fail(RTB_EINVAL, "device-built BVH deeper than the 64-entry traversal stack (bvh.h:80)");
+  return RTB_OK;
+}
+
 extern "C" {
 
 const char* rtb_last_error(void) { return g_error.c_str(); }
@@ -292,6 +353,9 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
   RtbScene* s = new RtbScene();
   s->device = g_device;
   rtb::DevScene& v = s->dev;
+  const bool device_build = (d->flags & RTB_SCENE_DEVICE_BUILD) != 0;
+  const uint32_t n_prims = d->n_spheres + d->n_triangles + d->n_rects;
+  size_t built_pairs_off = 0;
 #define PUT(expr)            \
   do {                       \
     rc = (expr);             \
@@ -307,7 +371,9 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
   std::vector<int2> dims;
   {  // interchange tree -> device-native sibling pairs (rtb_compile.h), unless the caller already did it
     const rtbc::Compiled* tree = d->compiled ? &d->compiled->tree : &local;
-    if (!d->compiled) {
+    if (device_build) {
+      tree = &local;  // stays empty: the pairs are written by the build kernels after the upload
+    } else if (!d->compiled) {
       rc = CompileTree(*d, &local);
       if (rc != RTB_OK) {
         rtb_scene_destroy(s);
@@ -317,6 +383,10 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
     PUT(s->Put(reinterpret_cast<const float4*>(tree->pairs.data()), 4 * tree->pairs.size(), &v.pairs));
     v.n_pairs = (uint32_t)tree->pairs.size();
     v.n_top_pairs = tree->top_pairs;
+    if (device_build && n_prims > 0) {
+      v.n_pairs = n_prims > 1 ? n_prims - 1 : 1;
+      built_pairs_off = s->Reserve((size_t)v.n_pairs * 64);
+    }
   }
   PUT(s->Put(reinterpret_cast<const double2*>(d->spheres), 2 * (size_t)d->n_spheres, &v.spheres));
   PUT(s->Put(reinterpret_cast<const double2*>(d->triangles), 5 * (size_t)d->n_triangles, &v.triangles));
@@ -353,9 +423,9 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
   PUT(s->Put(d->sphere_gid, d->n_spheres, &v.sphere_gid));
   PUT(s->Put(d->triangle_gid, d->n_triangles, &v.triangle_gid));
   PUT(s->Put(d->rect_gid, d->n_rects, &v.rect_gid));
-  PUT(s->Put(d->sphere_rank, d->n_spheres, &v.sphere_rank));
-  PUT(s->Put(d->triangle_rank, d->n_triangles, &v.triangle_rank));
-  PUT(s->Put(d->rect_rank, d->n_rects, &v.rect_rank));
+  PUT(s->Put(d->sphere_rank ? d->sphere_rank : d->sphere_gid, d->n_spheres, &v.sphere_rank));
+  PUT(s->Put(d->triangle_rank ? d->triangle_rank : d->triangle_gid, d->n_triangles, &v.triangle_rank));
+  PUT(s->Put(d->rect_rank ? d->rect_rank : d->rect_gid, d->n_rects, &v.rect_rank));
   PUT(s->Put(d->materials, d->n_materials, &v.materials));
   PUT(s->Put(d->textures, d->n_textures, &v.textures));
   {  // images -> point-sampled texture objects over RGBA8 arrays
@@ -402,6 +472,10 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
     return Fail(RTB_EINVAL, "n_top_nodes does not fit shared memory");
   }
   PUT(s->Commit(g_stream));
+  if (device_build && n_prims > 0) {
+    v.pairs = reinterpret_cast<const float4*>(s->arena + built_pairs_off);
+    PUT(BuildTreeOnDevice(s, d->n_spheres, d->n_triangles, n_prims, reinterpret_cast<float*>(s->arena + built_pairs_off)));
+  }
   // opt in to large dynamic shared memory for the two traversal kernels
   {
     const int with_top = (int)(s->smem_bytes + kStackSmem), without = (int)kStackSmem;
@@ -430,10 +504,15 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
 // structural validation: every index the kernels will follow must be in range
 static int ValidateDesc(const RtbSceneDesc* d) {
   if (d->abi_version != RTB_ABI_VERSION) return Fail(RTB_EINVAL, "RtbSceneDesc.abi_version mismatch");
-  if (d->n_nodes < 2 || (d->n_nodes & 1u) || !d->nodes) return Fail(RTB_EINVAL, "scene needs an even, non-zero node count");
+  const bool device_build = (d->flags & RTB_SCENE_DEVICE_BUILD) != 0;
+  if (device_build) {
+    if (d->n_spheres > (1u << 24) || d->n_triangles > (1u << 24) || d->n_rects > (1u << 24)) return Fail(RTB_EINVAL, "more than 2^24 primitives of one type");
+  } else if (d->n_nodes < 2 || (d->n_nodes & 1u) || !d->nodes) {
+    return Fail(RTB_EINVAL, "scene needs an even, non-zero node count");
+  }
   if (d->n_prim_refs >= (1u << 25)) return Fail(RTB_EINVAL, "more than 2^25 leaf entries");
   if (d->n_top_nodes > d->n_nodes || (d->n_top_nodes & 1u)) return Fail(RTB_EINVAL, "bad n_top_nodes");
-  for (uint32_t i = 0; i < d->n_nodes; ++i) {
+  for (uint32_t i = 0; i < (device_build ? 0u : d->n_nodes); ++i) {
     const RtbNode& n = d->nodes[i];
     if (n.b == 0) {
       if (!(n.lo[0] <= n.hi[0])) continue;  // padding slot (inverted box), never entered
@@ -442,7 +521,7 @@ static int ValidateDesc(const RtbSceneDesc* d) {
       return Fail(RTB_EINVAL, "leaf range out of bounds");
     }
   }
-  for (uint32_t i = 0; i < d->n_prim_refs; ++i) {
+  for (uint32_t i = 0; i < (device_build ? 0u : d->n_prim_refs); ++i) {
     const uint32_t ty = RTB_REF_TYPE(d->prim_refs[i]), idx = RTB_REF_INDEX(d->prim_refs[i]);
     const uint32_t lim = ty == RTB_PRIM_SPHERE ? d->n_spheres : ty == RTB_PRIM_TRIANGLE ? d->n_triangles : ty == RTB_PRIM_RECT ? d->n_rects : d->n_nodes;
     if (idx >= lim || (ty == RTB_PRIM_SUBTREE && (idx & 1u))) return Fail(RTB_EINVAL, "leaf entry out of range");

@@ -19,6 +19,7 @@
 #include <cstdint>
 #include <deque>
 #include <map>
+#include <unordered_map>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -61,6 +62,8 @@ struct FlatScene {
   // gid -> RTB_REF(type, table index)
   std::vector<uint32_t> gid_to_ref;
 
+  bool device_build = false;  // RunSoup(): primitive tables only, RTB_SCENE_DEVICE_BUILD
+
   RtbSceneDesc desc() const {
     RtbSceneDesc d{};
     d.abi_version = RTB_ABI_VERSION;
@@ -90,6 +93,12 @@ struct FlatScene {
     d.n_top_nodes = n_top_nodes;
     d.max_depth = max_depth;
     d.compiled = nullptr;  // rtb_tree_compile's result, set by whoever owns it (rth_capi.cc, B200Renderer)
+    d.flags = device_build ? RTB_SCENE_DEVICE_BUILD : 0u;
+    if (device_build) {  // no host tree: the device builds it, creation order breaks exact-t ties
+      d.nodes = nullptr;
+      d.prim_refs = nullptr;
+      d.sphere_rank = d.triangle_rank = d.rect_rank = nullptr;
+    }
     return d;
   }
 };
@@ -110,6 +119,21 @@ class Flattener : public geom::SceneSink, public material::MaterialSink, public 
       root = fnodes_[root.index].items[0];
     AssignRanks(root.index);
     Layout(root.index);
+    return std::move(out_);
+  }
+
+  // Primitive tables, materials and textures only, in creation order: the traversal tree is built on the device
+  // (RTB_SCENE_DEVICE_BUILD).  Host geom::Bvh objects met on the way contribute their primitives, never their nodes,
+  // so a scene assembled under geom::Bvh::DeferBuild never runs the SAH build at all.
+  FlatScene RunSoup(const scene::Scene& world) {
+    out_ = FlatScene();
+    fnodes_.clear();
+    soup_ = true;
+    Convert(world);
+    soup_ = false;
+    if (out_.n_prims == 0) throw std::runtime_error("flatten: empty scene");
+    for (size_t i = 0; i < out_.images.size(); ++i) out_.images[i].rgb = out_.image_bytes[i].empty() ? nullptr : out_.image_bytes[i].data();
+    out_.device_build = true;
     return std::move(out_);
   }
 
@@ -152,7 +176,7 @@ class Flattener : public geom::SceneSink, public material::MaterialSink, public 
     by_prim.reserve(bvh.primitives().size());
     for (const auto& p : bvh.primitives()) by_prim.push_back(Convert(*p));
     Export(kExBvhEnd, 0, {});
-    if (bvh.nodes().empty()) {
+    if (soup_ || bvh.nodes().empty()) {
       last_ = Item{kNone, 0};
       return;
     }
@@ -169,7 +193,7 @@ class Flattener : public geom::SceneSink, public material::MaterialSink, public 
       box = geom::Aabb(box, o->BoundingBox());
     }
     Export(kExListEnd, 0, {});
-    if (items.empty()) {
+    if (soup_ || items.empty()) {
       last_ = Item{kNone, 0};
       return;
     }
@@ -234,6 +258,7 @@ class Flattener : public geom::SceneSink, public material::MaterialSink, public 
   }
 
   void Export(int kind, uint32_t mat, std::initializer_list<double> params) {
+    if (soup_) return;  // the oracle's export stream is not produced for device-built scenes (640 MB at 5 M primitives)
     const size_t base = out_.prim_records.size();
     out_.prim_records.resize(base + kExportRecord, 0.0);
     out_.prim_records[base] = kind;
@@ -244,8 +269,13 @@ class Flattener : public geom::SceneSink, public material::MaterialSink, public 
 
   uint32_t MaterialId(const std::shared_ptr<material::Material>& m) {
     if (!m) throw std::runtime_error("flatten: primitive without material");
+    if (m.get() == last_mat_) return last_mat_id_;  // a mesh's triangles share one material
     auto it = mat_ids_.find(m.get());
-    if (it != mat_ids_.end()) return it->second;
+    if (it != mat_ids_.end()) {
+      last_mat_ = m.get();
+      last_mat_id_ = it->second;
+      return it->second;
+    }
     for (double& d : mat_d_) d = 0;
     m->Describe(*this);
     const uint32_t id = static_cast<uint32_t>(out_.materials.size());
@@ -475,6 +505,7 @@ class Flattener : public geom::SceneSink, public material::MaterialSink, public 
 
   uint32_t top_budget_;
   bool keep_info_ = false;
+  bool soup_ = false;
   FlatScene out_;
   std::vector<FNode> fnodes_;
   Item last_{kNone, 0};
@@ -482,8 +513,10 @@ class Flattener : public geom::SceneSink, public material::MaterialSink, public 
   RtbTexture tex_tmp_{};
   double mat_d_[5] = {0, 0, 0, 0, 0};
   double tex_d_[4] = {0, 0, 0, 0};
-  std::map<const material::Material*, uint32_t> mat_ids_;
-  std::map<const material::Texture*, uint32_t> tex_ids_;
+  std::unordered_map<const material::Material*, uint32_t> mat_ids_;
+  std::unordered_map<const material::Texture*, uint32_t> tex_ids_;
+  const material::Material* last_mat_ = nullptr;
+  uint32_t last_mat_id_ = 0;
 };
 
 }  // namespace rt::b200

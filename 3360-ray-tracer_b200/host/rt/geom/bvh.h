@@ -34,10 +34,22 @@ class Bvh : public Hittable {
  public:
   Bvh(scene::Scene& scene) : Bvh(scene.objects_) {}
   Bvh(Mesh& mesh) : Bvh(mesh.tris) {}
+  // While set (per thread), constructors only record their primitives and bounding box: for scenes whose traversal
+  // tree is built on the device (b200::Flattener::RunSoup, RTB_SCENE_DEVICE_BUILD) the SAH build is wasted work.
+  static bool& DeferBuild() {
+    thread_local bool defer = false;
+    return defer;
+  }
+
   Bvh(std::vector<std::shared_ptr<Hittable>>& objects) {
     if (objects.empty()) return;
     primitives_ = objects;
     const int n = static_cast<int>(primitives_.size());
+    if (DeferBuild()) {
+      deferred_box_ = primitives_[0]->BoundingBox();
+      for (int i = 1; i < n; ++i) deferred_box_ = Aabb(deferred_box_, primitives_[i]->BoundingBox());
+      return;
+    }
     prim_indices_.resize(n);
     bounds_.resize(n);
     centroids_.resize(n);
@@ -54,7 +66,7 @@ class Bvh : public Hittable {
     centroids_.shrink_to_fit();
   }
 
-  Aabb BoundingBox() const override { return root_index_ < 0 ? Aabb() : nodes_[root_index_].bbox; }
+  Aabb BoundingBox() const override { return root_index_ < 0 ? deferred_box_ : nodes_[root_index_].bbox; }
   int TypeId() const override { return -1; }
   int ObjectIndex() const override { return -1; }
   void set_object_index(int) override {}
@@ -154,6 +166,7 @@ class Bvh : public Hittable {
   std::vector<Aabb> bounds_;
   std::vector<core::Vec3> centroids_;
   std::vector<BvhNodeGPU> nodes_;
+  Aabb deferred_box_;
   int root_index_ = -1;
 };
 

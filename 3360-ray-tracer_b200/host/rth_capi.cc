@@ -31,11 +31,16 @@ int Fail(const std::exception& e) {
 }
 double Param(const double* p, int n, int i, double dflt) { return (p && i < n) ? p[i] : dflt; }
 
-void Finish(RthScene& s, uint32_t top_budget) {
-  s.flat = b200::Flattener(top_budget).Run(s.built.world);
-  s.desc = s.flat.desc();
-  if (rtb_tree_compile(&s.desc, &s.tree) != RTB_OK) throw std::runtime_error(rtb_last_error());
-  s.desc.compiled = s.tree;
+void Finish(RthScene& s, uint32_t top_budget, uint32_t flags = 0) {
+  if (flags & RTH_BUILD_DEVICE_TREE) {
+    s.flat = b200::Flattener(top_budget).RunSoup(s.built.world);
+    s.desc = s.flat.desc();
+  } else {
+    s.flat = b200::Flattener(top_budget).Run(s.built.world);
+    s.desc = s.flat.desc();
+    if (rtb_tree_compile(&s.desc, &s.tree) != RTB_OK) throw std::runtime_error(rtb_last_error());
+    s.desc.compiled = s.tree;
+  }
   s.image_paths.clear();
   for (const auto& p : s.flat.image_paths) {
     if (!s.image_paths.empty()) s.image_paths += '\n';
@@ -135,7 +140,17 @@ const char* rth_last_error(void) { return g_error.c_str(); }
 
 int rth_scene_build(const char* name, const double* params, int n_params, const char* asset_dir, uint32_t top_budget,
                     RthScene** out) {
+  return rth_scene_build_ex(name, params, n_params, asset_dir, top_budget, 0u, out);
+}
+
+int rth_scene_build_ex(const char* name, const double* params, int n_params, const char* asset_dir, uint32_t top_budget,
+                       uint32_t flags, RthScene** out) {
   if (!name || !out) return RTB_EINVAL;
+  struct DeferGuard {  // host geom::Bvh constructors skip their SAH build while the device will build the tree
+    bool old;
+    explicit DeferGuard(bool on) : old(geom::Bvh::DeferBuild()) { geom::Bvh::DeferBuild() = on; }
+    ~DeferGuard() { geom::Bvh::DeferBuild() = old; }
+  } guard((flags & RTH_BUILD_DEVICE_TREE) != 0);
   try {
     auto s = std::make_unique<RthScene>();
     const std::string n(name), assets(asset_dir ? asset_dir : "assets");
@@ -159,7 +174,7 @@ int rth_scene_build(const char* name, const double* params, int n_params, const 
     } else {
       throw std::runtime_error("unknown scene '" + n + "'");
     }
-    Finish(*s, top_budget ? top_budget : 1024);
+    Finish(*s, top_budget ? top_budget : 1024, flags);
     *out = s.release();
     return RTB_OK;
   } catch (const std::exception& e) {

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define RTB_ABI_VERSION 2
+#define RTB_ABI_VERSION 3
 
 /* ---- status codes ------------------------------------------------------ */
 enum {
@@ -152,7 +152,14 @@ typedef struct RtbSceneDesc {
    * to scene construction, like the reference's Bvh constructor (bvh.h:39-68), not to the render call.  NULL:
    * rtb_scene_create builds it itself. */
   const struct RtbCompiledTree* compiled;
+  /* RTB_SCENE_*.  With RTB_SCENE_DEVICE_BUILD rtb_scene_create ignores nodes / prim_refs / compiled (they may be
+   * NULL / 0) and builds the traversal tree on the GPU from the primitive tables (linear BVH, csrc/rtb_build.cuh):
+   * the host never runs geom::Bvh's SAH build (src/geom/bvh.h:166-344).  The closest hit does not depend on the
+   * tree; only the order of EXACT-t ties does: the *_rank arrays may then be NULL and creation order (gid) stands in
+   * for the reference's slot order (bvh.h:95-106). */
+  uint32_t flags;
 } RtbSceneDesc;
+#define RTB_SCENE_DEVICE_BUILD 1u
 typedef struct RtbCompiledTree RtbCompiledTree; /* opaque, host memory only */
 
 /* ---- rays and hits (seam 2) -------------------------------------------- */

@@ -37,6 +37,11 @@ const char* rth_last_error(void);
  * top_budget: nodes in the breadth-first prefix (0 = 1024). */
 int rth_scene_build(const char* name, const double* params, int n_params, const char* asset_dir,
                     uint32_t top_budget, RthScene** out);
+/* flags: RTH_BUILD_DEVICE_TREE = no host SAH build / flatten / compile; the RtbSceneDesc carries the primitive
+ * tables only and RTB_SCENE_DEVICE_BUILD, and rtb_scene_create builds the tree on the GPU. */
+#define RTH_BUILD_DEVICE_TREE 1u
+int rth_scene_build_ex(const char* name, const double* params, int n_params, const char* asset_dir,
+                       uint32_t top_budget, uint32_t flags, RthScene** out);
 /* Build from an export stream (16 doubles per primitive record, 8 per material / texture). */
 int rth_scene_from_records(const double* prims, size_t n_prims, const double* mats, size_t n_mats,
                            const double* texs, size_t n_texs, const char* image_paths,

@@ -32,7 +32,7 @@ def test_counters_build_exports_the_same_abi(rt):
 
 def test_abi_version_and_struct_sizes(rt):
     lib = rt.load()
-    assert lib.rtb_abi_version() == 2
+    assert lib.rtb_abi_version() == 3
     assert C.sizeof(rt.binding.RtbNode) == 32
     assert rt.RAY_DTYPE.itemsize == 32 and rt.HIT_DTYPE.itemsize == 16
     assert C.sizeof(rt.binding.RtbCamera) == 88
