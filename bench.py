@@ -155,6 +155,9 @@ def main():
     ap.add_argument("--mode", default="A", choices=["A", "B"])
     ap.add_argument("--pipeline", default="path", choices=["path", "wavefront"],
                     help="path = the default persistent path kernel; wavefront = generate/extend/shade kernels over queues")
+    ap.add_argument("--tree", default="auto", choices=["auto", "host", "device"],
+                    help="host = the reference's SAH tree built on the host and compiled for the device; device = linear BVH built on the GPU "
+                         "(RTB_SCENE_DEVICE_BUILD); auto = device for the stress scene (faster to build AND to traverse there), host otherwise")
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
@@ -193,8 +196,9 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     lib = rt.load()
 
+    device_tree = args.tree == "device" or (args.tree == "auto" and args.config == "stress")
     t_build = time.perf_counter()
-    hs = rt.HostScene.build(*cfg["scene"])
+    hs = rt.HostScene.build(*cfg["scene"], device_tree=device_tree)
     t_build = time.perf_counter() - t_build
     ds = rt.DeviceScene(hs, device=local_rank)
     cam_cfg = camera_for(rt, cfg, args.width or None, args.spp or None)
@@ -323,6 +327,8 @@ def main():
                        "l2": "384 MiB buffer written between timed steps (L2 flushed); scene itself is L2-resident by design",
                        "pipeline": "persistent path kernel (generate + traverse + shade per lane, one launch per step)" if args.pipeline == "path"
                        else f"wavefront: generate / extend / shade+compact over queues, pool {args.pool or (1 << 21)} paths x {os.environ.get('RTB_WAVES', '4')} wavefronts in flight",
+                       "tree": "linear BVH built on the GPU inside rtb_scene_create (RTB_SCENE_DEVICE_BUILD)" if device_tree
+                       else "host SAH tree (the reference's algorithm) compiled to sibling pairs",
                        "scene_build_s_untimed": round(t_build, 3)},
             "e2e": {"value": samples_per_step / (e2e_tot.item() / KE * 1e-3) / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_tot.item() / KE, "steps": KE,
@@ -338,7 +344,7 @@ def main():
                                           "wavefront in flight (RTB_RENDER_SERIAL) and events around every launch"},
         }
         if not args.no_roofline and world == 1:
-            line["roofline"] = roofline(rt, hs, cam, cfg, stats if args.pipeline == "path" else serial_stats, mode, args.pool, args.pipeline)
+            line["roofline"] = roofline(rt, hs, cam, cfg, stats if args.pipeline == "path" else serial_stats, mode, args.pool, args.pipeline, device_tree)
         elif not args.no_roofline:
             line["roofline"] = {"note": "measured at N=1 only (one process, one GPU)"}
         if not args.no_cpu_baseline and world == 1:
@@ -365,7 +371,7 @@ def scene_bytes(d):
                + d.n_materials * 32 + d.n_textures * 32)
 
 
-def roofline(rt, hs, cam, cfg, stats, mode, pool, pipeline):
+def roofline(rt, hs, cam, cfg, stats, mode, pool, pipeline, device_tree=False):
     """The dominant kernel - path_kernel (default pipeline: one launch per step) or extend_kernel (wavefront pipeline) -
     against the HBM roof the contract asks for and against the roof that actually binds an L2-resident scene.
     Algorithmic bytes / flops per ray are SURVEY 8(d)'s per-unit figures with the traversal counts of this workload
@@ -376,7 +382,7 @@ def roofline(rt, hs, cam, cfg, stats, mode, pool, pipeline):
         hbm_peak, src = float(json.loads(peaks_file.read_text())["hbm_gbs"]), "MEASURED_PEAKS.json"
     mp = rt.measure_peaks()
     # per-ray traversal counts from the instrumented build on the same workload at reduced spp (counts per ray are spp-invariant)
-    hs_c = rt.HostScene.build(*cfg["scene"], counters=True)
+    hs_c = rt.HostScene.build(*cfg["scene"], counters=True, device_tree=device_tree)
     ds_c = rt.DeviceScene(hs_c)
     _, sc = ds_c.render(cam, spp=max(1, min(4, cfg["spp"])), max_depth=cfg["depth"], mode=mode, pool_size=pool,
                         flags=rt.RENDER_WAVEFRONT if pipeline == "wavefront" else 0)
