@@ -96,6 +96,9 @@ struct RtbCompiledTree {
   rtbc::Compiled tree;
 };
 
+#ifndef RTB_TREE_REBUILD_DEFAULT
+#define RTB_TREE_REBUILD_DEFAULT false
+#endif
 static int CompileTree(const RtbSceneDesc& d, rtbc::Compiled* out) {
   try {
     RtbSceneDesc dd = d;
@@ -110,7 +113,9 @@ static int CompileTree(const RtbSceneDesc& d, rtbc::Compiled* out) {
       cost[0] = cost[1] = cost[2] = (float)std::atof(e);
       prim_cost = cost;
     }
-    *out = rtbc::Compiler(dd, leaf_max, prim_cost).Run();
+    bool rebuild = RTB_TREE_REBUILD_DEFAULT;
+    if (const char* e = std::getenv("RTB_TREE_REBUILD")) rebuild = std::atoi(e) != 0;
+    *out = rtbc::Compiler(dd, leaf_max, prim_cost).Run(rebuild);
   } catch (const std::exception& e) {
     return Fail(RTB_EINVAL, std::string("scene compile: ") + e.what());
   }

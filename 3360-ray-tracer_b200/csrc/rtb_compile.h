@@ -93,8 +93,11 @@ class Compiler {
     for (int k = 0; k < 3; ++k) prim_cost_[k] = prim_cost ? prim_cost[k] : def[k];
   }
 
-  Compiled Run() {
-    int root = FromNode(0, 0);
+  // rebuild = true: ignore the interchange topology and build the device tree from the primitive tables alone with a
+  // surface-area heuristic over all three axes (32 bins; every split position for small sets) and the device's costs.
+  // The reference's builder bins the longest centroid axis only (bvh.h:232-250) and stops at 4 primitives.
+  Compiled Run(bool rebuild = false) {
+    int root = rebuild ? Rebuild() : FromNode(0, 0);
     Compiled out;
     if (root < 0) return out;  // nothing to hit: no pairs, the kernels report a miss for every ray
     // Traversal starts at pair 0 = the root's two children (the root's own box is never tested: a
@@ -283,6 +286,140 @@ class Compiler {
     if (may_leaf && leaf_cost <= split_cost) {
       nodes_.resize(mark);  // drop the trial subtree
       SmallSort(items, lo, hi, by_index);
+      return make_leaf();
+    }
+    if (cost_out) *cost_out = split_cost;
+    return NewInternal(l, r);
+  }
+
+  // ---- full rebuild -------------------------------------------------------------------------------------------
+  struct RItem {
+    uint32_t type, idx;
+    Box box;
+    float c[3];
+  };
+  static Box RBox(const RItem* it, size_t lo, size_t hi) {
+    Box b = Box::Empty();
+    for (size_t i = lo; i < hi; ++i) b.Grow(it[i].box);
+    return b;
+  }
+  int Rebuild() {
+    std::vector<RItem> items;
+    items.reserve((size_t)d_.n_spheres + d_.n_triangles + d_.n_rects);
+    const uint32_t counts[3] = {d_.n_spheres, d_.n_triangles, d_.n_rects};
+    for (uint32_t ty = 0; ty < 3; ++ty)
+      for (uint32_t i = 0; i < counts[ty]; ++i) {
+        RItem t;
+        t.type = ty;
+        t.idx = i;
+        t.box = PrimBox(ty, i);
+        for (int k = 0; k < 3; ++k) t.c[k] = 0.5f * t.box.lo[k] + 0.5f * t.box.hi[k];
+        items.push_back(t);
+      }
+    if (items.empty()) return -1;
+    if (items.size() > kMaxFirst) throw std::runtime_error("more than 2^24 primitives");
+    return BuildSah(items.data(), 0, items.size(), nullptr);
+  }
+  float RLeafCost(const RItem* it, size_t lo, size_t hi) const {
+    float c = 0.f;
+    for (size_t i = lo; i < hi; ++i) c += prim_cost_[it[i].type];
+    return c;
+  }
+  int BuildSah(RItem* it, size_t lo, size_t hi, float* cost_out) {
+    const size_t n = hi - lo;
+    const Box box = RBox(it, lo, hi);
+    auto by_index = [](const RItem& a, const RItem& b) { return a.type < b.type || (a.type == b.type && a.idx < b.idx); };
+    const float leaf_cost = RLeafCost(it, lo, hi);
+    auto make_leaf = [&]() {
+      CNode c;
+      c.box = box;
+      c.desc = LeafDesc(it[lo].type, it[lo].idx, static_cast<uint32_t>(n));
+      nodes_.push_back(c);
+      if (cost_out) *cost_out = leaf_cost;
+      return static_cast<int>(nodes_.size()) - 1;
+    };
+    if (n == 1) return make_leaf();
+    bool may_leaf = n <= leaf_max_;
+    if (may_leaf) {
+      std::sort(it + lo, it + hi, by_index);
+      for (size_t i = lo + 1; i < hi; ++i) may_leaf = may_leaf && it[i].type == it[lo].type && it[i].idx == it[i - 1].idx + 1;
+    }
+    size_t best_mid = lo + n / 2;
+    int best_axis = -1;
+    auto by_axis = [](int axis) {
+      return [axis](const RItem& a, const RItem& b) { return a.c[axis] < b.c[axis] || (a.c[axis] == b.c[axis] && (a.type < b.type || (a.type == b.type && a.idx < b.idx))); };
+    };
+    if (n <= 12) {  // every axis, every position
+      float best = INFINITY;
+      for (int axis = 0; axis < 3; ++axis) {
+        std::sort(it + lo, it + hi, by_axis(axis));
+        for (size_t k = 1; k < n; ++k) {
+          const float c = Area(RBox(it, lo, lo + k)) * RLeafCost(it, lo, lo + k) + Area(RBox(it, lo + k, hi)) * RLeafCost(it, lo + k, hi);
+          if (c < best) {
+            best = c;
+            best_axis = axis;
+            best_mid = lo + k;
+          }
+        }
+      }
+      std::sort(it + lo, it + hi, by_axis(best_axis));
+    } else {  // 32 centroid bins per axis
+      constexpr int kBins = 32;
+      float cmin[3] = {INFINITY, INFINITY, INFINITY}, cmax[3] = {-INFINITY, -INFINITY, -INFINITY};
+      for (size_t i = lo; i < hi; ++i)
+        for (int k = 0; k < 3; ++k) {
+          cmin[k] = std::min(cmin[k], it[i].c[k]);
+          cmax[k] = std::max(cmax[k], it[i].c[k]);
+        }
+      float best = INFINITY;
+      int best_bin = -1;
+      for (int axis = 0; axis < 3; ++axis) {
+        const float ext = cmax[axis] - cmin[axis];
+        if (!(ext > 0.f)) continue;
+        const float scale = kBins / ext;
+        Box bb[kBins];
+        float bc[kBins];
+        for (int b = 0; b < kBins; ++b) { bb[b] = Box::Empty(); bc[b] = 0.f; }
+        for (size_t i = lo; i < hi; ++i) {
+          const int b = std::min(kBins - 1, std::max(0, static_cast<int>((it[i].c[axis] - cmin[axis]) * scale)));
+          bb[b].Grow(it[i].box);
+          bc[b] += prim_cost_[it[i].type];
+        }
+        float la[kBins], lc[kBins];
+        Box acc = Box::Empty();
+        float cc = 0.f;
+        for (int b = 0; b < kBins; ++b) { acc.Grow(bb[b]); cc += bc[b]; la[b] = cc > 0.f ? Area(acc) : 0.f; lc[b] = cc; }
+        acc = Box::Empty();
+        cc = 0.f;
+        for (int b = kBins - 1; b >= 1; --b) {
+          acc.Grow(bb[b]);
+          cc += bc[b];
+          if (cc <= 0.f || lc[b - 1] <= 0.f) continue;
+          const float c = la[b - 1] * lc[b - 1] + Area(acc) * cc;
+          if (c < best) { best = c; best_axis = axis; best_bin = b; }
+        }
+      }
+      if (best_axis >= 0) {
+        const float scale = kBins / (cmax[best_axis] - cmin[best_axis]), c0 = cmin[best_axis];
+        const int axis = best_axis, bin = best_bin;
+        RItem* mid = std::partition(it + lo, it + hi, [&](const RItem& t) {
+          return std::min(kBins - 1, std::max(0, static_cast<int>((t.c[axis] - c0) * scale))) < bin;
+        });
+        best_mid = static_cast<size_t>(mid - it);
+      }
+      if (best_axis < 0 || best_mid == lo || best_mid == hi) {  // coincident centroids: halve in table order
+        std::sort(it + lo, it + hi, by_index);
+        best_mid = lo + n / 2;
+      }
+    }
+    const size_t mark = nodes_.size();
+    float cl = 0.f, cr = 0.f;
+    const int l = BuildSah(it, lo, best_mid, &cl), r = BuildSah(it, best_mid, hi, &cr);
+    const float a = std::max(Area(box), 1e-30f);
+    const float split_cost = 1.f + (Area(nodes_[l].box) * cl + Area(nodes_[r].box) * cr) / a;
+    if (may_leaf && leaf_cost <= split_cost) {
+      nodes_.resize(mark);  // drop the trial subtree
+      std::sort(it + lo, it + hi, by_index);
       return make_leaf();
     }
     if (cost_out) *cost_out = split_cost;
