@@ -592,11 +592,22 @@ __device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts
 #ifndef RTB_PATH_MIN_BLOCKS
 #define RTB_PATH_MIN_BLOCKS 4  // 64 registers: measured faster than 3 x 80 or 2 x 128 despite the spills
 #endif
-// Adaptive state of a render (kAdaptive): per-pixel planes owned by the caller.  The lane that takes a pixel is
-// its only writer, so the planes are updated with plain loads and stores.
+// Adaptive rendering.  The reference's rule is sequential per pixel: sample n+1 is taken only if the pixel has not
+// converged after sample n (wavefront.cc:62-82, pixel_state.h:53-72).  A lane that owned a pixel and ran its samples
+// one after the other reproduced that exactly but left the GPU to the slowest pixel (360 k pixels over 151 k lanes:
+// 23 ms for 12 M samples on the bunny).  Instead the samples of a pixel are traced SPECULATIVELY, R at a time, as
+// independent work items - sample k of active pixel `slot` writes its radiance to chunk[slot * R + k] - and
+// adaptive_replay_kernel folds each pixel's chunk IN SAMPLE ORDER with the rule evaluated after every sample, stops at
+// the first n where it holds and discards the rest of the chunk (at most R - 1 wasted samples per pixel).  The image,
+// the counts and the planes are those of the sequential rule, sample for sample.
 struct AdaptivePlanes {
-  float* sumsq;      // W*H*3: sum of squared sample radiance (PixelState::m2 in its sum-of-squares form)
-  uint32_t* count;   // W*H: samples recorded (PixelState::samples)
+  float* sumsq;             // W*H*3: sum of squared sample radiance (PixelState::m2 in its sum-of-squares form)
+  uint32_t* count;          // W*H: samples recorded (PixelState::samples)
+  const uint32_t* active;   // pixels still sampling in this pass
+  const unsigned* n_active; // their number (device memory: passes are enqueued without a host round trip)
+  float* chunk;             // n_active * R * 3 sample radiances of this pass
+  uint32_t chunk_r;         // R of this pass
+  uint32_t base;            // samples every active pixel has taken in this call before this pass
 };
 
 template <bool kFromQueue, bool kAdaptive>
@@ -612,7 +623,6 @@ struct PathIo {
   const uint32_t* pixel_order;
   PathState ps;
   AdaptivePlanes ad;
-  unsigned samples;  // adaptive: camera samples started by this lane
   __device__ __forceinline__ void load(uint32_t i, float4& o, float4& d) {
     if (kFromQueue) {
       o = q.ro[i];
@@ -624,15 +634,13 @@ struct PathIo {
       ps.sample = meta.x;
       ps.bounce = meta.y;
     } else if (kAdaptive) {
-      // work item = a pixel; its samples run one after the other on this lane
-      const uint32_t pixel = __ldg(&pixel_order[i]);
-      camera_ray(rc, pixel, (uint32_t)rc.spp_begin, o, d, ps);
-      ++samples;
+      const uint32_t slot = i / ad.chunk_r, k = i - slot * ad.chunk_r;
+      camera_ray(rc, __ldg(&ad.active[slot]), (uint32_t)rc.spp_begin + ad.base + k, o, d, ps);
     } else {
       generate_sample(rc, pixel_order, s0, p0, i, o, d, ps);
     }
   }
-  __device__ __forceinline__ bool finish(uint32_t, uint32_t ref, float tf, const TravRay& r, float4& o, float4& d) {
+  __device__ __forceinline__ bool finish(uint32_t i, uint32_t ref, float tf, const TravRay& r, float4& o, float4& d) {
     o = make_float4(r.ox, r.oy, r.oz, r.tmin);
     d = make_float4(r.dx, r.dy, r.dz, r.tmax);
     if (!kAdaptive) {
@@ -641,44 +649,9 @@ struct PathIo {
     }
     LocalSink sink{mk3(0.0f, 0.0f, 0.0f)};
     if (shade_path(s, rc, sink, o, d, ps, tf, ref)) return true;
-    // ---- RecordSample + IsConverged (pixel_state.h:22-72) for the pixel this lane owns
-    const uint32_t pixel = ps.pixel;
-    float* a = accum + 3 * (size_t)pixel;
-    float* q2 = ad.sumsq + 3 * (size_t)pixel;
-    const uint32_t prev = ad.count[pixel];
-    const uint32_t k = ps.sample - (uint32_t)rc.spp_begin + 1u;  // samples of this call, this one included
-    const float n = (float)(prev + k);
-    const float sx = a[0] + sink.L.x, sy = a[1] + sink.L.y, sz = a[2] + sink.L.z;
-    const float qx = q2[0] + sink.L.x * sink.L.x, qy = q2[1] + sink.L.y * sink.L.y, qz = q2[2] + sink.L.z * sink.L.z;
-    a[0] = sx; a[1] = sy; a[2] = sz;
-    q2[0] = qx; q2[1] = qy; q2[2] = qz;
-    bool stop = (int)k >= rc.spp_max;
-    if (!stop && (int)(prev + k) >= rc.min_samples) {
-      const float inv_n = 1.0f / n;
-      const float mx = sx * inv_n, my = sy * inv_n, mz = sz * inv_n;
-      if (rc.criterion == RTB_ADAPT_PIXEL_STATE) {
-        // per channel: sqrt(s^2 / n) / max(|mean|, 1e-3) <= threshold, s^2 the sample variance m2 / (n - 1)
-        const float inv_n1 = 1.0f / fmaxf(n - 1.0f, 1.0f);
-        const float vx = fmaxf(qx - sx * mx, 0.0f) * inv_n1, vy = fmaxf(qy - sy * my, 0.0f) * inv_n1, vz = fmaxf(qz - sz * mz, 0.0f) * inv_n1;
-        const float tx = rc.rel_threshold * fmaxf(fabsf(mx), 1e-3f), ty = rc.rel_threshold * fmaxf(fabsf(my), 1e-3f),
-                    tz = rc.rel_threshold * fmaxf(fabsf(mz), 1e-3f);
-        stop = vx * inv_n <= tx * tx && vy * inv_n <= ty * ty && vz * inv_n <= tz * tz;
-      } else {
-        // AdaptiveSampler (sampler.h:61-71) with the running-total slip repaired: luminance of the population
-        // variance against the mean luminance
-        const float vx = qx * inv_n - mx * mx, vy = qy * inv_n - my * my, vz = qz * inv_n - mz * mz;
-        const float lum_v = fmaxf(0.2126f * vx + 0.7152f * vy + 0.0722f * vz, 0.0f);
-        const float lum_m = 0.2126f * mx + 0.7152f * my + 0.0722f * mz;
-        stop = sqrtf(lum_v * inv_n) < rc.rel_threshold * (lum_m + 1e-3f);
-      }
-    }
-    if (stop) {
-      ad.count[pixel] = prev + k;
-      return false;
-    }
-    camera_ray(rc, pixel, ps.sample + 1u, o, d, ps);
-    ++samples;
-    return true;
+    float* c = ad.chunk + 3 * (size_t)i;  // work item i = (slot, k): this sample's radiance (0 for an absorbed path)
+    c[0] = sink.L.x; c[1] = sink.L.y; c[2] = sink.L.z;
+    return false;
   }
 };
 
@@ -689,13 +662,71 @@ __global__ void __launch_bounds__(kTraceBlock, RTB_PATH_MIN_BLOCKS) path_kernel(
                                                                                unsigned long long* ray_count, HitCounters* cnt, AdaptivePlanes ad) {
   extern __shared__ float4 smem_pairs[];
   if (kUseSmem) stage_top(s, smem_pairs);
-  PathIo<kFromQueue, kAdaptive> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathState{}, ad, 0u};
+  if (kAdaptive) n = *ad.n_active * ad.chunk_r;  // one work item per (active pixel, sample of the chunk)
+  PathIo<kFromQueue, kAdaptive> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathState{}, ad};
   trace_loop<kUseSmem>(s, smem_pairs, smem_stack_base(s, smem_pairs, kUseSmem), io, cursor, cnt);
   const unsigned total = __reduce_add_sync(kFull, io.rays);
   if ((threadIdx.x & 31u) == 0u && total) atomicAdd(ray_count, (unsigned long long)total);
-  if (kAdaptive) {
-    const unsigned started = __reduce_add_sync(kFull, io.samples);
-    if ((threadIdx.x & 31u) == 0u && started) atomicAdd(ray_count + 1, (unsigned long long)started);
+  if (kAdaptive && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(ray_count + 1, (unsigned long long)n);  // camera samples started
+}
+
+// RecordSample + IsConverged (pixel_state.h:22-72) over one chunk of every active pixel, in sample order.  Pixels that
+// neither stopped nor reached spp_max are appended to the next pass's active list.
+__global__ void __launch_bounds__(256) adaptive_replay_kernel(RenderConsts rc, float* accum, AdaptivePlanes ad, uint32_t* next_active,
+                                                              unsigned* n_next) {
+  const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+  bool carry_on = false;
+  uint32_t pixel = 0;
+  if (slot < *ad.n_active) {
+    pixel = ad.active[slot];
+    float* a = accum + 3 * (size_t)pixel;
+    float* q2 = ad.sumsq + 3 * (size_t)pixel;
+    const uint32_t prev = ad.count[pixel];  // samples of earlier calls (RTB_RENDER_KEEP_ACCUM), written back when the pixel stops
+    float sx = a[0], sy = a[1], sz = a[2], qx = q2[0], qy = q2[1], qz = q2[2];
+    const float* c = ad.chunk + 3 * (size_t)slot * ad.chunk_r;
+    bool stop = false;
+    uint32_t k = 0;
+    while (k < ad.chunk_r && !stop) {
+      const float lx = c[3 * k], ly = c[3 * k + 1], lz = c[3 * k + 2];
+      ++k;
+      sx += lx; sy += ly; sz += lz;
+      qx += lx * lx; qy += ly * ly; qz += lz * lz;
+      const uint32_t mine = ad.base + k;  // samples of this call, this one included
+      const uint32_t total = prev + mine;
+      stop = (int)mine >= rc.spp_max;
+      if (!stop && (int)total >= rc.min_samples) {
+        const float n = (float)total, inv_n = 1.0f / n;
+        const float mx = sx * inv_n, my = sy * inv_n, mz = sz * inv_n;
+        if (rc.criterion == RTB_ADAPT_PIXEL_STATE) {
+          // per channel: sqrt(s^2 / n) / max(|mean|, 1e-3) <= threshold, s^2 the sample variance m2 / (n - 1)
+          const float inv_n1 = 1.0f / fmaxf(n - 1.0f, 1.0f);
+          const float vx = fmaxf(qx - sx * mx, 0.0f) * inv_n1, vy = fmaxf(qy - sy * my, 0.0f) * inv_n1, vz = fmaxf(qz - sz * mz, 0.0f) * inv_n1;
+          const float tx = rc.rel_threshold * fmaxf(fabsf(mx), 1e-3f), ty = rc.rel_threshold * fmaxf(fabsf(my), 1e-3f),
+                      tz = rc.rel_threshold * fmaxf(fabsf(mz), 1e-3f);
+          stop = vx * inv_n <= tx * tx && vy * inv_n <= ty * ty && vz * inv_n <= tz * tz;
+        } else {
+          // AdaptiveSampler (sampler.h:61-71) with the running-total slip repaired: luminance of the population
+          // variance against the mean luminance
+          const float vx = qx * inv_n - mx * mx, vy = qy * inv_n - my * my, vz = qz * inv_n - mz * mz;
+          const float lum_v = fmaxf(0.2126f * vx + 0.7152f * vy + 0.0722f * vz, 0.0f);
+          const float lum_m = 0.2126f * mx + 0.7152f * my + 0.0722f * mz;
+          stop = sqrtf(lum_v * inv_n) < rc.rel_threshold * (lum_m + 1e-3f);
+        }
+      }
+    }
+    a[0] = sx; a[1] = sy; a[2] = sz;
+    q2[0] = qx; q2[1] = qy; q2[2] = qz;
+    if (stop) ad.count[pixel] = prev + ad.base + k;
+    carry_on = !stop;
+  }
+  // compact the pixels that carry on: ballot + prefix inside the warp, one atomic per warp
+  const unsigned ballot = __ballot_sync(0xffffffffu, carry_on);
+  if (ballot) {
+    const unsigned lane = threadIdx.x & 31u;
+    unsigned base = 0;
+    if (lane == (unsigned)(__ffs(ballot) - 1)) base = atomicAdd(n_next, (unsigned)__popc(ballot));
+    base = __shfl_sync(0xffffffffu, base, __ffs(ballot) - 1);
+    if (carry_on) next_active[base + __popc(ballot & ((1u << lane) - 1u))] = pixel;
   }
 }
 

@@ -278,7 +278,9 @@ int rtb_render_device(RtbScene* scene, const RtbCamera* cam, const RtbRenderPara
  * planes: rgb_sum (W*H*3, PixelState::sum), rgb_sumsq (W*H*3, sum of squares: m2 = sumsq - sum^2/n) and count
  * (W*H, PixelState::samples).  The image is rgb_sum / count (wavefront.cc:229-234) - rtb_resolve_counts.
  * Without RTB_RENDER_KEEP_ACCUM the three planes are zeroed first; with it the call continues them (every pixel
- * takes at least one more sample).  RtbStats.samples = camera samples actually started.  Path kernel only. */
+ * takes at least one more sample).  Samples are traced speculatively, a chunk per pixel at a time, and folded in sample
+ * order with the rule evaluated after every one: planes and image are those of the sequential rule; RtbStats.samples
+ * counts the camera samples started, including the up to chunk-1 per pixel that the rule then discarded.  Path kernel only. */
 int rtb_render_adaptive(RtbScene* scene, const RtbCamera* cam, const RtbRenderParams* params, const RtbAdaptive* adaptive,
                         float* rgb_sum, float* rgb_sumsq, uint32_t* count, RtbStats* stats);
 int rtb_render_adaptive_device(RtbScene* scene, const RtbCamera* cam, const RtbRenderParams* params, const RtbAdaptive* adaptive,
