@@ -610,6 +610,35 @@ struct AdaptivePlanes {
   uint32_t base;            // samples every active pixel has taken in this call before this pass
 };
 
+// The path state (throughput, pixel, sample, bounce) is touched once per bounce, the slab constants of the ray once per
+// node step.  Left to itself ptxas keeps the former in registers across the traversal loop and spills six of the
+// latter (6 x LDL in every node step, profiles/r01_path_kernel_bunny_session17.txt), so the path state is parked in
+// shared memory explicitly: [field][thread], conflict-free, 6 KB per CTA.  Measured 10.28 -> 10.07 ms on bunny C3
+// (spill traffic 434/268 -> 338/140 bytes per thread).  Parking the ray's origin / direction and the best hit the
+// same way (reloaded at every leaf step) was 5-8 % slower.
+#ifndef RTB_PS_SMEM
+#define RTB_PS_SMEM 1
+#endif
+struct PathStateRef {
+#if RTB_PS_SMEM
+  uint32_t* col;  // this thread's column of the CTA's [6][kTraceBlock] array
+  __device__ __forceinline__ void put(const PathState& ps) {
+    col[0] = __float_as_uint(ps.tr); col[kTraceBlock] = __float_as_uint(ps.tg); col[2 * kTraceBlock] = __float_as_uint(ps.tb);
+    col[3 * kTraceBlock] = ps.pixel; col[4 * kTraceBlock] = ps.sample; col[5 * kTraceBlock] = ps.bounce;
+  }
+  __device__ __forceinline__ PathState get() const {
+    PathState ps;
+    ps.tr = __uint_as_float(col[0]); ps.tg = __uint_as_float(col[kTraceBlock]); ps.tb = __uint_as_float(col[2 * kTraceBlock]);
+    ps.pixel = col[3 * kTraceBlock]; ps.sample = col[4 * kTraceBlock]; ps.bounce = col[5 * kTraceBlock];
+    return ps;
+  }
+#else
+  PathState reg;
+  __device__ __forceinline__ void put(const PathState& ps) { reg = ps; }
+  __device__ __forceinline__ PathState get() const { return reg; }
+#endif
+};
+
 template <bool kFromQueue, bool kAdaptive>
 struct PathIo {
   static constexpr int kServiceLanes = RTB_PATH_REFILL_LANES;
@@ -621,9 +650,10 @@ struct PathIo {
   PathQueue q;
   uint32_t s0, p0;  // divmod(first sample of this launch, n_pixels)
   const uint32_t* pixel_order;
-  PathState ps;
+  PathStateRef psr;
   AdaptivePlanes ad;
   __device__ __forceinline__ void load(uint32_t i, float4& o, float4& d) {
+    PathState ps;
     if (kFromQueue) {
       o = q.ro[i];
       d = q.rd[i];
@@ -639,16 +669,23 @@ struct PathIo {
     } else {
       generate_sample(rc, pixel_order, s0, p0, i, o, d, ps);
     }
+    psr.put(ps);
   }
   __device__ __forceinline__ bool finish(uint32_t i, uint32_t ref, float tf, const TravRay& r, float4& o, float4& d) {
     o = make_float4(r.ox, r.oy, r.oz, r.tmin);
     d = make_float4(r.dx, r.dy, r.dz, r.tmax);
+    PathState ps = psr.get();
     if (!kAdaptive) {
       AtomicSink sink{accum};
-      return shade_path(s, rc, sink, o, d, ps, tf, ref);
+      const bool alive = shade_path(s, rc, sink, o, d, ps, tf, ref);
+      if (alive) psr.put(ps);
+      return alive;
     }
     LocalSink sink{mk3(0.0f, 0.0f, 0.0f)};
-    if (shade_path(s, rc, sink, o, d, ps, tf, ref)) return true;
+    if (shade_path(s, rc, sink, o, d, ps, tf, ref)) {
+      psr.put(ps);
+      return true;
+    }
     float* c = ad.chunk + 3 * (size_t)i;  // work item i = (slot, k): this sample's radiance (0 for an absorbed path)
     c[0] = sink.L.x; c[1] = sink.L.y; c[2] = sink.L.z;
     return false;
@@ -663,7 +700,12 @@ __global__ void __launch_bounds__(kTraceBlock, RTB_PATH_MIN_BLOCKS) path_kernel(
   extern __shared__ float4 smem_pairs[];
   if (kUseSmem) stage_top(s, smem_pairs);
   if (kAdaptive) n = *ad.n_active * ad.chunk_r;  // one work item per (active pixel, sample of the chunk)
-  PathIo<kFromQueue, kAdaptive> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathState{}, ad};
+#if RTB_PS_SMEM
+  __shared__ uint32_t path_state[6 * kTraceBlock];
+  PathIo<kFromQueue, kAdaptive> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathStateRef{path_state + threadIdx.x}, ad};
+#else
+  PathIo<kFromQueue, kAdaptive> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathStateRef{PathState{}}, ad};
+#endif
   trace_loop<kUseSmem>(s, smem_pairs, smem_stack_base(s, smem_pairs, kUseSmem), io, cursor, cnt);
   const unsigned total = __reduce_add_sync(kFull, io.rays);
   if ((threadIdx.x & 31u) == 0u && total) atomicAdd(ray_count, (unsigned long long)total);
