@@ -106,7 +106,7 @@ assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 16
 RTB_SYMBOLS = [
     "rtb_last_error", "rtb_abi_version", "rtb_tree_compile", "rtb_tree_destroy", "rtb_device_count", "rtb_init", "rtb_shutdown", "rtb_scene_create",
     "rtb_scene_destroy", "rtb_intersect_batch", "rtb_intersect_batch_device", "rtb_render", "rtb_render_device",
-    "rtb_render_adaptive", "rtb_render_adaptive_device", "rtb_resolve_counts", "rtb_resolve_counts_device",
+    "rtb_render_adaptive", "rtb_render_adaptive_device", "rtb_resolve_counts", "rtb_resolve_counts_device", "rtb_pixel_state_fold",
     "rtb_resolve_device", "rtb_resolve", "rtb_measure_l2_gbs", "rtb_measure_fp32_tflops", "rtb_measure_fp64_tflops",
 ]
 RTH_SYMBOLS = [
@@ -162,6 +162,7 @@ def load(counters: bool = False) -> C.CDLL:
     lib.rtb_render_adaptive.argtypes = [C.c_void_p, C.POINTER(RtbCamera), C.POINTER(RtbRenderParams), C.POINTER(RtbAdaptive), C.c_void_p,
                                         C.c_void_p, C.c_void_p, C.POINTER(RtbStats)]
     lib.rtb_render_adaptive_device.argtypes = lib.rtb_render_adaptive.argtypes
+    lib.rtb_pixel_state_fold.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.POINTER(RtbAdaptive), C.c_void_p, C.c_void_p, C.c_void_p]
     lib.rtb_resolve_counts.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     lib.rtb_resolve_counts_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
     lib.rtb_resolve.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]
@@ -373,6 +374,18 @@ class DeviceScene:
         st = RtbStats()
         _check(self._lib, self._lib.rtb_render_device(self._h, C.byref(cam), C.byref(prm), d_accum_ptr, C.byref(st)))
         return st.as_dict()
+
+
+def pixel_state_fold(samples: np.ndarray, rel_threshold: float = 0.05, min_samples: int = 16, criterion: int = ADAPT_PIXEL_STATE,
+                     counters: bool = False):
+    """integrator::RecordSample + IsConverged over given sample sequences [n, k, 3]: (sum[n,3], sumsq[n,3], count[n])."""
+    lib = load(counters)
+    a = np.ascontiguousarray(samples, dtype=np.float32)
+    n, k, _ = a.shape
+    ad = RtbAdaptive(rel_threshold, min_samples, criterion, 0)
+    s, q, c = np.zeros((n, 3), np.float32), np.zeros((n, 3), np.float32), np.zeros(n, np.uint32)
+    _check(lib, lib.rtb_pixel_state_fold(_ptr(a), n, k, C.byref(ad), _ptr(s), _ptr(q), _ptr(c)))
+    return s, q, c
 
 
 def resolve_counts(rgb_sum: np.ndarray, count: np.ndarray, counters: bool = False) -> np.ndarray:

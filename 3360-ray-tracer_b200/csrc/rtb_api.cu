@@ -1050,6 +1050,47 @@ int rtb_render_adaptive(RtbScene* s, const RtbCamera* cam, const RtbRenderParams
   return RTB_OK;
 }
 
+int rtb_pixel_state_fold(const float* samples, size_t n_pixels, int k, const RtbAdaptive* ad, float* rgb_sum, float* rgb_sumsq, uint32_t* count) {
+  if (!samples || !ad || !rgb_sum || !rgb_sumsq || !count || k < 1) return Fail(RTB_EINVAL, "bad argument");
+  if (ad->criterion != RTB_ADAPT_PIXEL_STATE && ad->criterion != RTB_ADAPT_LUMINANCE) return Fail(RTB_EINVAL, "unknown adaptive criterion");
+  if (n_pixels == 0) return RTB_OK;
+  if (n_pixels > (1u << 30) || n_pixels * (size_t)k > (1ull << 32)) return Fail(RTB_EINVAL, "too many samples");
+  int rc = EnsureInit();
+  if (rc != RTB_OK) return rc;
+  const size_t n = n_pixels, fb = n * 3 * sizeof(float), sb = n * (size_t)k * 3 * sizeof(float);
+  auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
+  const size_t o_sum = 0, o_sq = o_sum + up(fb), o_cnt = o_sq + up(fb), o_act = o_cnt + up(n * 4), o_next = o_act + up(n * 4), o_n = o_next + up(n * 4),
+               o_smp = o_n + 256, total = o_smp + up(sb);
+  char* d = nullptr;
+  RTB_CUDA(cudaMalloc(reinterpret_cast<void**>(&d), total));
+  cudaStream_t st = g_stream;
+  const uint32_t n32 = (uint32_t)n;
+  cudaError_t e = cudaMemsetAsync(d, 0, o_act, st);  // sum, sumsq, count
+  if (e == cudaSuccess) e = cudaMemsetAsync(d + o_n, 0, 256, st);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(d + o_n, &n32, 4, cudaMemcpyHostToDevice, st);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(d + o_smp, samples, sb, cudaMemcpyHostToDevice, st);
+  if (e == cudaSuccess) {
+    rtb::iota_kernel<<<(n32 + 255) / 256, 256, 0, st>>>(reinterpret_cast<uint32_t*>(d + o_act), n32);
+    rtb::RenderConsts rcst{};
+    rcst.spp_max = k;
+    rcst.min_samples = ad->min_samples;
+    rcst.criterion = ad->criterion;
+    rcst.rel_threshold = ad->rel_threshold;
+    rtb::AdaptivePlanes pl{reinterpret_cast<float*>(d + o_sq), reinterpret_cast<uint32_t*>(d + o_cnt), reinterpret_cast<uint32_t*>(d + o_act),
+                           reinterpret_cast<unsigned*>(d + o_n), reinterpret_cast<float*>(d + o_smp), (uint32_t)k, 0u};
+    rtb::adaptive_replay_kernel<<<(n32 + 255) / 256, 256, 0, st>>>(rcst, reinterpret_cast<float*>(d + o_sum), pl, reinterpret_cast<uint32_t*>(d + o_next),
+                                                                 reinterpret_cast<unsigned*>(d + o_n) + 1);
+    e = cudaMemcpyAsync(rgb_sum, d + o_sum, fb, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(rgb_sumsq, d + o_sq, fb, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(count, d + o_cnt, n * 4, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess) e = cudaGetLastError();
+  }
+  cudaFree(d);
+  if (e != cudaSuccess) return Fail(RTB_ECUDA, std::string("pixel_state_fold: ") + cudaGetErrorString(e));
+  return RTB_OK;
+}
+
 int rtb_resolve_counts_device(const float* d_rgb_sum, const uint32_t* d_count, size_t n_pixels, uint8_t* d_rgb8, void* stream) {
   if (!d_rgb_sum || !d_count || !d_rgb8) return Fail(RTB_EINVAL, "bad argument");
   int rc = EnsureInit();

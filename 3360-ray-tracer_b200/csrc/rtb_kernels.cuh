@@ -820,6 +820,11 @@ __global__ void resolve_kernel(const float* __restrict__ rgb_sum, size_t n_value
   rgb8[i] = (uint8_t)(int)(256 * g);
 }
 
+__global__ void iota_kernel(uint32_t* v, uint32_t n) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) v[i] = i;
+}
+
 // adaptive form: mean = sum / count of the pixel, black where nothing was recorded (wavefront.cc:229-234)
 __global__ void resolve_counts_kernel(const float* __restrict__ rgb_sum, const uint32_t* __restrict__ count, size_t n_values,
                                       uint8_t* __restrict__ rgb8) {

@@ -285,6 +285,12 @@ int rtb_render_adaptive(RtbScene* scene, const RtbCamera* cam, const RtbRenderPa
                         float* rgb_sum, float* rgb_sumsq, uint32_t* count, RtbStats* stats);
 int rtb_render_adaptive_device(RtbScene* scene, const RtbCamera* cam, const RtbRenderParams* params, const RtbAdaptive* adaptive,
                                float* d_rgb_sum, float* d_rgb_sumsq, uint32_t* d_count, RtbStats* stats);
+/* integrator::RecordSample + IsConverged (src/integrator/pixel_state.h:22-72) as a batch operation on given samples:
+ * for every pixel, fold samples[pixel*k .. pixel*k+k) (rgb floats) into its PixelState planes IN ORDER, evaluating the
+ * stop rule after each one exactly as rtb_render_adaptive does (same kernel), and stop at the first sample where it
+ * holds.  The planes are zeroed first; count[pixel] = samples recorded (k if the rule never held).  Host buffers. */
+int rtb_pixel_state_fold(const float* samples, size_t n_pixels, int k, const RtbAdaptive* adaptive, float* rgb_sum,
+                         float* rgb_sumsq, uint32_t* count);
 /* write_color of rgb_sum / count per pixel (black where count is 0, wavefront.cc:229-234). */
 int rtb_resolve_counts_device(const float* d_rgb_sum, const uint32_t* d_count, size_t n_pixels, uint8_t* d_rgb8, void* stream);
 int rtb_resolve_counts(const float* rgb_sum, const uint32_t* count, size_t n_pixels, uint8_t* rgb8);

@@ -305,3 +305,37 @@ void port_intersect(const void* h, const float* rays8, size_t n, double* t_out, 
     gid_out[i] = gid;
   }
 }
+
+/* ---- integrator::PixelState: RecordSample + Variance + IsConverged (src/integrator/pixel_state.h:13-72) ----------
+ * Welford update per channel (pixel_state.h:26-36), sample variance m2/(n-1) (pixel_state.h:41-49), converged when
+ * n >= min_spp and for every channel sqrt(var)/sqrt(n) / max(|mean|, 1e-3) <= rel_threshold (pixel_state.h:53-71).
+ * Driven as WavefrontRenderer::Render drives it (src/renderer/wavefront.cc:120-127, 70-71): record, test, and a
+ * converged pixel takes no further samples.  samples: n_seq x len x 3 doubles; stop_n[i] = samples recorded. */
+void port_pixel_state_run(const double* samples, size_t n_seq, int len, double rel_threshold, int min_spp, int32_t* stop_n, double* sum,
+                          double* m2_out) {
+  for (size_t i = 0; i < n_seq; ++i) {
+    double s[3] = {0, 0, 0}, mean[3] = {0, 0, 0}, m2[3] = {0, 0, 0};
+    int n = 0, converged = 0;
+    for (int k = 0; k < len && !converged; ++k) {
+      const double* x = samples + (i * (size_t)len + (size_t)k) * 3;
+      ++n;
+      for (int c = 0; c < 3; ++c) {
+        const double delta = x[c] - mean[c];
+        mean[c] += delta / n;
+        m2[c] += (x[c] - mean[c]) * delta;
+        s[c] += x[c];
+      }
+      if (n >= min_spp) {
+        int ok = 1;
+        for (int c = 0; c < 3 && ok; ++c) {
+          const double var = n > 1 ? m2[c] / (n - 1) : 0.0;
+          const double mu = fmax(fabs(mean[c]), 1e-3);
+          if (sqrt(var) / sqrt((double)n) / mu > rel_threshold) ok = 0;
+        }
+        converged = ok;
+      }
+    }
+    stop_n[i] = n;
+    for (int c = 0; c < 3; ++c) { sum[3 * i + c] = s[c]; m2_out[3 * i + c] = m2[c]; }
+  }
+}

@@ -25,8 +25,21 @@ def _load():
     lib.port_scene_free.argtypes = [C.c_void_p]
     lib.port_prim_count.argtypes = [C.c_void_p]
     lib.port_intersect.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int]
+    lib.port_pixel_state_run.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_double, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.port_pixel_state_run.restype = None
     _LIB = lib
     return lib
+
+
+def pixel_state_run(samples, rel_threshold: float = 0.05, min_spp: int = 16):
+    """oracle/port.c restatement of RecordSample / IsConverged on sample sequences [n, len, 3]: (stop_n, sum, m2)."""
+    lib = _load()
+    a = np.ascontiguousarray(samples, np.float64)
+    n, ln, _ = a.shape
+    stop = np.zeros(n, np.int32)
+    s, m2 = np.zeros((n, 3), np.float64), np.zeros((n, 3), np.float64)
+    lib.port_pixel_state_run(a.ctypes.data, n, ln, rel_threshold, min_spp, stop.ctypes.data, s.ctypes.data, m2.ctypes.data)
+    return stop, s, m2
 
 
 class PortOracle:

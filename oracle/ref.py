@@ -38,6 +38,8 @@ def _load(fast: bool):
                                  C.c_void_p, C.c_void_p, C.c_int]
     lib.ora_render_b.restype = C.c_double
     lib.ora_render_b.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+    lib.ora_pixel_state_run.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_double, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.ora_pixel_state_run.restype = None
     lib.ora_texture_value.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]
     _LIBS[fast] = lib
     return lib
@@ -135,6 +137,17 @@ def camera_rays(cfg16, ij, seed: int = 1, fast: bool = False) -> np.ndarray:
     out = np.zeros((ij.shape[0], 6), np.float64)
     lib.ora_camera_rays(_p(cfg), _p(ij), ij.shape[0], seed, _p(out))
     return out
+
+
+def pixel_state_run(samples, rel_threshold: float = 0.05, min_spp: int = 16, fast: bool = False):
+    """The reference's own RecordSample / IsConverged on sample sequences [n, len, 3]: (stop_n, sum, m2)."""
+    lib = _load(fast)
+    a = np.ascontiguousarray(samples, np.float64)
+    n, ln, _ = a.shape
+    stop = np.zeros(n, np.int32)
+    s, m2 = np.zeros((n, 3), np.float64), np.zeros((n, 3), np.float64)
+    lib.ora_pixel_state_run(_p(a), n, ln, rel_threshold, min_spp, _p(stop), _p(s), _p(m2))
+    return stop, s, m2
 
 
 def num_threads(fast: bool = False) -> int:

@@ -31,6 +31,7 @@
 
 #include "core/random.h"
 #include "integrator/cpu_ray_integrator.h"
+#include "integrator/pixel_state.h"
 #include "renderer/wavefront.h"
 #include "geom/bvh.h"
 #include "geom/rect.h"
@@ -406,6 +407,24 @@ double ora_render_b(void* h, const double* cfg, int max_depth, int max_samples, 
     queue_sizes[k] = int32_t(std::strtol(text.c_str() + pos, nullptr, 10));
   }
   return secs;
+}
+
+// integrator::RecordSample + IsConverged (src/integrator/pixel_state.h:22-72) driven the way WavefrontRenderer::Render
+// drives them (wavefront.cc:120-127: record, then mark converged; a converged pixel gets no further samples,
+// wavefront.cc:70-71).  samples: n_seq x len x 3 doubles.  stop_n[i] = PixelState::samples when the pixel stopped
+// (len if it never converged); sum / m2: the PixelState fields at that point.
+void ora_pixel_state_run(const double* samples, size_t n_seq, int len, double rel_threshold, int min_spp, int32_t* stop_n, double* sum,
+                         double* m2) {
+  for (size_t i = 0; i < n_seq; ++i) {
+    integrator::PixelState ps;
+    for (int k = 0; k < len && !ps.converged; ++k) {
+      const double* c = samples + (i * size_t(len) + size_t(k)) * 3;
+      integrator::RecordSample(ps, core::Color(c[0], c[1], c[2]));
+      if (!ps.converged && integrator::IsConverged(ps, rel_threshold, min_spp)) ps.converged = true;
+    }
+    stop_n[i] = ps.samples;
+    for (int ch = 0; ch < 3; ++ch) { sum[3 * i + ch] = ps.sum[ch]; m2[3 * i + ch] = ps.m2[ch]; }
+  }
 }
 
 // Texture::Value and Material::Emitted probes (ImageTexture pipeline check).

@@ -120,6 +120,29 @@ def test_matches_reference_wavefront_renderer(rt, golden_dir, scenes, name):
     assert abs(rgb8.mean() - mu.mean()) <= 1.0, f"{name}: mean byte {rgb8.mean():.2f} vs reference {mu.mean():.2f}"
 
 
+def test_stop_rule_against_reference_pixel_state(rt, golden_dir):
+    """rtb_pixel_state_fold (the replay kernel of the adaptive renderer) on 4096 given sample sequences against the
+    reference's own RecordSample / IsConverged (tests/golden/pixel_state.npz): the stop count is the reference's except
+    where the decision is within float rounding of the threshold; sums agree where the counts do."""
+    from test_oracle_port import _pixel_state_golden
+    g, x = _pixel_state_golden(golden_dir)
+    for i, (thr, mn) in enumerate(g["settings"]):
+        s, q, c = rt.pixel_state_fold(x, rel_threshold=float(thr), min_samples=int(mn))
+        ref_n = g[f"stop_{i}"]
+        same = c.astype(np.int64) == ref_n
+        assert same.mean() >= 0.995, f"setting {i}: only {same.mean():.4f} of the stop counts equal the reference's"
+        ref_sum = g[f"sum_{i}"]
+        assert np.all(np.abs(s[same] - ref_sum[same]) <= 2e-5 * np.maximum(np.abs(ref_sum[same]), 1e-3))
+        # m2 = sumsq - sum^2 / n
+        n = ref_n[same].astype(np.float64)[:, None]
+        m2 = q[same].astype(np.float64) - s[same].astype(np.float64) ** 2 / n
+        ref_m2 = g[f"m2_{i}"][same]
+        scale = np.maximum(q[same].astype(np.float64), 1e-6)
+        assert np.all(np.abs(m2 - ref_m2) <= 1e-4 * scale)
+        # a different count means the rule was decided the other way at ONE sample: both stop where their own arithmetic says
+        assert np.all(c >= int(mn)) and np.all(c <= x.shape[1])
+
+
 def test_continue_with_keep_accum(rt, scenes):
     ds = scenes["cornell"]
     cam = rt.camera_init(rt.camera_config(**PATHB_CAMERAS["cornell"]))
