@@ -376,9 +376,9 @@ __device__ __forceinline__ void camera_ray(const RenderConsts& rc, uint32_t pixe
   f3 origin = mk3(c.center[0], c.center[1], c.center[2]);
   if (c.defocus_angle > 0.0f) {
     // uniform point in the unit disk: same distribution as RandomInUnitDisk's rejection loop (math_utils.h:83-88)
-    const float rr = sqrtf(u01(rnd.z));
+    const float rr = shade_sqrt(u01(rnd.z));
     float sn, cs;
-    sincospif(2.0f * u01(rnd.w), &sn, &cs);
+    shade_sincos2pi(u01(rnd.w), &sn, &cs);
     const float dxk = rr * cs, dyk = rr * sn;
     origin = mk3(c.center[0] + dxk * c.disk_u[0] + dyk * c.disk_v[0], c.center[1] + dxk * c.disk_u[1] + dyk * c.disk_v[1],
                  c.center[2] + dxk * c.disk_u[2] + dyk * c.disk_v[2]);
@@ -508,7 +508,7 @@ __device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts
         const float eta = front ? (1.0f / m.ior) : m.ior;
         const f3 ud = normalize3(d);
         const float cos_theta = fminf(dot3(-ud, nrm), 1.0f);
-        const float sin_theta = sqrtf(fmaxf(0.0f, 1.0f - cos_theta * cos_theta));
+        const float sin_theta = shade_sqrt(fmaxf(0.0f, 1.0f - cos_theta * cos_theta));
         const bool cannot_refract = eta * sin_theta > 1.0f;
         dir = (cannot_refract || schlick(cos_theta, eta) > u01(rnd.z)) ? reflect3(ud, nrm) : refract3(ud, nrm, eta);
         alive = true;
@@ -531,8 +531,8 @@ __device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts
         // wavefront.cc:176-186 multiplies by f*cos/pdf = albedo.  RandomCosineDirection math_utils.h:104-123.
         const float r1 = u01(rnd.x), r2 = u01(rnd.y);
         float sn, cs;
-        sincospif(2.0f * r1, &sn, &cs);
-        const float rr = sqrtf(r2), z = sqrtf(fmaxf(0.0f, 1.0f - r2));
+        shade_sincos2pi(r1, &sn, &cs);
+        const float rr = shade_sqrt(r2), z = shade_sqrt(fmaxf(0.0f, 1.0f - r2));
         const f3 w = normalize3(nrm);
         const f3 a = fabsf(w.x) > 0.9f ? mk3(0, 1, 0) : mk3(1, 0, 0);
         const f3 vv = normalize3(cross3(w, a));
@@ -555,7 +555,7 @@ __device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts
         const float eta = front ? (1.0f / m.ior) : m.ior;
         const f3 wi_inc = normalize3(d);
         const float cos_i = fminf(fmaxf(dot3(wi_inc, nrm), -1.0f), 1.0f);
-        const float sin_i = sqrtf(fmaxf(0.0f, 1.0f - cos_i * cos_i));
+        const float sin_i = shade_sqrt(fmaxf(0.0f, 1.0f - cos_i * cos_i));
         const float sin_t = eta * sin_i;
         alive = true;
         if (sin_t >= 1.0f || u01(rnd.z) < schlick(fabsf(cos_i), m.ior)) {

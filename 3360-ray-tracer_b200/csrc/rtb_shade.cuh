@@ -23,11 +23,40 @@ __device__ __forceinline__ f3 normalize3(f3 v) {
 
 // Uniform direction on the unit sphere.  Same distribution as core::RandomUnitVector's rejection
 // loop (math_utils.h:62-70), sampled directly (z uniform, phi uniform) so the warp never diverges.
+// Shading arithmetic is Monte-Carlo sampling in FP32: the special-function units' accuracy (MUFU.RSQ / SIN / COS,
+// ~1e-6 absolute on [-pi, pi]) is far inside the estimator's noise, and saves the ~30 instructions per bounce that the
+// correctly rounded sqrtf / sincospif / division sequences cost (RTB_FAST_SHADE_MATH=0 restores them).
+#ifndef RTB_FAST_SHADE_MATH
+#define RTB_FAST_SHADE_MATH 1
+#endif
+__device__ __forceinline__ float shade_sqrt(float x) {  // x >= 0
+#if RTB_FAST_SHADE_MATH
+  const float t = fmaxf(x, 1e-30f);
+  return t * rsqrtf(t);
+#else
+  return sqrtf(x);
+#endif
+}
+__device__ __forceinline__ float shade_rcp(float x) {
+#if RTB_FAST_SHADE_MATH
+  return __fdividef(1.0f, x);
+#else
+  return 1.0f / x;
+#endif
+}
+// sine and cosine of 2 pi u, u in [0, 1)
+__device__ __forceinline__ void shade_sincos2pi(float u, float* s, float* c) {
+#if RTB_FAST_SHADE_MATH
+  __sincosf(fmaf(6.283185307179586f, u, -3.14159265358979f), s, c);  // the same uniform angle, shifted into MUFU's accurate range
+#else
+  sincospif(2.0f * u, s, c);
+#endif
+}
 __device__ __forceinline__ f3 unit_vector(float u1, float u2) {
   const float z = 1.0f - 2.0f * u1;
-  const float rxy = sqrtf(fmaxf(0.0f, 1.0f - z * z));
+  const float rxy = shade_sqrt(fmaxf(0.0f, 1.0f - z * z));
   float s, c;
-  sincospif(2.0f * u2, &s, &c);
+  shade_sincos2pi(u2, &s, &c);
   return {rxy * c, rxy * s, z};
 }
 
@@ -36,7 +65,7 @@ __device__ __forceinline__ f3 reflect3(f3 v, f3 n) { return v - (2.0f * dot3(v, 
 __device__ __forceinline__ f3 refract3(f3 uv, f3 n, float eta) {
   const float cos_theta = fminf(dot3(-uv, n), 1.0f);
   const f3 perp = eta * (uv + cos_theta * n);
-  const f3 par = (-sqrtf(fabsf(1.0f - dot3(perp, perp)))) * n;
+  const f3 par = (-shade_sqrt(fabsf(1.0f - dot3(perp, perp)))) * n;
   return perp + par;
 }
 
@@ -95,7 +124,7 @@ __device__ __forceinline__ void surface_at(const DevScene& s, uint32_t ref, f3 p
   v = 0.0f;
   if (ty == RTB_PRIM_SPHERE) {
     const float4 c = __ldg(&s.sphere_f[idx]);
-    const float inv_r = 1.0f / c.w;
+    const float inv_r = shade_rcp(c.w);
     n_out = inv_r * mk3(p.x - c.x, p.y - c.y, p.z - c.z);
     mat = __ldg(&s.sphere_mat[idx]);
   } else if (ty == RTB_PRIM_TRIANGLE) {
@@ -108,8 +137,8 @@ __device__ __forceinline__ void surface_at(const DevScene& s, uint32_t ref, f3 p
     mat = __float_as_uint(q1.z);
     n_out = mk3(axis == 0 ? 1.0f : 0.0f, axis == 1 ? 1.0f : 0.0f, axis == 2 ? 1.0f : 0.0f);
     const float pa = axis == 0 ? p.y : p.x, pb = axis == 2 ? p.y : p.z;
-    u = (pa - q0.y) / (q0.z - q0.y);
-    v = (pb - q0.w) / (q1.x - q0.w);
+    u = (pa - q0.y) * shade_rcp(q0.z - q0.y);
+    v = (pb - q0.w) * shade_rcp(q1.x - q0.w);
   }
 }
 
