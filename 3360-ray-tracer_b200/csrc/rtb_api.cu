@@ -5,6 +5,7 @@
 #include <rtb.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -98,8 +99,21 @@ void FreeFused(RenderCtx* s) {
 // shared memory of the traversal kernels besides the staged top of the tree: the stack columns
 constexpr size_t kStackSmem = (size_t)rtb::kSmemStack * rtb::kTraceBlock * sizeof(uint32_t);
 
+// The device image of a compiled scene, kept in pinned host memory by the RtbCompiledTree it belongs to: the first
+// rtb_scene_create that uses the tree lays every table out exactly as in the device arena; later ones are ONE
+// asynchronous copy (no float shadows to rebuild, nothing to stage).
+struct ArenaImage {
+  char* pinned = nullptr;
+  size_t bytes = 0;
+  bool filled = false;
+  uint32_t counts[6] = {0, 0, 0, 0, 0, 0};  // spheres, triangles, rects, materials, textures, images at snapshot time
+};
 struct RtbCompiledTree {
   rtbc::Compiled tree;
+  ArenaImage image;
+  ~RtbCompiledTree() {
+    if (image.pinned) cudaFreeHost(image.pinned);
+  }
 };
 
 #ifndef RTB_TREE_REBUILD_DEFAULT
@@ -148,6 +162,7 @@ struct RtbScene {
     const void* src;
     size_t bytes, off;
     const void** out;
+    bool fresh;  // differs from one rtb_scene_create to the next (texture object handles): never taken from an ArenaImage
   };
   std::vector<Pending> pending;
   std::vector<cudaArray_t> arrays;
@@ -163,14 +178,44 @@ struct RtbScene {
   }
   // queue `n` elements for upload; *out is set by Commit.  `host` must stay valid until then.
   template <class T>
-  int Put(const T* host, size_t n, const T** out) {
+  int Put(const T* host, size_t n, const T** out, bool fresh = false) {
     *out = nullptr;
     if (n == 0) return RTB_OK;
-    pending.push_back(Pending{host, n * sizeof(T), Reserve(n * sizeof(T)), reinterpret_cast<const void**>(out)});
+    pending.push_back(Pending{host, n * sizeof(T), Reserve(n * sizeof(T)), reinterpret_cast<const void**>(out), fresh});
     return RTB_OK;
   }
-  int Commit(cudaStream_t st) {
+  int FinishCommit(cudaStream_t st, size_t ctr_off) {
+    RTB_CUDA(cudaMemsetAsync(arena + ctr_off, 0, sizeof(rtb::HitCounters) + 16, st));
+    counters = reinterpret_cast<rtb::HitCounters*>(arena + ctr_off);
+    cursor = reinterpret_cast<unsigned int*>(arena + ctr_off + sizeof(rtb::HitCounters));
+    RTB_CUDA(cudaStreamSynchronize(st));  // the staging buffer and the caller's arrays are free again
+    pending.clear();
+    return RTB_OK;
+  }
+  // img != nullptr: upload through (and, the first time, fill) the compiled tree's pinned arena image
+  int Commit(cudaStream_t st, ArenaImage* img = nullptr) {
     const size_t ctr_off = Reserve(sizeof(rtb::HitCounters) + 16);
+    if (img && arena_bytes <= (256u << 20)) {
+      if (!img->filled || img->bytes != arena_bytes) {
+        for (const Pending& p : pending)
+          if (!p.fresh && !p.src) return Fail(RTB_EINVAL, "scene tables changed since rtb_tree_compile");
+        if (img->pinned) cudaFreeHost(img->pinned);
+        img->pinned = nullptr;
+        img->filled = false;
+        RTB_CUDA(cudaMallocHost(reinterpret_cast<void**>(&img->pinned), arena_bytes));
+        img->bytes = arena_bytes;
+        for (const Pending& p : pending)
+          if (!p.fresh) std::memcpy(img->pinned + p.off, p.src, p.bytes);
+        img->filled = true;
+      }
+      RTB_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&arena), arena_bytes, st));
+      RTB_CUDA(cudaMemcpyAsync(arena, img->pinned, ctr_off, cudaMemcpyHostToDevice, st));
+      for (const Pending& p : pending) {
+        if (p.fresh) RTB_CUDA(cudaMemcpyAsync(arena + p.off, p.src, p.bytes, cudaMemcpyHostToDevice, st));  // a few bytes, pageable
+        *p.out = arena + p.off;
+      }
+      return FinishCommit(st, ctr_off);
+    }
     // tables above 32 MB (the stress scene) go straight from the caller's memory; pinning gigabytes costs more than it saves
     constexpr size_t kDirect = 32u << 20;
     size_t staged = 0;
@@ -195,12 +240,7 @@ struct RtbScene {
       }
       *p.out = arena + p.off;
     }
-    RTB_CUDA(cudaMemsetAsync(arena + ctr_off, 0, sizeof(rtb::HitCounters) + 16, st));
-    counters = reinterpret_cast<rtb::HitCounters*>(arena + ctr_off);
-    cursor = reinterpret_cast<unsigned int*>(arena + ctr_off + sizeof(rtb::HitCounters));
-    RTB_CUDA(cudaStreamSynchronize(st));  // the staging buffer and the caller's arrays are free again
-    pending.clear();
-    return RTB_OK;
+    return FinishCommit(st, ctr_off);
   }
 };
 
@@ -359,10 +399,23 @@ int rtb_scene_destroy(RtbScene* s) {
 int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
   if (!d || !out) return Fail(RTB_EINVAL, "null argument");
   *out = nullptr;
-  int rc = ValidateDesc(d);
+  const bool trace_create = std::getenv("RTB_TRACE_CREATE") != nullptr;
+  const auto tc0 = std::chrono::steady_clock::now();
+  auto lap = [&](const char* what) {
+    if (trace_create) std::fprintf(stderr, "[rtb create] %-10s %.3f ms\n", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tc0).count());
+  };
+  // a compiled tree that has been uploaded before carries the scene's device image (pinned): its tables were
+  // validated by rtb_tree_compile and must not have changed since, so neither the checks nor the shadows are redone
+  ArenaImage* img = (d->compiled && !(d->flags & RTB_SCENE_DEVICE_BUILD)) ? &const_cast<RtbCompiledTree*>(d->compiled)->image : nullptr;
+  if (std::getenv("RTB_NO_ARENA_IMAGE")) img = nullptr;
+  const uint32_t counts_now[6] = {d->n_spheres, d->n_triangles, d->n_rects, d->n_materials, d->n_textures, d->n_images};
+  const bool cached = img && img->filled && std::memcmp(img->counts, counts_now, sizeof(counts_now)) == 0;
+  if (img && !cached) img->filled = false;
+  int rc = cached ? (d->abi_version == RTB_ABI_VERSION ? RTB_OK : Fail(RTB_EINVAL, "RtbSceneDesc.abi_version mismatch")) : ValidateDesc(d);
   if (rc != RTB_OK) return rc;
   rc = EnsureInit();
   if (rc != RTB_OK) return rc;
+  lap("validate");
 
   RtbScene* s = new RtbScene();
   s->device = g_device;
@@ -406,12 +459,12 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
   PUT(s->Put(reinterpret_cast<const double2*>(d->triangles), 5 * (size_t)d->n_triangles, &v.triangles));
   PUT(s->Put(reinterpret_cast<const double2*>(d->rects), 3 * (size_t)d->n_rects, &v.rects));
   {  // float shadows of the double tables (shading frame + pre-filter)
-    sf.resize(d->n_spheres);
-    for (uint32_t i = 0; i < d->n_spheres; ++i)
+    sf.resize(cached ? 0 : d->n_spheres);
+    for (uint32_t i = 0; i < (cached ? 0u : d->n_spheres); ++i)
       sf[i] = make_float4((float)d->spheres[i].c[0], (float)d->spheres[i].c[1], (float)d->spheres[i].c[2], (float)d->spheres[i].r);
-    PUT(s->Put(sf.data(), sf.size(), &v.sphere_f));
-    tf.resize(3 * (size_t)d->n_triangles);
-    for (uint32_t i = 0; i < d->n_triangles; ++i) {
+    PUT(s->Put(cached ? nullptr : sf.data(), (size_t)d->n_spheres, &v.sphere_f));
+    tf.resize(cached ? 0 : 3 * (size_t)d->n_triangles);
+    for (uint32_t i = 0; i < (cached ? 0u : d->n_triangles); ++i) {
       const RtbTriangle& t = d->triangles[i];
       float4 a = make_float4((float)t.a[0], (float)t.a[1], (float)t.a[2], 0.f);
       std::memcpy(&a.w, &t.mat, 4);
@@ -421,9 +474,9 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
       tf[3 * (size_t)i + 1] = make_float4((float)t.e1[0], (float)t.e1[1], (float)t.e1[2], mx(t.e1));
       tf[3 * (size_t)i + 2] = make_float4((float)t.e2[0], (float)t.e2[1], (float)t.e2[2], mx(t.e2));
     }
-    PUT(s->Put(tf.data(), tf.size(), &v.triangle_f));
-    rf.resize(2 * (size_t)d->n_rects);
-    for (uint32_t i = 0; i < d->n_rects; ++i) {
+    PUT(s->Put(cached ? nullptr : tf.data(), 3 * (size_t)d->n_triangles, &v.triangle_f));
+    rf.resize(cached ? 0 : 2 * (size_t)d->n_rects);
+    for (uint32_t i = 0; i < (cached ? 0u : d->n_rects); ++i) {
       const RtbRect& r = d->rects[i];
       rf[2 * (size_t)i] = make_float4((float)r.k, (float)r.a0, (float)r.a1, (float)r.b0);
       float4 q = make_float4((float)r.b1, 0.f, 0.f, 0.f);
@@ -431,7 +484,7 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
       std::memcpy(&q.z, &r.mat, 4);
       rf[2 * (size_t)i + 1] = q;
     }
-    PUT(s->Put(rf.data(), rf.size(), &v.rect_f));
+    PUT(s->Put(cached ? nullptr : rf.data(), 2 * (size_t)d->n_rects, &v.rect_f));
   }
   PUT(s->Put(d->sphere_mat, d->n_spheres, &v.sphere_mat));
   PUT(s->Put(d->sphere_gid, d->n_spheres, &v.sphere_gid));
@@ -477,15 +530,18 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
       objs[i] = tex;
       dims[i] = make_int2(im.width, im.height);
     }
-    PUT(s->Put(objs.data(), objs.size(), &v.image_tex));
-    PUT(s->Put(dims.data(), dims.size(), &v.image_dim));
+    PUT(s->Put(objs.data(), objs.size(), &v.image_tex, /*fresh=*/true));  // texture object handles belong to THIS scene
+    PUT(s->Put(dims.data(), dims.size(), &v.image_dim, /*fresh=*/true));
   }
   s->smem_bytes = (size_t)v.n_top_pairs * 64;  // + the stack columns, added at launch (TraceSmem)
   if (s->smem_bytes + kStackSmem > 200 * 1024) {
     rtb_scene_destroy(s);
     return Fail(RTB_EINVAL, "n_top_nodes does not fit shared memory");
   }
-  PUT(s->Commit(g_stream));
+  lap("tables");
+  PUT(s->Commit(g_stream, img));
+  if (img && img->filled) std::memcpy(img->counts, counts_now, sizeof(counts_now));
+  lap("commit");
   if (device_build && n_prims > 0) {
     v.pairs = reinterpret_cast<const float4*>(s->arena + built_pairs_off);
     PUT(BuildTreeOnDevice(s, d->n_spheres, d->n_triangles, n_prims, reinterpret_cast<float*>(s->arena + built_pairs_off)));

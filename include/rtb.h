@@ -252,7 +252,12 @@ int rtb_device_count(void);
 int rtb_init(int device);
 int rtb_shutdown(void);
 
-/* Host only (works without a GPU): interchange nodes -> the sibling-pair tree the kernels walk. */
+/* Host only (works without a GPU): interchange nodes -> the sibling-pair tree the kernels walk.
+ * The result also caches, from the first rtb_scene_create that uses it, the scene's complete device image in pinned
+ * host memory, so that creating the scene again (another frame, another GPU of the same process) is one asynchronous
+ * copy: the tables of `desc` must not change between rtb_tree_compile and the rtb_scene_create calls that pass its
+ * result in RtbSceneDesc.compiled (change the scene -> compile again).  Use one compiled tree from one host thread
+ * at a time. */
 int rtb_tree_compile(const RtbSceneDesc* desc, RtbCompiledTree** out);
 void rtb_tree_destroy(RtbCompiledTree* tree);
 

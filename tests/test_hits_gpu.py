@@ -155,3 +155,29 @@ def test_full_size_batch_properties(rt, scenes):
     clipped["tmax"][tri] = h1["t"][tri].astype(np.float32)  # Triangle::Hit accepts t == tmax (triangle.h:74); its t is a float
     h3 = ds.intersect(clipped)
     assert np.array_equal(h3["prim_id"][tri], h1["prim_id"][tri])
+
+
+def test_scene_recreated_from_the_cached_device_image(rt, golden_dir, monkeypatch):
+    """rtb_scene_create caches the scene's device image in the compiled tree (pinned): the second creation is one copy.
+    Both creations, and a creation with the cache switched off, answer the golden rays identically; an image-textured
+    scene keeps its per-scene texture handles out of the cache."""
+    for name, build in (("bunny", ("bunny", (50,))), ("earth_bubbles", ("earth_bubbles", ()))):
+        hs = rt.HostScene.build(*build)
+        g = np.load(golden_dir / f"hits_{name}.npz")
+        rays = np.ascontiguousarray(g["rays"]).view(rt.RAY_DTYPE).reshape(-1)
+        first = rt.DeviceScene(hs)
+        a = first.intersect(rays)
+        second = rt.DeviceScene(hs)  # from the cached image, while the first scene is still alive
+        b = second.intersect(rays)
+        first.close()
+        c = second.intersect(rays)
+        monkeypatch.setenv("RTB_NO_ARENA_IMAGE", "1")
+        plain = rt.DeviceScene(hs)
+        d = plain.intersect(rays)
+        monkeypatch.delenv("RTB_NO_ARENA_IMAGE")
+        for h in (a, b, c, d):
+            assert helpers.check_hits(h, g["t"], g["gid"])
+        cam = rt.camera_init(rt.camera_config(image_width=64, vfov=30.0, lookfrom=(0, 1, 3), lookat=(0, 0, 0)))
+        i1, s1 = second.render(cam, spp=8, max_depth=6)
+        i2, s2 = plain.render(cam, spp=8, max_depth=6)
+        assert s1["rays"] == s2["rays"] and np.abs(i1 - i2).max() <= 2e-5 * max(i1.max(), 1e-6)
