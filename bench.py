@@ -115,17 +115,19 @@ def cpu_reference_leg(rt, cfg_name, budget_s, steps=1, warmup=0):
     ora = checker.make_oracle(hs, fast=fast)
     cam_cfg = camera_for(rt, cfg)
     cam = rt.camera_init(cam_cfg)
-    cores = os.cpu_count() or 1
+    # every host thread this process may use: torchrun exports OMP_NUM_THREADS=1 to its workers, which would silently
+    # turn the "all-core" reference into a single-thread run, so the count is passed to omp_set_num_threads explicitly
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     # calibrate with whole-image passes at 1 and 2 spp (the first also warms the thread pool), then size
     # the sample to the budget: samples/s is spp-invariant
-    ora.render_a(cam_cfg.as_oracle_cfg(), 1, cfg["depth"], seed=1, want_m2=False)
-    _, _, secs, _ = ora.render_a(cam_cfg.as_oracle_cfg(), 2, cfg["depth"], seed=1, want_m2=False)
+    ora.render_a(cam_cfg.as_oracle_cfg(), 1, cfg["depth"], seed=1, want_m2=False, threads=cores)
+    _, _, secs, _ = ora.render_a(cam_cfg.as_oracle_cfg(), 2, cfg["depth"], seed=1, want_m2=False, threads=cores)
     rate = 2 * cam.width * cam.height / max(secs, 1e-6)
     spp = int(max(1, min(cfg["spp"], budget_s * rate / (cam.width * cam.height))))
     out = []
     for k in range(warmup + steps):
         this_spp = spp if k >= warmup else 1
-        _, _, secs, rays = ora.render_a(cam_cfg.as_oracle_cfg(), this_spp, cfg["depth"], seed=2 + k, want_m2=False)
+        _, _, secs, rays = ora.render_a(cam_cfg.as_oracle_cfg(), this_spp, cfg["depth"], seed=2 + k, want_m2=False, threads=cores)
         if k >= warmup:
             out.append((cam.width * cam.height * this_spp, rays, secs))
     samples = sum(o[0] for o in out); rays = sum(o[1] for o in out); secs = sum(o[2] for o in out)
