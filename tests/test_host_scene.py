@@ -1,5 +1,6 @@
 """Host-side logic (CPU): the SAH builder reproduces the reference's trees, the flattener's
 layout invariants hold, camera derivation matches the reference, loaders behave."""
+import ctypes as C
 import hashlib
 
 import numpy as np
@@ -174,3 +175,40 @@ def test_image_table_matches_reference_pipeline(rt):
 def test_obj_loader_counts(rt):
     hs = SCENES["bunny"](rt)
     assert hs.desc.n_triangles == 69451 and hs.desc.n_spheres == 1
+
+
+@pytest.mark.parametrize("name,build", [("cornell", ("cornell", ())), ("rtiow", ("rtiow", (11, 1))), ("bunny", ("bunny", (50,))),
+                                        ("earth_bubbles", ("earth_bubbles", ()))])
+def test_soup_description_for_the_device_built_tree(rt, name, build):
+    """RTH_BUILD_DEVICE_TREE: geom::Bvh constructors are deferred, Flattener::RunSoup emits the primitive tables in
+    CREATION order with no nodes / refs / ranks; the primitives are the ones of the normally built scene."""
+    soup = rt.HostScene.build(*build, device_tree=True)
+    full = rt.HostScene.build(*build)
+    ds, df = soup.desc, full.desc
+    assert ds.flags & 1 and not df.flags
+    assert not ds.nodes and not ds.prim_refs and not ds.compiled and not ds.sphere_rank and not ds.triangle_rank and not ds.rect_rank
+    assert (ds.n_spheres, ds.n_triangles, ds.n_rects, ds.n_materials, ds.n_textures, ds.n_images) == \
+           (df.n_spheres, df.n_triangles, df.n_rects, df.n_materials, df.n_textures, df.n_images)
+    # creation order: gid -> (type, k-th primitive of that type)
+    ref = soup.gid_to_ref()
+    for ty in range(3):
+        idx = ref[(ref >> 30) == ty] & 0x3FFFFFFF
+        assert np.array_equal(idx, np.arange(idx.size))
+
+    def table(d, ptr, n, words):
+        return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_double)), shape=(n * words,)).reshape(n, words).copy() if n else np.zeros((0, words))
+
+    # the same primitives, the full scene's tables permuted into its leaf order: compare through the gid maps
+    for (n, ptr_s, ptr_f, gid_s, gid_f, words) in ((ds.n_spheres, ds.spheres, df.spheres, ds.sphere_gid, df.sphere_gid, 4),
+                                                   (ds.n_triangles, ds.triangles, df.triangles, ds.triangle_gid, df.triangle_gid, 10),
+                                                   (ds.n_rects, ds.rects, df.rects, ds.rect_gid, df.rect_gid, 6)):
+        if not n:
+            continue
+        a, b = table(ds, ptr_s, n, words), table(df, ptr_f, n, words)
+        ga = np.ctypeslib.as_array(C.cast(gid_s, C.POINTER(C.c_uint32)), shape=(n,))
+        gb = np.ctypeslib.as_array(C.cast(gid_f, C.POINTER(C.c_uint32)), shape=(n,))
+        assert np.array_equal(a[np.argsort(ga)].view(np.uint64), b[np.argsort(gb)].view(np.uint64))
+    assert soup.bvh_count() == full.bvh_count()  # the deferred Bvh objects exist, unbuilt
+    for k in range(soup.bvh_count()):
+        nodes, idx = soup.bvh_dump(k)
+        assert nodes.shape[0] == 0
