@@ -106,7 +106,7 @@ assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 16
 RTB_SYMBOLS = [
     "rtb_last_error", "rtb_abi_version", "rtb_tree_compile", "rtb_tree_destroy", "rtb_device_count", "rtb_init", "rtb_shutdown", "rtb_scene_create",
     "rtb_scene_destroy", "rtb_intersect_batch", "rtb_intersect_batch_device", "rtb_render", "rtb_render_device",
-    "rtb_render_adaptive", "rtb_render_adaptive_device", "rtb_resolve_counts", "rtb_resolve_counts_device", "rtb_pixel_state_fold",
+    "rtb_render_adaptive", "rtb_render_adaptive_device", "rtb_resolve_counts", "rtb_resolve_counts_device", "rtb_pixel_state_fold", "rtb_render_multi",
     "rtb_resolve_device", "rtb_resolve", "rtb_measure_l2_gbs", "rtb_measure_fp32_tflops", "rtb_measure_fp64_tflops",
 ]
 RTH_SYMBOLS = [
@@ -162,6 +162,8 @@ def load(counters: bool = False) -> C.CDLL:
     lib.rtb_render_adaptive.argtypes = [C.c_void_p, C.POINTER(RtbCamera), C.POINTER(RtbRenderParams), C.POINTER(RtbAdaptive), C.c_void_p,
                                         C.c_void_p, C.c_void_p, C.POINTER(RtbStats)]
     lib.rtb_render_adaptive_device.argtypes = lib.rtb_render_adaptive.argtypes
+    lib.rtb_render_multi.argtypes = [C.POINTER(RtbSceneDesc), C.c_int, C.c_void_p, C.POINTER(RtbCamera), C.POINTER(RtbRenderParams), C.c_void_p,
+                                     C.POINTER(RtbStats)]
     lib.rtb_pixel_state_fold.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.POINTER(RtbAdaptive), C.c_void_p, C.c_void_p, C.c_void_p]
     lib.rtb_resolve_counts.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     lib.rtb_resolve_counts_device.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
@@ -374,6 +376,20 @@ class DeviceScene:
         st = RtbStats()
         _check(self._lib, self._lib.rtb_render_device(self._h, C.byref(cam), C.byref(prm), d_accum_ptr, C.byref(st)))
         return st.as_dict()
+
+
+def render_multi(host_scene: "HostScene", cam: RtbCamera, spp: int, max_depth: int, n_devices: int, devices=None, mode: int = MODE_A,
+                 seed: int = 0x3360, spp_begin: int = 0, flags: int = 0):
+    """seam 1 on several GPUs from one host thread (rtb_render_multi): (rgb_sum[h,w,3], stats)."""
+    lib = host_scene._lib
+    prm = RtbRenderParams(spp_begin, spp_begin + spp, max_depth, mode, seed, 0, flags)
+    out = np.zeros((cam.height, cam.width, 3), np.float32)
+    st = RtbStats()
+    dev = np.asarray(devices, np.int32) if devices is not None else None
+    desc = host_scene.desc
+    _check(lib, lib.rtb_render_multi(C.byref(desc), n_devices, _ptr(dev) if dev is not None else None, C.byref(cam), C.byref(prm), _ptr(out),
+                                     C.byref(st)))
+    return out, st.as_dict()
 
 
 def pixel_state_fold(samples: np.ndarray, rel_threshold: float = 0.05, min_samples: int = 16, criterion: int = ADAPT_PIXEL_STATE,

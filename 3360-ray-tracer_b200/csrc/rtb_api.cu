@@ -9,7 +9,12 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <condition_variable>
+#include <functional>
+#include <map>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "rtb_compile.h"
@@ -103,6 +108,7 @@ constexpr size_t kStackSmem = (size_t)rtb::kSmemStack * rtb::kTraceBlock * sizeo
 // rtb_scene_create that uses the tree lays every table out exactly as in the device arena; later ones are ONE
 // asynchronous copy (no float shadows to rebuild, nothing to stage).
 struct ArenaImage {
+  std::mutex mu;  // rtb_render_multi creates the scene on every device at once: one of them fills the image
   char* pinned = nullptr;
   size_t bytes = 0;
   bool filled = false;
@@ -193,10 +199,11 @@ struct RtbScene {
     return RTB_OK;
   }
   // img != nullptr: upload through (and, the first time, fill) the compiled tree's pinned arena image
-  int Commit(cudaStream_t st, ArenaImage* img = nullptr) {
+  int Commit(cudaStream_t st, ArenaImage* img = nullptr, const uint32_t* counts = nullptr) {
     const size_t ctr_off = Reserve(sizeof(rtb::HitCounters) + 16);
     if (img && arena_bytes <= (256u << 20)) {
-      if (!img->filled || img->bytes != arena_bytes) {
+      std::unique_lock<std::mutex> fill_lock(img->mu);
+      if (!img->filled || img->bytes != arena_bytes || (counts && std::memcmp(img->counts, counts, sizeof(img->counts)) != 0)) {
         for (const Pending& p : pending)
           if (!p.fresh && !p.src) return Fail(RTB_EINVAL, "scene tables changed since rtb_tree_compile");
         if (img->pinned) cudaFreeHost(img->pinned);
@@ -206,8 +213,10 @@ struct RtbScene {
         img->bytes = arena_bytes;
         for (const Pending& p : pending)
           if (!p.fresh) std::memcpy(img->pinned + p.off, p.src, p.bytes);
+        if (counts) std::memcpy(img->counts, counts, sizeof(img->counts));
         img->filled = true;
       }
+      fill_lock.unlock();
       RTB_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&arena), arena_bytes, st));
       RTB_CUDA(cudaMemcpyAsync(arena, img->pinned, ctr_off, cudaMemcpyHostToDevice, st));
       for (const Pending& p : pending) {
@@ -410,7 +419,6 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
   if (std::getenv("RTB_NO_ARENA_IMAGE")) img = nullptr;
   const uint32_t counts_now[6] = {d->n_spheres, d->n_triangles, d->n_rects, d->n_materials, d->n_textures, d->n_images};
   const bool cached = img && img->filled && std::memcmp(img->counts, counts_now, sizeof(counts_now)) == 0;
-  if (img && !cached) img->filled = false;
   int rc = cached ? (d->abi_version == RTB_ABI_VERSION ? RTB_OK : Fail(RTB_EINVAL, "RtbSceneDesc.abi_version mismatch")) : ValidateDesc(d);
   if (rc != RTB_OK) return rc;
   rc = EnsureInit();
@@ -539,8 +547,7 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
     return Fail(RTB_EINVAL, "n_top_nodes does not fit shared memory");
   }
   lap("tables");
-  PUT(s->Commit(g_stream, img));
-  if (img && img->filled) std::memcpy(img->counts, counts_now, sizeof(counts_now));
+  PUT(s->Commit(g_stream, img, counts_now));
   lap("commit");
   if (device_build && n_prims > 0) {
     v.pairs = reinterpret_cast<const float4*>(s->arena + built_pairs_off);
@@ -1069,6 +1076,194 @@ int rtb_render(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* prm, fl
   rc = rtb_render_device(s, cam, prm, d, stats);
   if (rc != RTB_OK) return rc;
   RTB_CUDA(cudaMemcpy(rgb_sum, d, bytes, cudaMemcpyDeviceToHost));
+  return RTB_OK;
+}
+
+// ---- seam 1 on several devices of one box -----------------------------------------------------------------------
+namespace {
+struct MultiWorker {
+  int device = 0;
+  int rc = RTB_OK;
+  std::string error;
+  float* accum = nullptr;  // the worker thread's grow-only accumulator on `device` (its RenderCtx), valid until its next job
+  RtbStats stats{};
+};
+
+// One device's share: scene, accumulator, render of [b, e).  Runs on the host thread that owns the device's state
+// (the library's state is per thread = per device).
+void MultiRenderOne(MultiWorker* w, const RtbSceneDesc* desc, const RtbCamera* cam, RtbRenderParams prm) {
+  auto fail = [&](int rc) {
+    w->rc = rc;
+    w->error = rtb_last_error();
+  };
+  int rc = rtb_init(w->device);
+  if (rc != RTB_OK) return fail(rc);
+  RtbScene* scene = nullptr;
+  rc = rtb_scene_create(desc, &scene);
+  if (rc != RTB_OK) return fail(rc);
+  const size_t bytes = (size_t)cam->width * cam->height * 3 * sizeof(float);
+  if (g_ctx.accum_bytes < bytes) {
+    if (g_ctx.accum) cudaFree(g_ctx.accum);
+    g_ctx.accum = nullptr;
+    g_ctx.accum_bytes = 0;
+    if (cudaMalloc(reinterpret_cast<void**>(&g_ctx.accum), bytes) != cudaSuccess) {
+      rtb_scene_destroy(scene);
+      w->rc = Fail(RTB_ENOMEM, "rtb_render_multi: accumulator allocation failed");
+      w->error = rtb_last_error();
+      return;
+    }
+    g_ctx.accum_bytes = bytes;
+  }
+  w->accum = g_ctx.accum;
+  prm.flags &= ~RTB_RENDER_KEEP_ACCUM;
+  rc = rtb_render_device(scene, cam, &prm, w->accum, &w->stats);
+  if (rc != RTB_OK) fail(rc);
+  rtb_scene_destroy(scene);
+}
+
+// Worker threads live as long as the process: one per device ever used as a peer, each keeping its stream, pools,
+// pixel order and accumulator between calls (creating them costs ~3 ms per device per call otherwise).
+struct DeviceThread {
+  std::mutex m;
+  std::condition_variable cv;
+  std::function<void()> job;
+  bool has_job = false, done = false;
+  void Loop() {
+    for (;;) {
+      std::unique_lock<std::mutex> lk(m);
+      cv.wait(lk, [&] { return has_job; });
+      std::function<void()> f = std::move(job);
+      has_job = false;
+      lk.unlock();
+      f();
+      lk.lock();
+      done = true;
+      cv.notify_all();
+    }
+  }
+  void Submit(std::function<void()> f) {
+    std::lock_guard<std::mutex> lk(m);
+    job = std::move(f);
+    done = false;
+    has_job = true;
+    cv.notify_all();
+  }
+  void Wait() {
+    std::unique_lock<std::mutex> lk(m);
+    cv.wait(lk, [&] { return done; });
+  }
+};
+std::mutex g_pool_mu;
+std::map<int, DeviceThread*> g_pool;
+DeviceThread* WorkerFor(int device) {
+  std::lock_guard<std::mutex> lk(g_pool_mu);
+  auto it = g_pool.find(device);
+  if (it != g_pool.end()) return it->second;
+  DeviceThread* t = new DeviceThread();
+  std::thread([t] { t->Loop(); }).detach();
+  g_pool[device] = t;
+  return t;
+}
+}  // namespace
+
+int rtb_render_multi(const RtbSceneDesc* desc, int n_devices, const int* devices, const RtbCamera* cam, const RtbRenderParams* prm, float* rgb_sum,
+                     RtbStats* stats) {
+  if (!desc || !cam || !prm || !rgb_sum || n_devices < 1 || n_devices > 9) return Fail(RTB_EINVAL, "bad argument");
+  if (prm->spp_end < prm->spp_begin || cam->width <= 0 || cam->height <= 0) return Fail(RTB_EINVAL, "bad camera / params");
+  const int visible = rtb_device_count();
+  if (visible <= 0) return Fail(RTB_ENODEVICE, "no CUDA device visible; this library has no CPU path");
+  std::vector<MultiWorker> work((size_t)n_devices);
+  for (int k = 0; k < n_devices; ++k) {
+    work[k].device = devices ? devices[k] : k;
+    if (work[k].device < 0 || work[k].device >= visible) return Fail(RTB_EINVAL, "device index out of range");
+    for (int j = 0; j < k; ++j)
+      if (work[j].device == work[k].device) return Fail(RTB_EINVAL, "device listed twice");
+  }
+  // slices of the global sample indices, sizes differ by at most one (multigpu.spp_slice)
+  const int total = prm->spp_end - prm->spp_begin, base = total / n_devices, extra = total % n_devices;
+  std::vector<RtbRenderParams> prms((size_t)n_devices, *prm);
+  for (int k = 0, b = prm->spp_begin; k < n_devices; ++k) {
+    const int len = base + (k < extra ? 1 : 0);
+    prms[k].spp_begin = b;
+    prms[k].spp_end = b + len;
+    b += len;
+  }
+  const auto t0 = std::chrono::steady_clock::now();
+  std::vector<DeviceThread*> peers;
+  for (int k = 1; k < n_devices; ++k) {
+    peers.push_back(WorkerFor(work[k].device));
+    MultiWorker* w = &work[k];
+    const RtbRenderParams pk = prms[k];
+    peers.back()->Submit([w, desc, cam, pk] { MultiRenderOne(w, desc, cam, pk); });
+  }
+  MultiRenderOne(&work[0], desc, cam, prms[0]);  // the caller's own thread renders the first device's share
+  for (DeviceThread* t : peers) t->Wait();
+  auto cleanup = [&]() { cudaSetDevice(work[0].device); };
+  for (auto& w : work)
+    if (w.rc != RTB_OK) {
+      const int rc = w.rc;
+      const std::string msg = "device " + std::to_string(w.device) + ": " + w.error;
+      cleanup();
+      return Fail(rc, msg);
+    }
+  // ---- reduce on devices[0]: peers read over NVLink where peer access is granted, staged copies otherwise
+  const size_t n = (size_t)cam->width * cam->height * 3, bytes = n * sizeof(float);
+  cudaSetDevice(work[0].device);
+  cudaStream_t st = g_stream;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  cudaEventRecord(e0, st);
+  rtb::PeerPtrs direct{};
+  int n_direct = 0;
+  float* staged = nullptr;
+  cudaError_t e = cudaSuccess;
+  for (int k = 1; k < n_devices && e == cudaSuccess; ++k) {
+    int can = 0;
+    cudaDeviceCanAccessPeer(&can, work[0].device, work[k].device);
+    if (can) {
+      const cudaError_t pe = cudaDeviceEnablePeerAccess(work[k].device, 0);
+      if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) can = 0;
+      cudaGetLastError();
+    }
+    if (can) {
+      direct.p[n_direct++] = work[k].accum;
+    } else {  // no peer access: copy through, then add
+      if (!staged) e = cudaMalloc(reinterpret_cast<void**>(&staged), bytes);
+      if (e == cudaSuccess) e = cudaMemcpyPeerAsync(staged, work[0].device, work[k].accum, work[k].device, bytes, st);
+      if (e == cudaSuccess) {
+        rtb::PeerPtrs one{};
+        one.p[0] = staged;
+        rtb::peer_sum_kernel<<<g_sm_count * 4, 256, 0, st>>>(work[0].accum, one, 1, n);
+      }
+    }
+  }
+  if (e == cudaSuccess && n_direct > 0) rtb::peer_sum_kernel<<<g_sm_count * 4, 256, 0, st>>>(work[0].accum, direct, n_direct, n);
+  cudaEventRecord(e1, st);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(rgb_sum, work[0].accum, bytes, cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e == cudaSuccess) e = cudaGetLastError();
+  float ms_reduce = 0.f;
+  cudaEventElapsedTime(&ms_reduce, e0, e1);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (staged) cudaFree(staged);
+  cleanup();
+  if (e != cudaSuccess) return Fail(RTB_ECUDA, std::string("rtb_render_multi reduce: ") + cudaGetErrorString(e));
+  if (stats) {
+    std::memset(stats, 0, sizeof(*stats));
+    for (const auto& w : work) {
+      stats->samples += w.stats.samples;
+      stats->rays += w.stats.rays;
+      stats->launches += w.stats.launches;
+      stats->iterations = std::max(stats->iterations, w.stats.iterations);
+      stats->ms_total = std::max(stats->ms_total, w.stats.ms_total);
+    }
+    stats->ms_total += ms_reduce;
+    stats->launches += (uint32_t)std::max(1, n_devices - 1);
+    stats->ms_shade = ms_reduce;  // reported separately: the reduce (no shade kernel runs in the default pipeline)
+    (void)t0;
+  }
   return RTB_OK;
 }
 

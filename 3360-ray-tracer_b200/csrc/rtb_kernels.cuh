@@ -820,6 +820,30 @@ __global__ void resolve_kernel(const float* __restrict__ rgb_sum, size_t n_value
   rgb8[i] = (uint8_t)(int)(256 * g);
 }
 
+// Multi-GPU reduce without a library: the root device adds its peers' accumulators, read directly over NVLink
+// (peer access) 128 bits at a time.  n4 = number of float4 (the tail, < 4 floats, is handled by the last threads).
+struct PeerPtrs {
+  const float* p[8];
+};
+__global__ void __launch_bounds__(256) peer_sum_kernel(float* __restrict__ root, PeerPtrs peers, int n_peers, size_t n) {
+  const size_t n4 = n / 4;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += stride) {
+    float4 a = reinterpret_cast<float4*>(root)[i];
+    for (int k = 0; k < n_peers; ++k) {
+      const float4 b = reinterpret_cast<const float4*>(peers.p[k])[i];
+      a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    }
+    reinterpret_cast<float4*>(root)[i] = a;
+  }
+  const size_t t = 4 * n4 + blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (t < n) {
+    float a = root[t];
+    for (int k = 0; k < n_peers; ++k) a += peers.p[k][t];
+    root[t] = a;
+  }
+}
+
 __global__ void iota_kernel(uint32_t* v, uint32_t n) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) v[i] = i;

@@ -5,7 +5,8 @@
 //   rt_b200 [preset] [--scene cornell|rtiow|rtiow110|checkered|earth|earth_bubbles|bunny|stress]
 //           [--cameras file.json] [--mode A|B] [--spp N] [--depth N] [--seed N] [--assets dir]
 //           [--adaptive [threshold [min_samples]]]   per-pixel stop of the reference's WavefrontRenderer
-//           [--width N] [--p6]  binary PPM   [--dump file] [--resume file]  progressive accumulator
+//           [--gpus N] [--width N] [--p6]  binary PPM   [--dump file] [--resume file]  progressive accumulator
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 #include <iomanip>
@@ -36,6 +37,7 @@ int main(int argc, char** argv) {
     else if (a == "--spp") opt.samples_per_pixel = std::atoi(next().c_str());
     else if (a == "--depth") opt.max_depth = std::atoi(next().c_str());
     else if (a == "--seed") opt.seed = std::strtoull(next().c_str(), nullptr, 0);
+    else if (a == "--gpus") opt.gpus = std::max(1, std::atoi(next().c_str()));
     else if (a == "--width") width = std::atoi(next().c_str());
     else if (a == "--p6") opt.binary_ppm = true;
     else if (a == "--dump") opt.dump_to = next();

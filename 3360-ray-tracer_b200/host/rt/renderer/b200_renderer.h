@@ -29,6 +29,7 @@ struct B200Options {
   int max_depth = -1;         // <0: camera.max_depth_
   uint64_t seed = 0x3360;
   int device = 0;
+  int gpus = 1;               // > 1: rtb_render_multi over devices 0 .. gpus-1 (spp split, peer reduce); fixed-spp renders
   uint32_t pool_size = 0;
   // adaptive per-pixel stop (rtb_render_adaptive): samples_per_pixel is then the per-pixel maximum
   bool adaptive = false;
@@ -57,7 +58,13 @@ class B200Renderer {
     core::Timer clock;
     if (rtb_init(opt_.device) != RTB_OK) throw std::runtime_error(std::string("B200Renderer: ") + rtb_last_error());
     b200::FlatScene flat = b200::Flattener().Run(world_);
-    const RtbSceneDesc desc = flat.desc();
+    RtbSceneDesc desc = flat.desc();
+    struct TreeGuard {  // the device-native tree: host work, once per scene, shared by every device that renders it
+      RtbCompiledTree* t = nullptr;
+      ~TreeGuard() { rtb_tree_destroy(t); }
+    } tree;
+    if (rtb_tree_compile(&desc, &tree.t) != RTB_OK) throw std::runtime_error(std::string("B200Renderer: ") + rtb_last_error());
+    desc.compiled = tree.t;
     RtbScene* scene = nullptr;
     if (rtb_scene_create(&desc, &scene) != RTB_OK) throw std::runtime_error(std::string("B200Renderer: ") + rtb_last_error());
     const double t_upload = clock.elapsed();
@@ -91,6 +98,10 @@ class B200Renderer {
       count_.assign(static_cast<size_t>(w) * h, 0u);
       const int rc = rtb_render_adaptive(scene, &dc, &prm, &ad, sum_.data(), sumsq_.data(), count_.data(), &stats_);
       rc2 = rc == RTB_OK ? rtb_resolve_counts(sum_.data(), count_.data(), count_.size(), rgb8.data()) : rc;
+    } else if (opt_.gpus > 1) {
+      if (prm.flags & RTB_RENDER_KEEP_ACCUM) throw std::runtime_error("B200Renderer: resume runs on one GPU");
+      const int rc = rtb_render_multi(&desc, opt_.gpus, nullptr, &dc, &prm, sum_.data(), &stats_);
+      rc2 = rc == RTB_OK ? rtb_resolve(sum_.data(), static_cast<size_t>(w) * h, spp_total, rgb8.data()) : rc;
     } else {
       const int rc = rtb_render(scene, &dc, &prm, sum_.data(), &stats_);
       rc2 = rc == RTB_OK ? rtb_resolve(sum_.data(), static_cast<size_t>(w) * h, spp_total, rgb8.data()) : rc;

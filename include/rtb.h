@@ -279,6 +279,17 @@ int rtb_render(RtbScene* scene, const RtbCamera* cam, const RtbRenderParams* par
 int rtb_render_device(RtbScene* scene, const RtbCamera* cam, const RtbRenderParams* params,
                       float* d_rgb_sum, RtbStats* stats);
 
+/* seam 1 on several GPUs of one box, from ONE host thread (what the reference's single-threaded main()
+ * would call).  The library runs one worker thread per device: each creates the scene on its device (scene
+ * replicated), renders its slice of the GLOBAL sample indices [spp_begin, spp_end) (slices differ by at most one
+ * sample per pixel) and leaves a float32 accumulator in its HBM; devices[0] then sums the peers' accumulators with
+ * one kernel that reads them over NVLink peer access (staged through cudaMemcpyPeer where peer access is refused)
+ * and the sum is copied to rgb_sum (W*H*3 floats, host).  The image equals the single-GPU render of the same
+ * range up to float summation order.  stats: samples / rays / launches summed over the devices, ms_total = the
+ * slowest device's render + the reduce.  devices == NULL: 0 .. n_devices-1. */
+int rtb_render_multi(const RtbSceneDesc* desc, int n_devices, const int* devices, const RtbCamera* cam,
+                     const RtbRenderParams* params, float* rgb_sum, RtbStats* stats);
+
 /* seam 1, adaptive: as rtb_render, plus the per-pixel state of integrator::PixelState (pixel_state.h:13-19) in
  * planes: rgb_sum (W*H*3, PixelState::sum), rgb_sumsq (W*H*3, sum of squares: m2 = sumsq - sum^2/n) and count
  * (W*H, PixelState::samples).  The image is rgb_sum / count (wavefront.cc:229-234) - rtb_resolve_counts.
