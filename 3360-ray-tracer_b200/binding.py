@@ -112,7 +112,7 @@ RTB_SYMBOLS = [
 RTH_SYMBOLS = [
     "rth_last_error", "rth_scene_build", "rth_scene_build_ex", "rth_scene_from_records", "rth_scene_desc", "rth_scene_export",
     "rth_scene_gid_map", "rth_scene_bvh_count", "rth_scene_bvh_size", "rth_scene_bvh_dump", "rth_scene_free",
-    "rth_camera_init", "rth_camera_preset",
+    "rth_camera_init", "rth_camera_preset", "rth_encode_png",
 ]
 
 
@@ -153,6 +153,7 @@ def load(counters: bool = False) -> C.CDLL:
     lib.rth_scene_free.restype = None
     lib.rth_camera_init.argtypes = [C.POINTER(RthCameraConfig), C.c_int, C.POINTER(RtbCamera)]
     lib.rth_camera_preset.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(RthCameraConfig)]
+    lib.rth_encode_png.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
     lib.rtb_scene_create.argtypes = [C.POINTER(RtbSceneDesc), C.POINTER(C.c_void_p)]
     lib.rtb_scene_destroy.argtypes = [C.c_void_p]
     lib.rtb_intersect_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
@@ -295,6 +296,20 @@ def camera_preset(json_path, name: str, counters: bool = False) -> RthCameraConf
     c = RthCameraConfig()
     _check(lib, lib.rth_camera_preset(str(json_path).encode(), name.encode(), C.byref(c)), host=True)
     return c
+
+
+def encode_png(rgb8: np.ndarray, counters: bool = False) -> bytes:
+    """rgb8: uint8 [H, W, 3] (what `resolve` returns) -> the bytes of a PNG file (rth_encode_png)."""
+    lib = load(counters)
+    img = np.ascontiguousarray(rgb8, dtype=np.uint8)
+    if img.ndim != 3 or img.shape[2] != 3:
+        raise ValueError("encode_png: expected uint8 [H, W, 3]")
+    h, w = img.shape[:2]
+    n = C.c_size_t(0)
+    _check(lib, lib.rth_encode_png(_ptr(img), w, h, None, 0, C.byref(n)), host=True)
+    out = np.empty(n.value, dtype=np.uint8)
+    _check(lib, lib.rth_encode_png(_ptr(img), w, h, _ptr(out), out.size, C.byref(n)), host=True)
+    return out[: n.value].tobytes()
 
 
 def camera_init(cfg: RthCameraConfig, depth_camera: bool = False, counters: bool = False) -> RtbCamera:

@@ -5,7 +5,7 @@
 //   rt_b200 [preset] [--scene cornell|rtiow|rtiow110|checkered|earth|earth_bubbles|bunny|stress]
 //           [--cameras file.json] [--mode A|B] [--spp N] [--depth N] [--seed N] [--assets dir]
 //           [--adaptive [threshold [min_samples]]]   per-pixel stop of the reference's WavefrontRenderer
-//           [--gpus N] [--width N] [--p6]  binary PPM   [--dump file] [--resume file]  progressive accumulator
+//           [--gpus N] [--width N] [--p6]  binary PPM  [--png]  PNG   [--dump file] [--resume file]  progressive accumulator
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
@@ -40,6 +40,7 @@ int main(int argc, char** argv) {
     else if (a == "--gpus") opt.gpus = std::max(1, std::atoi(next().c_str()));
     else if (a == "--width") width = std::atoi(next().c_str());
     else if (a == "--p6") opt.binary_ppm = true;
+    else if (a == "--png") opt.png = true;
     else if (a == "--dump") opt.dump_to = next();
     else if (a == "--resume") opt.resume_from = next();
     else if (a == "--adaptive") {

@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "../b200/flatten.h"
+#include "../core/png.h"
 #include "../core/timer.h"
 #include "../integrator/ray_integrator.h"
 #include "../integrator/sampler.h"
@@ -38,6 +39,7 @@ struct B200Options {
   int criterion = RTB_ADAPT_PIXEL_STATE;
   bool emit_ppm = true;       // write the image to `out`
   bool binary_ppm = false;    // "P6" (3 bytes per pixel) instead of the reference's ASCII "P3": same bytes, 1/4 of the text
+  bool png = false;           // PNG (8-bit RGB, core/png.h) instead of a PPM; wins over binary_ppm
   // progressive accumulator: `resume_from` continues a dumped render with its next global sample
   // indices, `dump_to` writes the accumulator after this call.  File: "RTBACC1\n" w h spp | float32 sums.
   std::string resume_from, dump_to;
@@ -117,7 +119,10 @@ class B200Renderer {
                 << "  flatten+upload " << t_upload << "s  render " << stats_.ms_total * 1e-3 << "s  "
                 << stats_.samples / (stats_.ms_total * 1e3) << " Msamples/s  " << stats_.rays / (stats_.ms_total * 1e3) << " Mrays/s\n";
     }
-    if (opt_.emit_ppm && opt_.out && opt_.binary_ppm) {
+    if (opt_.emit_ppm && opt_.out && opt_.png) {
+      const std::string file = core::EncodePng(rgb8.data(), w, h);
+      opt_.out->write(file.data(), static_cast<std::streamsize>(file.size()));
+    } else if (opt_.emit_ppm && opt_.out && opt_.binary_ppm) {
       const std::string head = "P6\n" + std::to_string(w) + ' ' + std::to_string(h) + "\n255\n";
       opt_.out->write(head.data(), static_cast<std::streamsize>(head.size()));
       opt_.out->write(reinterpret_cast<const char*>(rgb8.data()), static_cast<std::streamsize>(rgb8.size()));

@@ -10,6 +10,7 @@
 
 #include "rt/b200/flatten.h"
 #include "rt/b200/scenes.h"
+#include "rt/core/png.h"
 #include "rt/scene/camera.h"
 
 using namespace rt;
@@ -297,6 +298,20 @@ int rth_camera_preset(const char* json_path, const char* name, RthCameraConfig* 
     for (int i = 0; i < 3; ++i) { out->lookfrom[i] = c.lookfrom[i]; out->lookat[i] = c.lookat[i]; out->vup[i] = c.vup[i]; }
     out->defocus_angle = c.defocus_angle;
     out->focus_dist = c.focus_dist;
+    return RTB_OK;
+  } catch (const std::exception& e) {
+    return Fail(e);
+  }
+}
+
+int rth_encode_png(const uint8_t* rgb8, int width, int height, uint8_t* out, size_t capacity, size_t* n_bytes) {
+  if (!rgb8 || !n_bytes || width <= 0 || height <= 0) return RTB_EINVAL;
+  try {
+    const std::string file = core::EncodePng(rgb8, width, height);
+    *n_bytes = file.size();
+    if (!out) return RTB_OK;  // size query
+    if (capacity < file.size()) throw std::runtime_error("rth_encode_png: buffer of " + std::to_string(capacity) + " bytes, need " + std::to_string(file.size()));
+    std::memcpy(out, file.data(), file.size());
     return RTB_OK;
   } catch (const std::exception& e) {
     return Fail(e);

@@ -59,6 +59,11 @@ void rth_scene_free(RthScene* s);
 int rth_camera_init(const RthCameraConfig* cfg, int depth_camera, RtbCamera* out);
 int rth_camera_preset(const char* json_path, const char* name, RthCameraConfig* out);
 
+/* The 8-bit image of rtb_resolve as a PNG file (8-bit RGB, stored deflate blocks; host/rt/core/png.h) — the binary
+ * output SURVEY 8f-4 asks for beside the reference's ASCII "P3" (src/core/color.h:18-33).  out == NULL: *n_bytes = the
+ * size needed.  Otherwise writes at most `capacity` bytes. */
+int rth_encode_png(const uint8_t* rgb8, int width, int height, uint8_t* out, size_t capacity, size_t* n_bytes);
+
 #ifdef __cplusplus
 }
 #endif

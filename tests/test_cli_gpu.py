@@ -54,6 +54,15 @@ def test_p6_carries_the_same_bytes():
     assert np.abs(a - b).max() <= 1 and (a != b).mean() < 0.01
 
 
+def test_png_carries_the_same_bytes():
+    from test_png import decode_png
+    args = ("cornell", "--scene", "cornell", "--width", "60", "--spp", "64", "--depth", "8")
+    a = parse_p3(run(*args)[0])
+    b = decode_png(run(*args, "--png")[0]).astype(np.int32)
+    assert b.shape == (40, 60, 3)
+    assert np.abs(a - b).max() <= 1 and (a != b).mean() < 0.01
+
+
 def test_dump_and_resume(tmp_path):
     base = ("cornell", "--scene", "cornell", "--width", "60", "--depth", "8")
     acc = tmp_path / "acc.bin"
