@@ -264,7 +264,14 @@ void rtb_tree_destroy(RtbCompiledTree* tree);
 int rtb_scene_create(const RtbSceneDesc* desc, RtbScene** out);
 int rtb_scene_destroy(RtbScene* scene);
 
-/* seam 2: closest hit for n rays, host buffers (copies inside). */
+/* seam 2: closest hit for n rays, host buffers (copies inside).
+ * Input domain: finite origin and direction, tmin and tmax not NaN (tmax = +inf is the usual open interval).  Inside it
+ * the answer is the reference's (id bit-exact), including the edges — a zero direction, an empty or inverted interval
+ * and tmin < 0 report what Bvh::Hit reports, direction components that are zero, denormal or below 1e-20 next to
+ * normal ones are handled as axis-parallel (tests/test_hits_gpu.py::test_degenerate_rays).  A direction whose EVERY
+ * component is below 1e-20 in magnitude has hit distances beyond the float range of RtbHit.t and is outside the domain.
+ * Non-finite components are outside it too: the reference lets NaN through its comparisons and reports hits at t = NaN
+ * (sphere.h:34-45); here the call returns normally and every ray reports a miss or some primitive of the scene. */
 int rtb_intersect_batch(RtbScene* scene, const RtbRay* rays, size_t n, RtbHit* hits);
 /* same, device buffers, asynchronous on `stream` (a cudaStream_t, 0 = library stream). */
 int rtb_intersect_batch_device(RtbScene* scene, const RtbRay* d_rays, size_t n, RtbHit* d_hits,

@@ -99,6 +99,42 @@ def test_adversarial_rays(rt, scenes):
         assert helpers.check_hits(ds.intersect(r), t_ref, gid_ref)
 
 
+@pytest.mark.parametrize("name", ["mixed", "bunny"])
+def test_degenerate_rays(rt, scenes, name):
+    """The edges of the input domain.  Zero directions, empty / inverted intervals, a negative tmin and direction
+    components that are zero, denormal or tiny next to normal ones answer like the reference.  Non-finite components
+    are outside the contract (include/rtb.h: the reference itself lets NaN through its comparisons and reports hits at
+    t = NaN, sphere.h:34-45): the call returns, and what it returns is a miss or a primitive of the scene."""
+    from oracle import checker
+    hs, ds = scenes[name]
+    ora = checker.make_oracle(hs)
+    rng = np.random.default_rng(77)
+    n = 4096
+    o = rng.uniform(-3, 3, (n, 3))
+    d = rng.normal(size=(n, 3))
+    pick = (np.arange(n), rng.integers(0, 3, n))
+    one = d.copy(); one[pick] = rng.choice([1e-41, -1e-41, 1e-30, -3e-25, 0.0, -0.0], n)
+    two = np.full((n, 3), 1e-41) * rng.choice([-1.0, 1.0], (n, 3)); two[pick] = rng.normal(size=n)
+
+    def batch(oo, dd, tmin, tmax):
+        r = np.zeros(n, rt.RAY_DTYPE)
+        r["o"], r["d"], r["tmin"], r["tmax"] = oo.astype(np.float32), dd.astype(np.float32), tmin, tmax
+        return r
+
+    for r in (batch(o, np.zeros((n, 3)), 0.001, np.inf), batch(o, d, 5.0, 1.0), batch(o, d, 2.0, 2.0), batch(o, d, -10.0, np.inf),
+              batch(o, one, 0.001, np.inf), batch(o, two, 0.001, np.inf)):
+        t_ref, gid_ref = ora.intersect(r)
+        assert helpers.check_hits(ds.intersect(r), t_ref, gid_ref)
+    n_prims = int((hs.export()[0][:, 0] < 3).sum())
+    bad_o, bad_d = o.copy(), d.copy()
+    bad_o[pick] = rng.choice([np.nan, np.inf, -np.inf], n)
+    bad_d[pick] = rng.choice([np.nan, np.inf, -np.inf], n)
+    for r in (batch(bad_o, d, 0.001, np.inf), batch(o, bad_d, 0.001, np.inf), batch(o * np.nan, d * np.nan, np.nan, np.nan),
+              batch(o, d, 0.001, np.nan)):
+        h = ds.intersect(r)
+        assert len(h) == n and np.all((h["prim_id"] >= -1) & (h["prim_id"] < n_prims))
+
+
 def test_exact_ties_follow_reference_slot_order(rt, scenes):
     """Duplicated primitives: a later triangle wins an exact-t tie, an earlier sphere / rect does (bvh.h:95-106)."""
     from oracle import checker
