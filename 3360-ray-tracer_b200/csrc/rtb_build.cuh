@@ -179,8 +179,9 @@ __global__ void __launch_bounds__(256) build_hierarchy_kernel(const unsigned lon
 
 __device__ __forceinline__ void store_half(float* pair, uint32_t side, const BuildBox& b, uint32_t desc) {
   float* p = pair + 6 * side;
-  p[0] = b.lo[0]; p[1] = b.lo[1]; p[2] = b.lo[2];
-  p[3] = b.hi[0]; p[4] = b.hi[1]; p[5] = b.hi[2];
+  p[0] = b.lo[0]; p[1] = b.hi[0];  // {lo.x hi.x lo.y hi.y lo.z hi.z}, rtb_compile.h Pair
+  p[2] = b.lo[1]; p[3] = b.hi[1];
+  p[4] = b.lo[2]; p[5] = b.hi[2];
   reinterpret_cast<uint32_t*>(pair)[12 + side] = desc;
 }
 
@@ -207,8 +208,8 @@ __global__ void __launch_bounds__(256) build_emit_kernel(const BuildBox* __restr
     const float* o = pair + 6 * (side ^ 1u);
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-      box.lo[c] = fminf(box.lo[c], __ldcg(o + c));
-      box.hi[c] = fmaxf(box.hi[c], __ldcg(o + 3 + c));
+      box.lo[c] = fminf(box.lo[c], __ldcg(o + 2 * c));  // {lo.x hi.x lo.y hi.y lo.z hi.z}
+      box.hi[c] = fmaxf(box.hi[c], __ldcg(o + 2 * c + 1));
     }
     desc = p;
     ++levels;

@@ -4,7 +4,7 @@
 // The closest hit the kernels return is a pure function of (exact primitive tests, tie rule)
 // (rtb_device.cuh), so the device tree only has to be CONSERVATIVE, not equal to the reference's
 // geom::Bvh (src/geom/bvh.h:166-367).  That freedom is used here:
-//   * sibling PAIRS are the unit: one 64-byte record {lo0 hi0 lo1 hi1 | desc0 desc1 | pad} per
+//   * sibling PAIRS are the unit: one 64-byte record {box0 box1 | desc0 desc1 | pad}, box = {lo.x hi.x lo.y hi.y lo.z hi.z}, per
 //     internal node, i.e. one 128-bit x4 fetch and both slab tests per traversal step;
 //   * a child descriptor says everything needed to continue (no second fetch): internal -> pair
 //     index; leaf -> primitive type, count and first index into that type's leaf-ordered table.
@@ -70,8 +70,7 @@ inline float Up(double v) {
 }
 
 struct Pair {  // 64 bytes, the device record: three 128-bit loads of boxes + one 64-bit load of descriptors
-  float lo0[3], hi0[3];
-  float lo1[3], hi1[3];
+  float box0[6], box1[6];  // each {lo.x hi.x lo.y hi.y lo.z hi.z}: (lo, hi) of an axis is one aligned 64-bit pair (FADD2 / FMUL2 operand)
   uint32_t d0, d1;
   uint32_t pad[2];
 };
@@ -478,11 +477,10 @@ class Compiler {
   }
 
   static void SetChild(Pair& p, int side, const Box& b, uint32_t desc) {
-    float* lo = side ? p.lo1 : p.lo0;
-    float* hi = side ? p.hi1 : p.hi0;
+    float* box = side ? p.box1 : p.box0;
     for (int k = 0; k < 3; ++k) {
-      lo[k] = b.lo[k];
-      hi[k] = b.hi[k];
+      box[2 * k] = b.lo[k];
+      box[2 * k + 1] = b.hi[k];
     }
     (side ? p.d1 : p.d0) = desc;
     p.pad[0] = p.pad[1] = 0;

@@ -95,10 +95,8 @@ __device__ __forceinline__ float4 ld_pair_global(unsigned long long addr) {
 #ifndef RTB_LD256
 #define RTB_LD256 1
 #endif
-__device__ __forceinline__ void ld256_global(unsigned long long addr, float (&v)[8]) {
-  asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-      : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
-      : "l"(addr));
+__device__ __forceinline__ void ld256_global(unsigned long long addr, unsigned long long (&v)[4]) {
+  asm("ld.global.nc.v4.b64 {%0,%1,%2,%3}, [%4];" : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3]) : "l"(addr));
 }
 
 // Per-thread traversal stack: the first kSmemStack entries in shared memory, laid out [entry][thread]
@@ -160,31 +158,35 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
   // one node step of this lane (both children of pair `cur`, near one first, far one pushed)
   auto node_step = [&]() {
     const unsigned long long addr = ((kUseSmem && cur < n_top) ? base_top : base_all) + (unsigned long long)cur * 64ull;
-    // record = {lo0.xyz hi0.xyz lo1.xyz hi1.xyz desc0 desc1 - -}
-    float4 q0, q1, q2;
+    // record = {box0 box1 desc0 desc1 - -}, box = {lo.x hi.x lo.y hi.y lo.z hi.z}: six 64-bit (lo, hi) pairs
+    f32x2 bx[6];
     uint2 dd;
     if (!kUseSmem && RTB_LD256) {
-      float a[8], c[8];
-      ld256_global(addr, a);
+      f32x2 c[4];
+      ld256_global(addr, c);
+      bx[0] = c[0]; bx[1] = c[1]; bx[2] = c[2]; bx[3] = c[3];
       ld256_global(addr + 32, c);
-      q0 = make_float4(a[0], a[1], a[2], a[3]); q1 = make_float4(a[4], a[5], a[6], a[7]); q2 = make_float4(c[0], c[1], c[2], c[3]);
-      dd = make_uint2(__float_as_uint(c[4]), __float_as_uint(c[5]));
-    } else if (kUseSmem) {
-      q0 = ld_pair_generic(addr); q1 = ld_pair_generic(addr + 16); q2 = ld_pair_generic(addr + 32);
-      asm("ld.v2.u32 {%0,%1}, [%2];" : "=r"(dd.x), "=r"(dd.y) : "l"(addr + 48));
+      bx[4] = c[0]; bx[5] = c[1];
+      dd = make_uint2((uint32_t)c[2], (uint32_t)(c[2] >> 32));
     } else {
-      q0 = ld_pair_global(addr); q1 = ld_pair_global(addr + 16); q2 = ld_pair_global(addr + 32);
-      asm("ld.global.nc.v2.u32 {%0,%1}, [%2];" : "=r"(dd.x), "=r"(dd.y) : "l"(addr + 48));
+      float4 q0, q1, q2;
+      if (kUseSmem) {
+        q0 = ld_pair_generic(addr); q1 = ld_pair_generic(addr + 16); q2 = ld_pair_generic(addr + 32);
+        asm("ld.v2.u32 {%0,%1}, [%2];" : "=r"(dd.x), "=r"(dd.y) : "l"(addr + 48));
+      } else {
+        q0 = ld_pair_global(addr); q1 = ld_pair_global(addr + 16); q2 = ld_pair_global(addr + 32);
+        asm("ld.global.nc.v2.u32 {%0,%1}, [%2];" : "=r"(dd.x), "=r"(dd.y) : "l"(addr + 48));
+      }
+      bx[0] = pack2(q0.x, q0.y); bx[1] = pack2(q0.z, q0.w); bx[2] = pack2(q1.x, q1.y);
+      bx[3] = pack2(q1.z, q1.w); bx[4] = pack2(q2.x, q2.y); bx[5] = pack2(q2.z, q2.w);
     }
-    const float4 llo = make_float4(q0.x, q0.y, q0.z, 0.f), lhi = make_float4(q0.w, q1.x, q1.y, 0.f);
-    const float4 rlo = make_float4(q1.z, q1.w, q2.x, 0.f), rhi = make_float4(q2.y, q2.z, q2.w, 0.f);
 #ifdef RTB_COUNTERS
     ++n_pairs;
     ++steps;
 #endif
     float tl, tr;
-    const bool hl = slab(r, llo, lhi, b.hi, tl);
-    const bool hr = slab(r, rlo, rhi, b.hi, tr);
+    const bool hl = slab(r, bx[0], bx[1], bx[2], b.hi, tl);
+    const bool hr = slab(r, bx[3], bx[4], bx[5], b.hi, tr);
     const uint32_t dl = dd.x, dr = dd.y;
     if (hl && hr) {
       const bool left_first = tl <= tr;
