@@ -791,7 +791,7 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
     for (size_t k = 0; k < n_waves; ++k) waves.push_back(&ctx->waves[k]);
   rtb::RenderConsts rcst{};
   rcst.cam = *cam;
-  rcst.key = make_uint2((uint32_t)prm->seed, (uint32_t)(prm->seed >> 32));
+  rcst.round_keys = rtb::philox_key_schedule((uint32_t)prm->seed, (uint32_t)(prm->seed >> 32));
   rcst.max_depth = prm->max_depth;
   rcst.mode = prm->mode;
   rcst.spp_begin = prm->spp_begin;

@@ -67,15 +67,28 @@ struct HitCounters {  // only touched when RTB_COUNTERS is defined
 #ifndef RTB_PHILOX_ROUNDS
 #define RTB_PHILOX_ROUNDS 10
 #endif
-__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
-  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+constexpr uint32_t kPhiloxW0 = 0x9E3779B9u, kPhiloxW1 = 0xBB67AE85u;
+// The key schedule (key + r * W) depends on the seed only: the host writes it once per render into the kernel's
+// parameter block (RenderConsts::round_keys), where every round reads it as a constant-bank operand — 2 integer adds
+// per round and call less than stepping the key in registers.
+struct PhiloxKeys {
+  uint32_t k[2 * RTB_PHILOX_ROUNDS];
+};
+inline __host__ __device__ PhiloxKeys philox_key_schedule(uint32_t k0, uint32_t k1) {
+  PhiloxKeys ks;
+  for (int r = 0; r < RTB_PHILOX_ROUNDS; ++r) {
+    ks.k[2 * r] = k0 + (uint32_t)r * kPhiloxW0;
+    ks.k[2 * r + 1] = k1 + (uint32_t)r * kPhiloxW1;
+  }
+  return ks;
+}
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, const PhiloxKeys& ks) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
 #pragma unroll
   for (int r = 0; r < RTB_PHILOX_ROUNDS; ++r) {
     const uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
     const uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
-    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
-    key.x += W0;
-    key.y += W1;
+    ctr = make_uint4(hi1 ^ ctr.y ^ ks.k[2 * r], lo1, hi0 ^ ctr.w ^ ks.k[2 * r + 1], lo0);
   }
   return ctr;
 }
@@ -115,11 +128,18 @@ __device__ __forceinline__ float safe_dir(float d) {
 //   2  the same on the packed FP32 pipe: FADD2 / FMUL2 take (lo, hi) of an axis as one operand and the ray
 //      constant as a broadcast scalar — 6 + 6 instructions per pair step and 6 registers fewer than form 0
 //   3  form 0 as 6 FFMA2 with (b_lo, b_hi) as a register pair
+#ifndef RTB_SLAB_BCAST
+#define RTB_SLAB_BCAST 1  // 0: packs built outside the asm (the compiler hoists them into register pairs: +6 registers, measured slower)
+#endif
 typedef unsigned long long f32x2;
 __device__ __forceinline__ f32x2 pack2(float a, float b) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
 __device__ __forceinline__ void unpack2(f32x2 v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
 __device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
 __device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+// pair (op) scalar: the pack sits inside the asm block so that the compiler cannot hoist {s, s} out of the traversal loop as a
+// 64-bit loop invariant (two registers per constant); ptxas folds it into the broadcast operand form `FADD2 Rd, Ra, -Rs.F32`
+__device__ __forceinline__ f32x2 sub2s(f32x2 a, float s) { f32x2 d; asm("{\n .reg .b64 t;\n mov.b64 t, {%2, %2};\n sub.rn.f32x2 %0, %1, t;\n}" : "=l"(d) : "l"(a), "f"(s)); return d; }
+__device__ __forceinline__ f32x2 mul2s(f32x2 a, float s) { f32x2 d; asm("{\n .reg .b64 t;\n mov.b64 t, {%2, %2};\n mul.rn.f32x2 %0, %1, t;\n}" : "=l"(d) : "l"(a), "f"(s)); return d; }
 __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
 
 __device__ __forceinline__ void slab_axis(float o, float d, float& inv, float& bl, float& bh) {
@@ -159,9 +179,15 @@ __device__ __forceinline__ void prepare_ray(TravRay& r, float4 o, float4 d) {
 __device__ __forceinline__ bool slab(const TravRay& r, f32x2 px, f32x2 py, f32x2 pz, float thi, float& tn) {
   float ax, bx, ay, by, az, bz;
 #if RTB_SLAB_FORM == 2
+#if RTB_SLAB_BCAST
+  unpack2(mul2s(sub2s(px, r.ox), r.ix), ax, bx);
+  unpack2(mul2s(sub2s(py, r.oy), r.iy), ay, by);
+  unpack2(mul2s(sub2s(pz, r.oz), r.iz), az, bz);
+#else
   unpack2(mul2(add2(px, pack2(-r.ox, -r.ox)), pack2(r.ix, r.ix)), ax, bx);
   unpack2(mul2(add2(py, pack2(-r.oy, -r.oy)), pack2(r.iy, r.iy)), ay, by);
   unpack2(mul2(add2(pz, pack2(-r.oz, -r.oz)), pack2(r.iz, r.iz)), az, bz);
+#endif
 #elif RTB_SLAB_FORM == 3
   unpack2(fma2(px, pack2(r.ix, r.ix), r.bx2), ax, bx);
   unpack2(fma2(py, pack2(r.iy, r.iy), r.by2), ay, by);

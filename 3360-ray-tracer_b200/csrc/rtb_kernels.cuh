@@ -16,7 +16,7 @@ struct PathQueue {
 
 struct RenderConsts {
   RtbCamera cam;
-  uint2 key;  // Philox key
+  PhiloxKeys round_keys;  // Philox4x32 key schedule of the seed (philox_key_schedule)
   int max_depth;
   int mode;
   int spp_begin;
@@ -65,6 +65,9 @@ __device__ __forceinline__ void stage_top(const DevScene& s, float4* smem_pairs)
 #endif
 #ifndef RTB_NODE_STEPS_PER_VOTE
 #define RTB_NODE_STEPS_PER_VOTE 2
+#endif
+#ifndef RTB_STACK_SENTINEL
+#define RTB_STACK_SENTINEL 0
 #endif
 #ifndef RTB_SMEM_STACK  // traversal-stack entries per thread kept in shared memory (the rest: local memory)
 #define RTB_SMEM_STACK 0
@@ -150,9 +153,15 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
     }
 #endif
   };
+  // RTB_STACK_SENTINEL: entry 0 of every ray's stack is the DONE mark, so a pop needs no "stack empty?" test —
+  // popping the sentinel IS finishing (rtb_scene_create keeps two entries of headroom, rtb_api.cu)
   auto pop_or_finish = [&]() {
-    if (sp > 0) cur = stack.at(--sp);
+#if RTB_STACK_SENTINEL && !defined(RTB_COUNTERS)
+    cur = stack.at(--sp);
+#else
+    if (sp > (RTB_STACK_SENTINEL ? 1 : 0)) cur = stack.at(--sp);
     else finish();
+#endif
   };
 
   // one node step of this lane (both children of pair `cur`, near one first, far one pushed)
@@ -254,7 +263,12 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
         prepare_ray(r, o, d);
         b.ref = kNoHit; b.tf = d.w; b.ef = 0.f; b.hi = d.w;
         cur = 0;  // pair 0 = the root's two children
+#if RTB_STACK_SENTINEL
+        stack.push(0, kDoneMark);
+        sp = 1;
+#else
         sp = 0;
+#endif
         ++io.rays;
 #ifdef RTB_COUNTERS
         ++n_rays;
@@ -369,7 +383,7 @@ struct PathState {  // what a path carries besides its ray
 // Camera::GetRay for global sample `sample` of `pixel`: Philox(pixel, sample, stream -1) -> jitter + lens point.
 __device__ __forceinline__ void camera_ray(const RenderConsts& rc, uint32_t pixel, uint32_t sample, float4& ro, float4& rd, PathState& ps) {
   const int px = (int)(pixel % (uint32_t)rc.cam.width), py = (int)(pixel / (uint32_t)rc.cam.width);
-  const uint4 rnd = philox4x32_10(make_uint4(pixel, sample, 0xffffffffu, 0u), rc.key);
+  const uint4 rnd = philox4x32_10(make_uint4(pixel, sample, 0xffffffffu, 0u), rc.round_keys);
   const RtbCamera& c = rc.cam;
   const float jx = u01(rnd.x) - 0.5f, jy = u01(rnd.y) - 0.5f;
   const float fi = (float)px + jx, fj = (float)py + jy;
@@ -494,7 +508,7 @@ __device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts
     const bool front = dot3(d, n_out) < 0.0f;  // HitRecord::set_face_normal, hittable.h:31-34
     const f3 nrm = front ? n_out : -n_out;
     const RtbMaterial m = s.materials[mat_id];
-    const uint4 rnd = philox4x32_10(make_uint4(pixel, ps.sample, bounce, 0u), rc.key);
+    const uint4 rnd = philox4x32_10(make_uint4(pixel, ps.sample, bounce, 0u), rc.round_keys);
     f3 atten = mk3(1.0f, 1.0f, 1.0f), dir = nrm;
     if (rc.mode == RTB_MODE_A) {
       if (m.type == RTB_MAT_LAMBERTIAN) {  // material.cc:20-34
