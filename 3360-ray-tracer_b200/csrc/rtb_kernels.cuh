@@ -69,6 +69,9 @@ __device__ __forceinline__ void stage_top(const DevScene& s, float4* smem_pairs)
 #ifndef RTB_STACK_SENTINEL
 #define RTB_STACK_SENTINEL 0
 #endif
+#ifndef RTB_NODE_BRANCHLESS
+#define RTB_NODE_BRANCHLESS 0
+#endif
 #ifndef RTB_SMEM_STACK  // traversal-stack entries per thread kept in shared memory (the rest: local memory)
 #define RTB_SMEM_STACK 0
 #endif
@@ -197,6 +200,17 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
     const bool hl = slab(r, bx[0], bx[1], bx[2], b.hi, tl);
     const bool hr = slab(r, bx[3], bx[4], bx[5], b.hi, tr);
     const uint32_t dl = dd.x, dr = dd.y;
+#if RTB_NODE_BRANCHLESS && RTB_STACK_SENTINEL && !defined(RTB_COUNTERS)
+    // straight-line form: selects and predicated stack accesses instead of a three-way branch (each arm of which
+    // costs a BRA and its own arrival at the reconvergence barrier)
+    const bool left_first = tl <= tr;
+    const bool both = hl && hr;
+    if (both) stack.push(sp, left_first ? dr : dl);
+    sp += both ? 1 : 0;
+    uint32_t next = (hl && (left_first || !hr)) ? dl : dr;
+    if (!(hl || hr)) next = stack.at(--sp);
+    cur = next;
+#else
     if (hl && hr) {
       const bool left_first = tl <= tr;
       stack.push(sp++, left_first ? dr : dl);
@@ -206,6 +220,7 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
     } else {
       pop_or_finish();
     }
+#endif
   };
   // one primitive of the leaf this lane stands at; the descriptor itself is the loop counter
   auto leaf_step = [&](uint32_t type) {
