@@ -69,6 +69,9 @@ __device__ __forceinline__ void stage_top(const DevScene& s, float4* smem_pairs)
 #ifndef RTB_STACK_SENTINEL
 #define RTB_STACK_SENTINEL 0
 #endif
+#ifndef RTB_POSTPONE_LEAF
+#define RTB_POSTPONE_LEAF 0
+#endif
 #ifndef RTB_NODE_BRANCHLESS
 #define RTB_NODE_BRANCHLESS 0
 #endif
@@ -131,6 +134,9 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
   TravRay r;
   Best b{kNoHit, 0.f, 0.f, 0.f};
   uint32_t cur = 0, slot = 0;
+#if RTB_POSTPONE_LEAF
+  uint32_t post = 0;  // a leaf descriptor waiting for the leaf phase (0 = none: leaf descriptors have bit 31 set)
+#endif
   bool active = false;
   unsigned pool_next = 0, pool_end = 0;  // warp-uniform: claimed, not yet assigned ray indices
   bool exhausted = false;                 // warp-uniform: the global cursor ran past n
@@ -297,9 +303,18 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
     const int n_act = n_trace;
     // ---- node phase: descend while the descending lanes are the majority
     for (;;) {
-      const bool at_node = active && !(cur & kLeafBit);
+      bool at_node = active && !(cur & kLeafBit);
       const unsigned nm = __ballot_sync(kFull, at_node);
       if (nm == 0u || RTB_NODE_EXIT_DEN * __popc(nm) < RTB_NODE_EXIT_NUM * n_act) break;
+#if RTB_POSTPONE_LEAF
+      // speculative traversal (Aila & Laine 2009): the node phase goes on, so a lane standing at a leaf keeps it for the
+      // leaf phase and descends from its stack with the others instead of idling; one leaf per lane can wait
+      if (active && !at_node && post == 0u && cur != kDoneMark) {
+        post = cur;
+        pop_or_finish();
+        at_node = !(cur & kLeafBit);
+      }
+#endif
       if (at_node) node_step();
 #pragma unroll
       for (int extra = 1; extra < RTB_NODE_STEPS_PER_VOTE; ++extra)  // more steps on the same vote: less vote overhead
@@ -307,6 +322,13 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
     }
     // ---- leaf phase, one primitive type at a time (the types are different code, SIMT would serialise
     // them anyway); each lane works through its whole leaf, the descriptor counting down
+#if RTB_POSTPONE_LEAF
+    if (post != 0u) {  // the waiting leaf first; where the lane stands now (pair, leaf or DONE) goes back on the stack
+      stack.push(sp++, cur);
+      cur = post;
+      post = 0u;
+    }
+#endif
 #pragma unroll 1
     for (uint32_t type = 0; type < 3; ++type) {
       const uint32_t want = 4u + type;  // leaf bit + type in the top three bits
