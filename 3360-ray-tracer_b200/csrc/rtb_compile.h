@@ -69,7 +69,7 @@ inline float Up(double v) {
   return f;
 }
 
-struct Pair {  // 64 bytes, the device record: three 128-bit loads of boxes + one 64-bit load of descriptors
+struct Pair {  // 64 bytes, the device record: two 256-bit loads per traversal step
   float box0[6], box1[6];  // each {lo.x hi.x lo.y hi.y lo.z hi.z}: (lo, hi) of an axis is one aligned 64-bit pair (FADD2 / FMUL2 operand)
   uint32_t d0, d1;
   uint32_t pad[2];

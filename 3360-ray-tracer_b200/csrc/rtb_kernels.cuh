@@ -104,8 +104,11 @@ __device__ __forceinline__ float4 ld_pair_global(unsigned long long addr) {
 #ifndef RTB_LD256
 #define RTB_LD256 1
 #endif
+#ifndef RTB_PAIR_LD_HINT  // cache hints of the pair loads, e.g. ".L1::evict_last" or ".L2::128B" (measured: profiles/r01_traversal_probes.txt)
+#define RTB_PAIR_LD_HINT ""
+#endif
 __device__ __forceinline__ void ld256_global(unsigned long long addr, unsigned long long (&v)[4]) {
-  asm("ld.global.nc.v4.b64 {%0,%1,%2,%3}, [%4];" : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3]) : "l"(addr));
+  asm("ld.global.nc" RTB_PAIR_LD_HINT ".v4.b64 {%0,%1,%2,%3}, [%4];" : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3]) : "l"(addr));
 }
 
 // Per-thread traversal stack: the first kSmemStack entries in shared memory, laid out [entry][thread]
