@@ -848,10 +848,19 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   if (trace && fused && ad && total > 0) {
     // passes of R speculative samples per active pixel + an in-order replay of the stop rule (rtb_kernels.cuh);
     // the active count stays on the device, so the passes are enqueued back to back without a host round trip
-    uint32_t R = 16;  // = kMinSamples of the reference: the first chunk is never wasted; 8 -> 16 measured 9.5 -> 8.1 ms on bunny C3
+    // Chunk size: every pass ends in a kernel tail (the deepest paths running alone, ~0.4-0.8 ms on bunny C3), every chunk wastes
+    // up to R - 1 samples per pixel.  Measured on bunny C3, max 100 (profiles/r01_traversal_probes.txt): R = 8 / 16 / 28 / 40 / 64 ->
+    // 9.8 / 7.8 / 7.05 / 7.1 / 7.6 ms with estimator B, 14.4 / 10.4 / 8.65 / 8.25 / 8.25 with A.  The passes are then made equal
+    // (100 -> 34 + 34 + 32 rather than 40 + 40 + 20): a short last pass pays a whole tail for a few samples.
+    uint32_t R = 40;
     if (const char* e = std::getenv("RTB_ADAPT_CHUNK")) R = (uint32_t)std::min(64, std::max(1, std::atoi(e)));
     const uint32_t spp_max = (uint32_t)rcst.spp_max;
+    while (R > 16 && (size_t)n_pixels * R * 12 > ((size_t)2 << 30)) R -= 8;  // the chunk buffer stays below 2 GB (4K: R = 16)
     R = std::min(R, spp_max);
+    if (!std::getenv("RTB_ADAPT_UNEVEN")) {
+      const uint32_t n_pass = (spp_max + R - 1) / R;
+      R = (spp_max + n_pass - 1) / n_pass;
+    }
     const size_t list_bytes = ((size_t)n_pixels * 4 + 255) & ~(size_t)255, chunk_bytes = (size_t)n_pixels * R * 12;
     const size_t need = 2 * list_bytes + 256 + chunk_bytes;
     if (ctx->adapt_bytes < need) {

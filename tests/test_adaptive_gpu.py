@@ -81,8 +81,8 @@ def test_luminance_criterion(rt, scenes):
     cam = rt.camera_init(rt.camera_config(**PATHB_CAMERAS["rtiow"]))
     thr, mn, mx = 0.03, 8, 64
     s, q, c, st = ds.render_adaptive(cam, max_spp=mx, max_depth=10, rel_threshold=thr, min_samples=mn, criterion=rt.ADAPT_LUMINANCE, mode=rt.MODE_A)
-    # samples are traced speculatively in chunks of 16; what the stop rule did not need is discarded, not recorded
-    assert c.min() >= mn and c.max() <= mx and int(c.sum()) <= st["samples"] <= int(c.sum()) + 15 * c.size
+    # samples are traced speculatively in chunks of at most 64; what the stop rule did not need is discarded, not recorded
+    assert c.min() >= mn and c.max() <= mx and int(c.sum()) <= st["samples"] <= int(c.sum()) + 63 * c.size
     lum = np.array([0.2126, 0.7152, 0.0722])
     n = c.astype(np.float64)[..., None]
     mean = s / n
@@ -105,7 +105,7 @@ def test_matches_reference_wavefront_renderer(rt, golden_dir, scenes, name):
     cam = rt.camera_init(rt.camera_config(**PATHB_CAMERAS[name]))
     n_pix = cam.width * cam.height
     s, q, c, st = scenes[name].render_adaptive(cam, max_spp=max_samples, max_depth=depth, rel_threshold=0.05, min_samples=16, mode=rt.MODE_B)
-    assert int(c.sum()) <= st["samples"] <= int(c.sum()) + 15 * c.size
+    assert int(c.sum()) <= st["samples"] <= int(c.sum()) + 63 * c.size
     active = np.array([(c > k).sum() for k in range(max_samples)], dtype=np.float64)
     ref_a, ref_s = g["active_mean"], g["active_std"]
     assert np.all(active[:16] == n_pix) and np.all(ref_a[:16] == n_pix)
