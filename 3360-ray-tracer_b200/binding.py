@@ -110,7 +110,7 @@ RTB_SYMBOLS = [
     "rtb_resolve_device", "rtb_resolve", "rtb_measure_l2_gbs", "rtb_measure_fp32_tflops", "rtb_measure_fp64_tflops",
 ]
 RTH_SYMBOLS = [
-    "rth_last_error", "rth_scene_build", "rth_scene_build_ex", "rth_scene_from_records", "rth_scene_desc", "rth_scene_export",
+    "rth_last_error", "rth_set_tree_compiler", "rth_scene_build", "rth_scene_build_ex", "rth_scene_from_records", "rth_scene_desc", "rth_scene_export",
     "rth_scene_gid_map", "rth_scene_bvh_count", "rth_scene_bvh_size", "rth_scene_bvh_dump", "rth_scene_free",
     "rth_camera_init", "rth_camera_preset", "rth_encode_png",
 ]
@@ -123,21 +123,30 @@ def lib_path(counters: bool = False) -> Path:
     return PKG_DIR / ("librtb200_counters.so" if counters else "librtb200.so")
 
 
+def host_lib_path() -> Path:
+    return PKG_DIR / "librth.so"
+
+
 _LIBS: dict = {}
+_HOST: list = []
+# rth_set_tree_compiler's callback types (include/rth.h)
+_COMPILE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p)
+_DESTROY_FN = C.CFUNCTYPE(None, C.c_void_p)
+_ERROR_FN = C.CFUNCTYPE(C.c_char_p)
 
 
-def load(counters: bool = False) -> C.CDLL:
-    """Load the CUDA extension.  Fails loudly when it has not been built — there is no fallback."""
-    key = bool(counters)
-    if key in _LIBS:
-        return _LIBS[key]
-    p = lib_path(counters)
+def load_host() -> C.CDLL:
+    """librth.so alone: the host C++ scene API (scene builders, flattener, cameras, PNG).  Pure C++ - loading it does not map
+    the CUDA library, which is what `bench.py --impl reference` and the oracle-only tests use."""
+    if _HOST:
+        return _HOST[0]
+    p = host_lib_path()
     if not p.exists():
-        raise ImportError(f"{p} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` (nvcc, sm_100a). "
-                          "There is no CPU or PyTorch fallback for the path-tracing hot path.")
+        raise ImportError(f"{p} is missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
     lib = C.CDLL(str(p))
-    lib.rtb_last_error.restype = C.c_char_p
     lib.rth_last_error.restype = C.c_char_p
+    lib.rth_set_tree_compiler.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.rth_set_tree_compiler.restype = None
     lib.rth_scene_desc.restype = C.POINTER(RtbSceneDesc)
     lib.rth_scene_desc.argtypes = [C.c_void_p]
     lib.rth_scene_build.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_char_p, C.c_uint32, C.POINTER(C.c_void_p)]
@@ -154,6 +163,32 @@ def load(counters: bool = False) -> C.CDLL:
     lib.rth_camera_init.argtypes = [C.POINTER(RthCameraConfig), C.c_int, C.POINTER(RtbCamera)]
     lib.rth_camera_preset.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(RthCameraConfig)]
     lib.rth_encode_png.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+    _HOST.append(lib)
+    return lib
+
+
+class _Product:
+    """Both libraries behind one object: rth_* resolves in librth.so, rtb_* in librtb200.so (or a counters / variant build)."""
+
+    def __init__(self, host, cuda):
+        self._host, self._cuda = host, cuda
+
+    def __getattr__(self, name):
+        return getattr(self._host if name.startswith("rth_") else self._cuda, name)
+
+
+def load(counters: bool = False) -> "_Product":
+    """Load the CUDA extension (and the host library).  Fails loudly when it has not been built — there is no fallback."""
+    key = bool(counters)
+    if key in _LIBS:
+        return _LIBS[key]
+    p = lib_path(counters)
+    if not p.exists():
+        raise ImportError(f"{p} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` (nvcc, sm_100a). "
+                          "There is no CPU or PyTorch fallback for the path-tracing hot path.")
+    host = load_host()
+    lib = C.CDLL(str(p))
+    lib.rtb_last_error.restype = C.c_char_p
     lib.rtb_scene_create.argtypes = [C.POINTER(RtbSceneDesc), C.POINTER(C.c_void_p)]
     lib.rtb_scene_destroy.argtypes = [C.c_void_p]
     lib.rtb_intersect_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
@@ -174,8 +209,17 @@ def load(counters: bool = False) -> C.CDLL:
     lib.rtb_measure_fp32_tflops.argtypes = [C.c_int, C.POINTER(C.c_float)]
     lib.rtb_measure_fp64_tflops.argtypes = [C.c_int, C.POINTER(C.c_float)]
     lib.rtb_init.argtypes = [C.c_int]
-    _LIBS[key] = lib
-    return lib
+    prod = _Product(host, lib)
+    _LIBS[key] = prod
+    return prod
+
+
+def _use_compiler(lib):
+    """Scenes built from now on are compiled (rtb_tree_compile: host work, once per scene) by THIS device library; a scene
+    keeps the destroyer of the library that compiled it."""
+    cuda = lib._cuda
+    lib._host.rth_set_tree_compiler(C.cast(cuda.rtb_tree_compile, C.c_void_p), C.cast(cuda.rtb_tree_destroy, C.c_void_p),
+                                    C.cast(cuda.rtb_last_error, C.c_void_p))
 
 
 def _check(lib, rc: int, host: bool = False):
@@ -195,9 +239,17 @@ class HostScene:
         self._h, self._lib = handle, lib
 
     @classmethod
-    def build(cls, name: str, params=(), top_budget: int = 0, counters: bool = False, asset_dir=None, device_tree: bool = False) -> "HostScene":
-        """device_tree: no host SAH build; rtb_scene_create builds a linear BVH on the GPU (RTB_SCENE_DEVICE_BUILD)."""
-        lib = load(counters)
+    def build(cls, name: str, params=(), top_budget: int = 0, counters: bool = False, asset_dir=None, device_tree: bool = False,
+              host_only: bool = False) -> "HostScene":
+        """device_tree: no host SAH build; rtb_scene_create builds a linear BVH on the GPU (RTB_SCENE_DEVICE_BUILD).
+        host_only: librth.so alone (the CUDA library is not loaded; the scene carries no compiled device tree) - for feeding
+        the oracle from a process that must not touch the product's kernels."""
+        if host_only:
+            lib = load_host()
+            lib.rth_set_tree_compiler(None, None, None)
+        else:
+            lib = load(counters)
+            _use_compiler(lib)
         p = np.asarray(params, dtype=np.float64)
         h = C.c_void_p()
         rc = lib.rth_scene_build_ex(name.encode(), _ptr(p) if p.size else None, int(p.size),
@@ -208,6 +260,7 @@ class HostScene:
     @classmethod
     def from_records(cls, prims, mats, texs, image_paths: str = "", top_budget: int = 0, counters: bool = False) -> "HostScene":
         lib = load(counters)
+        _use_compiler(lib)
         prims = np.ascontiguousarray(prims, dtype=np.float64).reshape(-1, 16)
         mats = np.ascontiguousarray(mats, dtype=np.float64).reshape(-1, 8)
         texs = np.ascontiguousarray(texs, dtype=np.float64).reshape(-1, 8)
@@ -292,7 +345,7 @@ def camera_config(**kw) -> RthCameraConfig:
 
 
 def camera_preset(json_path, name: str, counters: bool = False) -> RthCameraConfig:
-    lib = load(counters)
+    lib = load_host()
     c = RthCameraConfig()
     _check(lib, lib.rth_camera_preset(str(json_path).encode(), name.encode(), C.byref(c)), host=True)
     return c
@@ -300,7 +353,7 @@ def camera_preset(json_path, name: str, counters: bool = False) -> RthCameraConf
 
 def encode_png(rgb8: np.ndarray, counters: bool = False) -> bytes:
     """rgb8: uint8 [H, W, 3] (what `resolve` returns) -> the bytes of a PNG file (rth_encode_png)."""
-    lib = load(counters)
+    lib = load_host()
     img = np.ascontiguousarray(rgb8, dtype=np.uint8)
     if img.ndim != 3 or img.shape[2] != 3:
         raise ValueError("encode_png: expected uint8 [H, W, 3]")
@@ -313,7 +366,7 @@ def encode_png(rgb8: np.ndarray, counters: bool = False) -> bytes:
 
 
 def camera_init(cfg: RthCameraConfig, depth_camera: bool = False, counters: bool = False) -> RtbCamera:
-    lib = load(counters)
+    lib = load_host()
     cam = RtbCamera()
     _check(lib, lib.rth_camera_init(C.byref(cfg), int(depth_camera), C.byref(cam)), host=True)
     return cam

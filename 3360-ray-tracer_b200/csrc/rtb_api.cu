@@ -44,6 +44,24 @@ int EnsureInit() {
   return rtb_init(0);
 }
 
+// cudaEvent_t owner: every early return (RTB_CUDA) destroys what was created so far
+struct Events {
+  std::vector<cudaEvent_t> all;
+  int Create(cudaEvent_t* e, unsigned flags = cudaEventDefault) {
+    RTB_CUDA(cudaEventCreateWithFlags(e, flags));
+    all.push_back(*e);
+    return RTB_OK;
+  }
+  ~Events() {
+    for (cudaEvent_t e : all) cudaEventDestroy(e);
+  }
+};
+#define RTB_TRY(expr)                 \
+  do {                                \
+    const int rc_ = (expr);           \
+    if (rc_ != RTB_OK) return rc_;    \
+  } while (0)
+
 // Wavefront state, per host thread (= per device), allocated lazily by rtb_render* and kept across
 // scenes and calls.  A Wave is one independent wavefront: its own path pool (two queues), hit
 // arrays, counters and stream.  Several waves are kept in flight so that the drain tail of one
@@ -253,6 +271,15 @@ struct RtbScene {
   }
 };
 
+// The library's state (stream, pools, accumulator) is per host thread = per device, so a scene is used from a thread whose
+// library device (rtb_init) is the one the scene was created on; anything else would launch its device pointers
+// on another GPU's stream.
+static int CheckSceneDevice(const RtbScene* s) {
+  if (s->device == g_device) return RTB_OK;
+  return Fail(RTB_EINVAL, "scene lives on device " + std::to_string(s->device) + " but this thread's library device is " + std::to_string(g_device) +
+                              ": call rtb_init(" + std::to_string(s->device) + ") first");
+}
+
 // RTB_SCENE_DEVICE_BUILD: the pair records of a linear BVH over every primitive, written straight into the scene's
 // arena by the kernels of rtb_build.cuh.  Scratch lives in the stream-ordered pool for the duration of the build.
 __global__ void build_single_kernel(rtb::DevScene s, uint32_t n_s, uint32_t n_t, float* pairs) {
@@ -392,6 +419,8 @@ int rtb_shutdown(void) {
 
 int rtb_scene_destroy(RtbScene* s) {
   if (!s) return RTB_OK;
+  int prev = -1;
+  cudaGetDevice(&prev);
   cudaSetDevice(s->device);
   for (auto t : s->textures)
     if (t) cudaDestroyTextureObject(t);
@@ -401,6 +430,7 @@ int rtb_scene_destroy(RtbScene* s) {
     if (g_stream && g_device == s->device) cudaFreeAsync(s->arena, g_stream);
     else cudaFree(s->arena);
   }
+  if (prev >= 0 && prev != s->device) cudaSetDevice(prev);  // the caller's current device is not ours to change
   delete s;
   return RTB_OK;
 }
@@ -642,6 +672,7 @@ int rtb_intersect_batch_device(RtbScene* s, const RtbRay* d_rays, size_t n, RtbH
   if (n > 0xffffff00ull) return Fail(RTB_EINVAL, "batch too large");
   int rc = EnsureInit();
   if (rc != RTB_OK) return rc;
+  RTB_TRY(CheckSceneDevice(s));
   cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : g_stream;
   RTB_CUDA(cudaMemsetAsync(s->cursor, 0, 8, st));
   const bool use_smem = s->dev.n_top_pairs > 0 && std::getenv("RTB_SMEM_TOP") != nullptr;
@@ -760,6 +791,7 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   if (prm->mode != RTB_MODE_A && prm->mode != RTB_MODE_B) return Fail(RTB_EINVAL, "unknown estimator mode");
   int rc = EnsureInit();
   if (rc != RTB_OK) return rc;
+  RTB_TRY(CheckSceneDevice(s));
   const uint32_t n_pixels = (uint32_t)cam->width * (uint32_t)cam->height;
   uint32_t pool = prm->pool_size ? prm->pool_size : (1u << 21);
   pool = std::min(std::max(pool, 1u << 10), 1u << 28);
@@ -811,10 +843,11 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   const int path_grid = use_smem ? PersistentGrid(fused ? rtb::path_kernel<true, false> : rtb::path_kernel<true, true>, kTraceBlock, ext_smem)
                                  : PersistentGrid(fused ? rtb::path_kernel<false, false> : rtb::path_kernel<false, true>, kTraceBlock, ext_smem);
 
+  Events events;  // destroyed on every return path
   cudaEvent_t ev0, ev1, ev_ready;
-  RTB_CUDA(cudaEventCreate(&ev0));
-  RTB_CUDA(cudaEventCreate(&ev1));
-  RTB_CUDA(cudaEventCreateWithFlags(&ev_ready, cudaEventDisableTiming));
+  RTB_TRY(events.Create(&ev0));
+  RTB_TRY(events.Create(&ev1));
+  RTB_TRY(events.Create(&ev_ready, cudaEventDisableTiming));
   RTB_CUDA(cudaEventRecord(ev0, st));
   if (!(prm->flags & RTB_RENDER_KEEP_ACCUM)) {
     RTB_CUDA(cudaMemsetAsync(d_rgb_sum, 0, (size_t)n_pixels * 3 * sizeof(float), st));
@@ -841,7 +874,7 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> drain_events;  // serial mode: around each drain launch
   cudaEvent_t ek[4] = {nullptr, nullptr, nullptr, nullptr};  // serial mode: before generate / extend / shade, after shade
   if (serial)
-    for (auto& e : ek) RTB_CUDA(cudaEventCreate(&e));
+    for (auto& e : ek) RTB_TRY(events.Create(&e));
   // max_depth == 0: GetPixel returns black without tracing (camera.h:149-151)
   const bool trace = prm->max_depth > 0 || prm->mode == RTB_MODE_B || cam->depth_camera;
   bool any = trace && !fused;
@@ -945,8 +978,8 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
           cudaStream_t ws = w.stream;
           cudaEvent_t d0 = nullptr, d1 = nullptr;
           if (serial) {
-            RTB_CUDA(cudaEventCreate(&d0));
-            RTB_CUDA(cudaEventCreate(&d1));
+            RTB_TRY(events.Create(&d0));
+            RTB_TRY(events.Create(&d1));
             drain_events.emplace_back(d0, d1);
           }
           RTB_CUDA(cudaMemsetAsync(w.counts, 0, 4, ws));
@@ -995,8 +1028,6 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
       any = true;
     }
   }
-  for (auto& e : ek)
-    if (e) cudaEventDestroy(e);
   for (Wave* wp : waves) {
     Wave& w = *wp;  // the library stream joins every wave
     RTB_CUDA(cudaEventRecord(w.done, w.stream));
@@ -1015,14 +1046,9 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
     float d = 0.f;
     cudaEventElapsedTime(&d, de.first, de.second);
     ms_drain += d;
-    cudaEventDestroy(de.first);
-    cudaEventDestroy(de.second);
   }
   float ms = 0.f;
   cudaEventElapsedTime(&ms, ev0, ev1);
-  cudaEventDestroy(ev0);
-  cudaEventDestroy(ev1);
-  cudaEventDestroy(ev_ready);
   if (stats) {
     std::memset(stats, 0, sizeof(*stats));
     stats->samples = generated;

@@ -186,6 +186,10 @@ __device__ __forceinline__ void store_half(float* pair, uint32_t side, const Bui
 }
 
 // One thread per leaf (sorted position k).  pairs: (n-1) x 16 floats, flags: n-1 zeros, depth: one zero.
+// Depth: every arrival leaves the HEIGHT of its subtree in its half's pad word (14 + side) of the pair record; the
+// second arrival carries max(own, sibling) + 1 upward, so the value that reaches the root is the height of the whole
+// tree (the length of one leaf-to-root chain, which is what the first version counted, is the depth of whichever
+// leaf happened to finish last).  The traversal never reads the pad words.
 __global__ void __launch_bounds__(256) build_emit_kernel(const BuildBox* __restrict__ boxes, const uint32_t* __restrict__ order, uint32_t n, uint32_t n_s,
                                                          uint32_t n_t, const uint32_t* __restrict__ parent_internal,
                                                          const uint32_t* __restrict__ parent_leaf, float* pairs, unsigned* flags, unsigned* depth) {
@@ -197,11 +201,12 @@ __global__ void __launch_bounds__(256) build_emit_kernel(const BuildBox* __restr
   BuildBox box = boxes[prim];
   uint32_t desc = kLeafBit | (type << 29) | idx;  // count - 1 = 0
   uint32_t link = parent_leaf[k];
-  unsigned levels = 1;
+  unsigned levels = 0;  // height of the subtree this thread carries (a leaf: 0)
   for (;;) {
     const uint32_t p = link >> 1, side = link & 1u;
     float* pair = pairs + 16 * (size_t)p;
     store_half(pair, side, box, desc);
+    reinterpret_cast<unsigned*>(pair)[14 + side] = levels;
     __threadfence();
     if (atomicAdd(&flags[p], 1u) == 0u) return;  // the sibling subtree is not finished: its last thread carries on
     // second arrival: the other half was written (and fenced) before its atomicAdd
@@ -212,7 +217,7 @@ __global__ void __launch_bounds__(256) build_emit_kernel(const BuildBox* __restr
       box.hi[c] = fmaxf(box.hi[c], __ldcg(o + 2 * c + 1));
     }
     desc = p;
-    ++levels;
+    levels = max(levels, __ldcg(reinterpret_cast<const unsigned*>(pair) + 14 + (side ^ 1u))) + 1u;
     if (p == 0u) break;
     link = parent_internal[p];
   }

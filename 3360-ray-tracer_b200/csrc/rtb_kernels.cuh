@@ -780,12 +780,16 @@ __global__ void __launch_bounds__(256) adaptive_replay_kernel(RenderConsts rc, f
     float* a = accum + 3 * (size_t)pixel;
     float* q2 = ad.sumsq + 3 * (size_t)pixel;
     const uint32_t prev = ad.count[pixel];  // samples of earlier calls (RTB_RENDER_KEEP_ACCUM), written back when the pixel stops
-    float sx = a[0], sy = a[1], sz = a[2], qx = q2[0], qy = q2[1], qz = q2[2];
+    // The fold runs in double, like PixelState (pixel_state.h:13-38 keeps mean / m2 / sum as doubles): in float32 the
+    // variance sumsq - sum * mean carries a relative error of ~u * n, which at the 0.001-0.003 thresholds the reference's
+    // sampler.h suggests for final renders is comparable to threshold^2 and moves per-pixel stop counts.  The planes stay
+    // float32 (they are the stored state, rounded once per pass); the kernel is stream-bound, the doubles cost nothing.
+    double sx = a[0], sy = a[1], sz = a[2], qx = q2[0], qy = q2[1], qz = q2[2];
     const float* c = ad.chunk + 3 * (size_t)slot * ad.chunk_r;
     bool stop = false;
     uint32_t k = 0;
     while (k < ad.chunk_r && !stop) {
-      const float lx = c[3 * k], ly = c[3 * k + 1], lz = c[3 * k + 2];
+      const double lx = c[3 * k], ly = c[3 * k + 1], lz = c[3 * k + 2];
       ++k;
       sx += lx; sy += ly; sz += lz;
       qx += lx * lx; qy += ly * ly; qz += lz * lz;
@@ -793,27 +797,27 @@ __global__ void __launch_bounds__(256) adaptive_replay_kernel(RenderConsts rc, f
       const uint32_t total = prev + mine;
       stop = (int)mine >= rc.spp_max;
       if (!stop && (int)total >= rc.min_samples) {
-        const float n = (float)total, inv_n = 1.0f / n;
-        const float mx = sx * inv_n, my = sy * inv_n, mz = sz * inv_n;
+        const double n = (double)total, inv_n = 1.0 / n;
+        const double mx = sx * inv_n, my = sy * inv_n, mz = sz * inv_n;
+        const double thr = (double)rc.rel_threshold;
         if (rc.criterion == RTB_ADAPT_PIXEL_STATE) {
           // per channel: sqrt(s^2 / n) / max(|mean|, 1e-3) <= threshold, s^2 the sample variance m2 / (n - 1)
-          const float inv_n1 = 1.0f / fmaxf(n - 1.0f, 1.0f);
-          const float vx = fmaxf(qx - sx * mx, 0.0f) * inv_n1, vy = fmaxf(qy - sy * my, 0.0f) * inv_n1, vz = fmaxf(qz - sz * mz, 0.0f) * inv_n1;
-          const float tx = rc.rel_threshold * fmaxf(fabsf(mx), 1e-3f), ty = rc.rel_threshold * fmaxf(fabsf(my), 1e-3f),
-                      tz = rc.rel_threshold * fmaxf(fabsf(mz), 1e-3f);
+          const double inv_n1 = 1.0 / fmax(n - 1.0, 1.0);
+          const double vx = fmax(qx - sx * mx, 0.0) * inv_n1, vy = fmax(qy - sy * my, 0.0) * inv_n1, vz = fmax(qz - sz * mz, 0.0) * inv_n1;
+          const double tx = thr * fmax(fabs(mx), 1e-3), ty = thr * fmax(fabs(my), 1e-3), tz = thr * fmax(fabs(mz), 1e-3);
           stop = vx * inv_n <= tx * tx && vy * inv_n <= ty * ty && vz * inv_n <= tz * tz;
         } else {
           // AdaptiveSampler (sampler.h:61-71) with the running-total slip repaired: luminance of the population
           // variance against the mean luminance
-          const float vx = qx * inv_n - mx * mx, vy = qy * inv_n - my * my, vz = qz * inv_n - mz * mz;
-          const float lum_v = fmaxf(0.2126f * vx + 0.7152f * vy + 0.0722f * vz, 0.0f);
-          const float lum_m = 0.2126f * mx + 0.7152f * my + 0.0722f * mz;
-          stop = sqrtf(lum_v * inv_n) < rc.rel_threshold * (lum_m + 1e-3f);
+          const double vx = qx * inv_n - mx * mx, vy = qy * inv_n - my * my, vz = qz * inv_n - mz * mz;
+          const double lum_v = fmax(0.2126 * vx + 0.7152 * vy + 0.0722 * vz, 0.0);
+          const double lum_m = 0.2126 * mx + 0.7152 * my + 0.0722 * mz;
+          stop = sqrt(lum_v * inv_n) < thr * (lum_m + 1e-3);
         }
       }
     }
-    a[0] = sx; a[1] = sy; a[2] = sz;
-    q2[0] = qx; q2[1] = qy; q2[2] = qz;
+    a[0] = (float)sx; a[1] = (float)sy; a[2] = (float)sz;
+    q2[0] = (float)qx; q2[1] = (float)qy; q2[2] = (float)qz;
     if (stop) ad.count[pixel] = prev + ad.base + k;
     carry_on = !stop;
   }

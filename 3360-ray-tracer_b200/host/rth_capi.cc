@@ -1,6 +1,8 @@
 // rth_* — C wrappers over the host C++ scene API so that the Python tests / bench can build the
 // named scenes, flatten them to an RtbSceneDesc and export them for the oracle.  Declared in
-// include/rth.h.  Pure host code: no CUDA in this translation unit.
+// include/rth.h.  Pure host code: no CUDA in this translation unit, and librth.so does not link librtb200.so — the
+// device library's tree compiler reaches it through rth_set_tree_compiler (so a process that only needs the host scene
+// API, e.g. bench.py --impl reference feeding the oracle, never maps the CUDA library).
 #include <rth.h>
 
 #include <cstring>
@@ -15,13 +17,22 @@
 
 using namespace rt;
 
+namespace {
+RthTreeCompileFn g_compile = nullptr;
+RthTreeDestroyFn g_destroy = nullptr;
+RthLastErrorFn g_compile_error = nullptr;
+}  // namespace
+
 struct RthScene {
   b200::BuiltScene built;
   b200::FlatScene flat;
   RtbSceneDesc desc;
   RtbCompiledTree* tree = nullptr;  // device-native traversal tree, built once with the scene (host work)
   std::string image_paths;  // '\n'-joined
-  ~RthScene() { rtb_tree_destroy(tree); }
+  RthTreeDestroyFn destroy = nullptr;  // the destroyer that belongs to the compiler which made `tree`
+  ~RthScene() {
+    if (tree && destroy) destroy(tree);
+  }
 };
 
 namespace {
@@ -39,8 +50,11 @@ void Finish(RthScene& s, uint32_t top_budget, uint32_t flags = 0) {
   } else {
     s.flat = b200::Flattener(top_budget).Run(s.built.world);
     s.desc = s.flat.desc();
-    if (rtb_tree_compile(&s.desc, &s.tree) != RTB_OK) throw std::runtime_error(rtb_last_error());
-    s.desc.compiled = s.tree;
+    if (g_compile) {
+      if (g_compile(&s.desc, &s.tree) != RTB_OK) throw std::runtime_error(g_compile_error ? g_compile_error() : "tree compile failed");
+      s.destroy = g_destroy;
+      s.desc.compiled = s.tree;
+    }
   }
   s.image_paths.clear();
   for (const auto& p : s.flat.image_paths) {
@@ -138,6 +152,12 @@ struct RecordReader {
 extern "C" {
 
 const char* rth_last_error(void) { return g_error.c_str(); }
+
+void rth_set_tree_compiler(RthTreeCompileFn compile, RthTreeDestroyFn destroy, RthLastErrorFn last_error) {
+  g_compile = compile;
+  g_destroy = destroy;
+  g_compile_error = last_error;
+}
 
 int rth_scene_build(const char* name, const double* params, int n_params, const char* asset_dir, uint32_t top_budget,
                     RthScene** out) {

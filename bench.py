@@ -111,7 +111,7 @@ def cpu_reference_leg(rt, cfg_name, budget_s, steps=1, warmup=0):
     from oracle import checker, ref
     cfg = CONFIGS[cfg_name]
     fast = ref.available(fast=True) and _cpu_has("avx2") and _cpu_has("fma")
-    hs = rt.HostScene.build(*cfg["scene"])
+    hs = rt.HostScene.build(*cfg["scene"], host_only=True)  # librth.so alone: the CUDA library is never mapped by this leg
     ora = checker.make_oracle(hs, fast=fast)
     cam_cfg = camera_for(rt, cfg)
     cam = rt.camera_init(cam_cfg)

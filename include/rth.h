@@ -32,6 +32,16 @@ typedef struct RthCameraConfig {
 
 const char* rth_last_error(void);
 
+/* librth.so (this header: host C++ scene API, no CUDA) and librtb200.so (rtb.h: the kernels) are separate libraries.
+ * The host library can hand a freshly built scene to the device library's tree compiler (rtb_tree_compile, host work
+ * done once per scene like the reference's geom::Bvh constructor, src/geom/bvh.h:39-68) if the embedder registers it;
+ * without it RtbSceneDesc.compiled stays NULL and rtb_scene_create compiles the tree itself on every call.
+ * Pass NULLs to unregister.  Scenes built while a compiler was registered must be freed before it is unregistered. */
+typedef int (*RthTreeCompileFn)(const RtbSceneDesc*, RtbCompiledTree**);
+typedef void (*RthTreeDestroyFn)(RtbCompiledTree*);
+typedef const char* (*RthLastErrorFn)(void);
+void rth_set_tree_compiler(RthTreeCompileFn compile, RthTreeDestroyFn destroy, RthLastErrorFn last_error);
+
 /* name: cornell | rtiow | checkered_spheres | earth | earth_bubbles | bunny | stress.
  * params: scene-specific doubles (see rth_capi.cc); asset_dir holds models/ and textures/.
  * top_budget: nodes in the breadth-first prefix (0 = 1024). */

@@ -4,7 +4,7 @@
     python tests/golden/make_golden_pixel_state.py
 
 Output (committed): pixel_state.npz - the generator parameters of 4096 sample sequences (regenerated from the seed by
-`sequences()`, which the tests import) and, for three (threshold, min_spp) settings, the sample count at which the
+`sequences()`, which the tests import) and, for four (threshold, min_spp) settings, the sample count at which the
 reference stopped each of them plus its PixelState::sum and ::m2 there.
 """
 import sys
@@ -15,7 +15,7 @@ import numpy as np
 ROOT = Path(__file__).resolve().parents[2]
 sys.path.insert(0, str(ROOT))
 OUT = Path(__file__).resolve().parent
-SETTINGS = [(0.05, 16), (0.02, 8), (0.1, 32)]
+SETTINGS = [(0.05, 16), (0.02, 8), (0.1, 32), (0.002, 16)]  # the last one: the "final render" thresholds sampler.h suggests
 N_SEQ, LEN, SEED = 4096, 128, 20261104
 
 

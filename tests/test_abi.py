@@ -19,9 +19,26 @@ def test_every_declared_symbol_is_exported(rt):
     names = declared("rtb.h") + declared("rth.h")
     assert len(names) >= 28
     for n in names:
-        assert hasattr(lib, n), f"{n} declared in include/ but not exported by librtb200.so"
+        assert hasattr(lib, n), f"{n} declared in include/ but not exported by librtb200.so / librth.so"
     assert set(rt.binding.RTB_SYMBOLS) == set(declared("rtb.h"))
     assert set(rt.binding.RTH_SYMBOLS) == set(declared("rth.h"))
+
+
+def test_the_two_libraries_are_separate(rt):
+    """librth.so (host scene API) carries no rtb_* entry and needs neither CUDA nor librtb200.so; librtb200.so carries no
+    rth_* entry.  `bench.py --impl reference` builds its scene through librth.so alone."""
+    import subprocess
+    host, cuda = rt.binding.load_host(), rt.load()._cuda
+    for n in declared("rtb.h"):
+        assert not hasattr(host, n), f"librth.so exports {n}"
+    for n in declared("rth.h"):
+        assert not hasattr(cuda, n), f"librtb200.so exports {n}"
+    needed = subprocess.run(["objdump", "-p", str(rt.binding.host_lib_path())], capture_output=True, text=True).stdout
+    assert "cudart" not in needed and "rtb200" not in needed
+    code = ("import sys; sys.path.insert(0, %r); import __graft_entry__ as g; rt = g.load_package(); "
+            "hs = rt.HostScene.build('cornell', host_only=True); assert hs.desc.n_rects == 6 and not hs.desc.compiled; "
+            "import os; m = open('/proc/%%d/maps' %% os.getpid()).read(); assert 'librtb200' not in m and 'libcudart' not in m") % str(ROOT)
+    subprocess.run([__import__("sys").executable, "-c", code], check=True, cwd=ROOT)
 
 
 def test_counters_build_exports_the_same_abi(rt):
@@ -66,6 +83,7 @@ def test_scene_create_rejects_malformed_descriptions(rt):
 def test_missing_library_fails_loudly(rt, monkeypatch, tmp_path):
     monkeypatch.setattr(rt.binding, "PKG_DIR", tmp_path)
     monkeypatch.setattr(rt.binding, "_LIBS", {})
+    monkeypatch.setattr(rt.binding, "_HOST", [])
     with pytest.raises(ImportError):
         rt.binding.load()
 

@@ -29,8 +29,8 @@ def golden_camera(rt, g):
 
 @pytest.mark.parametrize("name", list(SCENES))
 def test_image_within_3_sigma_of_reference(rt, golden_dir, scenes, name):
-    """Per pixel-channel |mu_gpu - mu_ref| <= 3 sqrt(s^2/N_gpu + s^2/N_ref) for >= 99.7 % - slack of the
-    channels, and RMSE <= 1.5 x the reference-vs-reference RMSE at equal spp."""
+    """Per pixel-channel |mu_gpu - mu_ref| <= 3 sqrt(s^2/N_gpu + s^2/N_ref) for >= min(99.7 %, what the reference scores
+    against itself - 0.3) of the channels, and RMSE <= 1.5 x the reference-vs-reference RMSE at equal spp."""
     g = np.load(golden_dir / f"image_{name}.npz")
     cfg, cam = golden_camera(rt, g)
     img, st = scenes[name][1].render(cam, spp=GPU_SPP, max_depth=cfg.max_depth, seed=0x3360)
@@ -38,9 +38,14 @@ def test_image_within_3_sigma_of_reference(rt, golden_dir, scenes, name):
     ref, var, n_ref = g["mean"].astype(np.float64), g["var"].astype(np.float64), int(g["spp"])
     assert mu.shape == ref.shape
     sigma = np.sqrt(var / GPU_SPP + var / n_ref)
-    # variance itself is estimated: give channels with tiny estimated variance an absolute floor
-    ok = np.abs(mu - ref) <= 3 * sigma + 2e-3 * np.maximum(ref, 1.0)
-    assert ok.mean() >= 0.99, f"{name}: only {ok.mean():.4f} of pixel-channels within 3 sigma"
+    # The bar is the reference's own score on the same statistic (its second render, mean_256, against the golden mean):
+    # per-pixel path-tracing samples are not Gaussian and sigma is itself estimated, so the reference reaches 99.58-99.80 %
+    # against itself, not 99.73 %.  The only absolute term covers float32 accumulation on zero-variance channels.
+    floor = 1e-4 * np.maximum(ref, 1.0)
+    ok = np.abs(mu - ref) <= 3 * sigma + floor
+    ok_ref = np.abs(g["mean_256"].astype(np.float64) - ref) <= 3 * sigma + floor
+    print(f"[parity] {name}: 3-sigma fraction gpu-vs-ref {ok.mean():.5f}, ref-vs-ref {ok_ref.mean():.5f}")
+    assert ok.mean() >= min(0.997, ok_ref.mean() - 0.003), f"{name}: {ok.mean():.5f} of pixel-channels within 3 sigma (reference vs itself: {ok_ref.mean():.5f})"
     rmse_gpu = np.sqrt(np.mean((mu - ref) ** 2))
     rmse_ref = np.sqrt(np.mean((g["mean_256"].astype(np.float64) - ref) ** 2))
     assert rmse_gpu <= 1.5 * rmse_ref + 1e-3, f"{name}: RMSE {rmse_gpu:.5f} vs reference-vs-reference {rmse_ref:.5f}"
