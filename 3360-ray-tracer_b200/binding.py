@@ -19,7 +19,7 @@ ASSET_DIR = REPO_ROOT / "assets"
 RTB_OK, RTB_EINVAL, RTB_ENODEVICE, RTB_ECUDA, RTB_ENOMEM = 0, -1, -2, -3, -4
 PRIM_SPHERE, PRIM_TRIANGLE, PRIM_RECT, PRIM_SUBTREE = 0, 1, 2, 3
 MODE_A, MODE_B = 0, 1
-RENDER_SMEM_TOP, RENDER_KEEP_ACCUM, RENDER_SERIAL, RENDER_WAVEFRONT, RENDER_NO_DRAIN = 1, 2, 4, 8, 16
+RENDER_SMEM_TOP, RENDER_KEEP_ACCUM, RENDER_SERIAL, RENDER_WAVEFRONT, RENDER_NO_DRAIN, RENDER_POOL_PATHS = 1, 2, 4, 8, 16, 32
 ADAPT_PIXEL_STATE, ADAPT_LUMINANCE = 0, 1
 EX_SPHERE, EX_TRIANGLE, EX_RECT, EX_BVH_BEGIN, EX_BVH_END, EX_LIST_BEGIN, EX_LIST_END = 0, 1, 2, 10, 11, 12, 13
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_DIFFUSE_LIGHT = 0, 1, 2, 3
@@ -490,13 +490,18 @@ def resolve(rgb_sum: np.ndarray, spp: int, counters: bool = False) -> np.ndarray
     return out
 
 
-def measure_peaks(counters: bool = False) -> dict:
+def measure_peaks(counters: bool = False, l2_mib=(64,)) -> dict:
+    """Roofline denominators measured on this GPU, now: L2 read bandwidth (ld.global.cg sweep of a 64 MiB buffer - inside the
+    126 MB L2, far outside the L1s; other footprints in l2_gbs_by_mib), FP32 and FP64 FMA rates."""
     lib = load(counters)
     l2, f32, f64 = C.c_float(), C.c_float(), C.c_float()
-    _check(lib, lib.rtb_measure_l2_gbs(32 << 20, 50, C.byref(l2)))
+    by = {}
+    for mib in l2_mib:
+        _check(lib, lib.rtb_measure_l2_gbs(int(mib) << 20, 40, C.byref(l2)))
+        by[int(mib)] = l2.value
     _check(lib, lib.rtb_measure_fp32_tflops(20000, C.byref(f32)))
     _check(lib, lib.rtb_measure_fp64_tflops(20000, C.byref(f64)))
-    return {"l2_gbs": l2.value, "fp32_tflops": f32.value, "fp64_tflops": f64.value}
+    return {"l2_gbs": by[int(l2_mib[0])], "l2_gbs_by_mib": by, "fp32_tflops": f32.value, "fp64_tflops": f64.value}
 
 
 def write_ppm(path, rgb8: np.ndarray):

@@ -20,6 +20,7 @@
 #include "rtb_compile.h"
 #include "rtb_build.cuh"
 #include "rtb_kernels.cuh"
+#include "rtb_pool.cuh"
 
 namespace {
 
@@ -844,6 +845,10 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
                                  : PersistentGrid(fused ? rtb::path_kernel<false, false> : rtb::path_kernel<false, true>, kTraceBlock, ext_smem);
 
   Events events;  // destroyed on every return path
+  // on request: the pool kernel (64 paths per warp in shared memory, rtb_pool.cuh) instead of one path per lane
+  const bool use_pool = fused && !use_smem && ((prm->flags & RTB_RENDER_POOL_PATHS) || std::getenv("RTB_POOL_PATHS"));
+  const int pool_grid = use_pool ? PersistentGrid(rtb::pool_kernel<false, false>, kTraceBlock, 0) : 0;
+  const int pool_grid_ad = use_pool && ad ? PersistentGrid(rtb::pool_kernel<false, true>, kTraceBlock, 0) : 0;
   cudaEvent_t ev0, ev1, ev_ready;
   RTB_TRY(events.Create(&ev0));
   RTB_TRY(events.Create(&ev1));
@@ -924,7 +929,10 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
         pl.base = base;
         RTB_CUDA(cudaMemsetAsync(w.counts, 0, 4, w.stream));
         RTB_CUDA(cudaMemsetAsync(cnt + ((pass + 1) & 1), 0, 4, w.stream));
-        if (use_smem)
+        if (use_pool)
+          rtb::pool_kernel<false, true><<<pool_grid_ad, kTraceBlock, 0, w.stream>>>(s->dev, rtb::PathQueue{}, 0u, 0u, 0u, rcst, ctx->pixel_order, d_rgb_sum,
+                                                                                w.counts, rc64, s->counters, pl);
+        else if (use_smem)
           rtb::path_kernel<true, false, true><<<grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, 0u, 0u, 0u, rcst, ctx->pixel_order,
                                                                                      d_rgb_sum, w.counts, rc64, s->counters, pl);
         else
@@ -942,7 +950,10 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
       const uint32_t s0 = (uint32_t)(generated / n_pixels), p0 = (uint32_t)(generated % n_pixels);
       RTB_CUDA(cudaMemsetAsync(w.counts, 0, 4, w.stream));
       auto* rc64 = reinterpret_cast<unsigned long long*>(w.counts + 2);
-      if (use_smem)
+      if (use_pool)
+        rtb::pool_kernel<false, false><<<pool_grid, kTraceBlock, 0, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, ctx->pixel_order, d_rgb_sum,
+                                                                              w.counts, rc64, s->counters, planes);
+      else if (use_smem)
         rtb::path_kernel<true, false><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, ctx->pixel_order,
                                                                                   d_rgb_sum, w.counts, rc64, s->counters, planes);
       else

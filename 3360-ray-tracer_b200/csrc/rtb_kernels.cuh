@@ -923,15 +923,20 @@ __global__ void resolve_counts_kernel(const float* __restrict__ rgb_sum, const u
 }
 
 // ---- roofline denominators ----------------------------------------------------------------------
-// L2-resident 128-bit read sweep.
+// L2-resident 128-bit read sweep that cannot be served by the L1: ld.global.cg caches at L2 only, and the block -> address
+// mapping rotates every iteration so that no SM re-reads the addresses it touched last time (the first version
+// re-read 221 KB per SM with __ldg, which fits the 256 KB L1 - its 26 TB/s was partly an L1 number).
 __global__ void l2_read_kernel(const float4* __restrict__ buf, size_t n4, int iters, float* sink) {
   float acc = 0.f;
   const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (int it = 0; it < iters; ++it)
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += stride) {
-      const float4 v = __ldg(&buf[i]);
+  for (int it = 0; it < iters; ++it) {
+    const size_t b = (blockIdx.x + (size_t)it * 37u) % gridDim.x;
+    for (size_t i = b * blockDim.x + threadIdx.x; i < n4; i += stride) {
+      float4 v;
+      asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(buf + i));
       acc += v.x + v.y + v.z + v.w;
     }
+  }
   if (acc == 123.456f) *sink = acc;
 }
 __global__ void fp32_fma_kernel(int iters, float* sink) {

@@ -5,16 +5,24 @@ reference's CPU path, with the extend kernel's roofline.  Contract: see DESIGN.m
   python bench.py [--gpus N] [--steps K] [--warmup W] [--config bunny|rtiow|cornell|earth|stress] [--impl reference]
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
 
-A "step" is one complete render of the named configuration (all pixels x spp x bounces).  At N>1
-every rank renders the configuration's spp with its own slice of GLOBAL sample indices
-(rank k: [k*spp,(k+1)*spp)), scene replicated, and the float32 radiance accumulators are summed
-onto rank 0 with one NCCL reduce; per-GPU work is fixed, so scaling is "weak".
+A "step" is one complete render of the named configuration (all pixels x spp x bounces).  At N>1 the
+configuration's spp is SPLIT: rank k renders the slice multigpu.spp_slice(spp, k, N) of the global sample
+indices of every pixel (scene replicated, no data-path collective), the float32 radiance accumulators are
+summed onto rank 0 with one NCCL reduce and resolved there - one image of the configuration's spp, as the
+reference renders it (src/integrator/sampler.h:26-34) - so the total work is fixed and scaling is "strong".
+The weak figure (every rank renders the full spp: N x the samples) is measured too and reported under "weak".
 """
 from __future__ import annotations
 
 import argparse
 import json
 import os
+
+# The CPU legs (oracle/_ref: the reference's OpenMP pixel loop) wandered between 6.5 and 9.3 Msamples/s for the same render
+# in round 1 (threads migrating between cores, a cold first pass): pin them before libgomp reads its environment.
+HOST_CORES = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)  # before libgomp binds this thread to one place
+os.environ.setdefault("OMP_PROC_BIND", "close")
+os.environ.setdefault("OMP_PLACES", "cores")
 import subprocess
 import sys
 import threading
@@ -117,7 +125,7 @@ def cpu_reference_leg(rt, cfg_name, budget_s, steps=1, warmup=0):
     cam = rt.camera_init(cam_cfg)
     # every host thread this process may use: torchrun exports OMP_NUM_THREADS=1 to its workers, which would silently
     # turn the "all-core" reference into a single-thread run, so the count is passed to omp_set_num_threads explicitly
-    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    cores = HOST_CORES
     # calibrate with whole-image passes at 1 and 2 spp (the first also warms the thread pool), then size
     # the sample to the budget: samples/s is spp-invariant
     ora.render_a(cam_cfg.as_oracle_cfg(), 1, cfg["depth"], seed=1, want_m2=False, threads=cores)
@@ -131,10 +139,22 @@ def cpu_reference_leg(rt, cfg_name, budget_s, steps=1, warmup=0):
         if k >= warmup:
             out.append((cam.width * cam.height * this_spp, rays, secs))
     samples = sum(o[0] for o in out); rays = sum(o[1] for o in out); secs = sum(o[2] for o in out)
-    return {"value": samples / secs / 1e6, "unit": "Msamples/s", "mrays_per_s": rays / secs / 1e6, "cores": cores,
+    host = {"nproc": os.cpu_count(), "affinity": cores, "cpu_model": _cpu_model(), "omp_proc_bind": os.environ.get("OMP_PROC_BIND"),
+            "omp_places": os.environ.get("OMP_PLACES"), "warm_passes": 2 + warmup}
+    return {"value": samples / secs / 1e6, "unit": "Msamples/s", "mrays_per_s": rays / secs / 1e6, "cores": cores, "host": host,
             "kind": ora.kind, "build": "-O3 -mavx2 -mfma -fopenmp" if fast else "-O2 -fopenmp (strict IEEE)",
             "sample": f"{cfg_name} {cam.width}x{cam.height} at {spp} of {cfg['spp']} spp, maxDepth {cfg['depth']}, estimator A, "
                       f"{len(out)} pass(es), {secs:.1f} s", "seconds": secs, "ms_per_step": 1e3 * secs / max(1, len(out))}
+
+
+def _cpu_model():
+    try:
+        for line in Path("/proc/cpuinfo").read_text().split("\n"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
 
 
 def _cpu_has(flag):
@@ -179,10 +199,10 @@ def main():
         per_step = min(12.0, 150.0 / (K + W))
         leg = cpu_reference_leg(rt, args.config, per_step, steps=K, warmup=W)
         line = {"metric": "msamples_per_s", "value": leg["value"], "unit": "Msamples/s", "n_gpus": args.gpus, "steps": K, "warmup": W,
-                "ms_per_step": leg["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                "ms_per_step": leg["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic", "impl": "reference", "mrays_per_s": leg["mrays_per_s"],
                 "config": {"workload": cfg["label"], "estimator": "A (MegaKernel + DefaultSampler + Camera::GetPixel)", "sample": leg["sample"]},
-                "cpu_baseline": {k: leg[k] for k in ("value", "unit", "cores", "kind", "sample", "build")},
+                "cpu_baseline": {k: leg[k] for k in ("value", "unit", "cores", "kind", "sample", "build", "host")},
                 "e2e": {"value": leg["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
         print(json.dumps(line), flush=True)
@@ -220,20 +240,21 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step(flags=None):
+    def step(flags=None, weak=False):
+        """one render of the configuration (this rank's slice of its spp) + reduce + resolve; returns (device ms, stats, reduce ms)"""
         flags = base_flags if flags is None else flags
-        """one render of the configuration at this rank + reduce + resolve; returns (device ms, stats)"""
-        b_, e_ = rt.multigpu.weak_slice(spp, rank)
+        b_, e_ = rt.multigpu.weak_slice(spp, rank) if weak else rt.multigpu.spp_slice(spp, rank, world)
         st = ds.render_device(cam, accum.data_ptr(), b_, e_, depth, mode=mode, pool_size=args.pool, flags=flags)  # synchronous
         with torch.cuda.stream(tstream):
             ev[0].record(tstream)
             if world > 1:
                 dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
             if rank == 0:
-                rt.binding._check(lib, lib.rtb_resolve_device(accum.data_ptr(), n_pix, spp * world, rgb8.data_ptr(), tstream.cuda_stream))
+                rt.binding._check(lib, lib.rtb_resolve_device(accum.data_ptr(), n_pix, spp * world if weak else spp, rgb8.data_ptr(), tstream.cuda_stream))
             ev[1].record(tstream)
         torch.cuda.synchronize()
-        return st["ms_total"] + ev[0].elapsed_time(ev[1]), st
+        tail = ev[0].elapsed_time(ev[1])
+        return st["ms_total"] + tail, st, tail
 
     clocks = ClockSampler(local_rank)
     if rank == 0:
@@ -242,16 +263,17 @@ def main():
         flush.fill_(1)
         barrier()
         step()
-    dev_ms, wall_ms, stats = [], [], []
+    dev_ms, wall_ms, stats, reduce_ms = [], [], [], []
     t_region = time.perf_counter()
     for _ in range(K):
         flush.fill_(1)  # evict the scene and the path pool from L2 between timed steps (untimed)
         barrier()
         t0 = time.perf_counter()
-        ms, st = step()
+        ms, st, red = step()
         wall_ms.append(1e3 * (time.perf_counter() - t0))
         dev_ms.append(ms)
         stats.append(st)
+        reduce_ms.append(red)
     barrier()
     clocks.window = (t_region, time.perf_counter())
     clk = clocks.stop() if rank == 0 else None
@@ -268,9 +290,22 @@ def main():
     for k in range(1 + min(K, 5)):
         flush.fill_(1)
         barrier()
-        ms_o, _ = step(other_flags)
+        ms_o = step(other_flags)[0]
         if k:
             other_ms.append(ms_o)
+    # weak scaling for the record: every rank renders the configuration's full spp (N x the samples, one reduce)
+    weak_ms, weak_samples = [], 0
+    if world > 1:
+        for k in range(1 + min(K, 5)):
+            flush.fill_(1)
+            barrier()
+            ms_w, st_w, _ = step(weak=True)
+            if k:
+                weak_ms.append(ms_w)
+        wk = torch.tensor([sum(weak_ms)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(wk, op=dist.ReduceOp.MAX)
+        weak_ms = wk.item() / max(1, min(K, 5))
+        weak_samples = sum_over_ranks(dist, world, st_w["samples"])
     # max over ranks of the K-step time
     tot = torch.tensor([sum(dev_ms), sum(wall_ms)], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -298,7 +333,8 @@ def main():
             s2 = rt.binding.RtbStats()
             rt.binding._check(lib, lib.rtb_render(ds2._h, C.byref(cam), C.byref(prm), host_img.data_ptr(), C.byref(s2)))
         else:
-            ds2.render_device(cam, accum.data_ptr(), rank * spp, (rank + 1) * spp, depth, mode=mode, pool_size=args.pool, flags=base_flags)
+            b_, e_ = rt.multigpu.spp_slice(spp, rank, world)
+            ds2.render_device(cam, accum.data_ptr(), b_, e_, depth, mode=mode, pool_size=args.pool, flags=base_flags)
             dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
             if rank == 0:
                 host_img.copy_(accum, non_blocking=False)
@@ -318,14 +354,15 @@ def main():
         value = samples_per_step / (ms_per_step * 1e-3) / 1e6
         line = {
             "metric": "msamples_per_s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": K, "warmup": W,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32 shading / f64 exact hit replay", "data": "synthetic", "impl": "b200",
             "mrays_per_s": rays_per_step / (ms_per_step * 1e-3) / 1e6,
             "wall_ms_per_step": total_wall_ms / K,
             "config": {"workload": cfg["label"] + ("" if not (args.spp or args.width) else f" [OVERRIDDEN: width {cam.width}, spp {spp}]"),
                        "why_this_config": "north_star quotes its headline target (>=100x CPU, traversal roofline) on the bunny mesh scene",
-                       "image": [cam.width, cam.height], "spp_per_gpu": spp, "spp_total": spp * world, "max_depth": depth,
-                       "estimator": args.mode, "parallelism": f"spp-split x{world}, scene replicated, 1 NCCL reduce(sum,f32) of {n_pix * 12} B",
+                       "image": [cam.width, cam.height], "spp_total": spp, "spp_per_gpu": [list(rt.multigpu.spp_slice(spp, r, world)) for r in range(world)],
+                       "max_depth": depth, "estimator": args.mode,
+                       "parallelism": f"spp SPLIT x{world} (one image of {spp} spp), scene replicated, 1 NCCL reduce(sum,f32) of {n_pix * 12} B onto rank 0, resolve there",
                        "l2": "384 MiB buffer written between timed steps (L2 flushed); scene itself is L2-resident by design",
                        "pipeline": "persistent path kernel (generate + traverse + shade per lane, one launch per step)" if args.pipeline == "path"
                        else f"wavefront: generate / extend / shade+compact over queues, pool {args.pool or (1 << 21)} paths x {os.environ.get('RTB_WAVES', '4')} wavefronts in flight",
@@ -339,6 +376,9 @@ def main():
             "gpu_launches": int(sum(s["launches"] for s in stats) + K),
             "other_pipeline": {"name": "path" if args.pipeline == "wavefront" else "wavefront", "ms_per_step": float(np.mean(other_ms)),
                                "msamples_per_s": stats[-1]["samples"] / float(np.mean(other_ms)) / 1e3},
+            "reduce_and_resolve_ms_rank0": float(np.mean(reduce_ms)),
+            "weak": None if world == 1 else {"what": f"every rank renders the full {spp} spp ({world}x the samples), one reduce", "ms_per_step": weak_ms,
+                                              "msamples_per_s": weak_samples / (weak_ms * 1e-3) / 1e6, "spp_total": spp * world},
             "clocks": clk,
             "kernel_ms_per_step": {"path_kernel": float(np.mean([s["ms_total"] for s in stats])) if args.pipeline == "path" else None,
                                    "wavefront_serial": {k: float(np.mean([s[k] for s in serial_stats])) for k in ("ms_generate", "ms_extend", "ms_shade", "ms_drain", "ms_total")},
@@ -351,7 +391,7 @@ def main():
             line["roofline"] = {"note": "measured at N=1 only (one process, one GPU)"}
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = {k: v for k, v in cpu_reference_leg(rt, args.config, args.cpu_budget).items()
-                                    if k in ("value", "unit", "cores", "kind", "sample", "build", "mrays_per_s")}
+                                    if k in ("value", "unit", "cores", "kind", "sample", "build", "mrays_per_s", "host")}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

@@ -28,6 +28,8 @@ def _load(fast: bool):
     lib.ora_intersect.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int]
     lib.ora_intersect_world.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int]
     lib.ora_intersect_world.restype = C.c_double
+    lib.ora_intersect_records.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int]
+    lib.ora_intersect_records.restype = None
     lib.ora_bvh_count.argtypes = [C.c_void_p]
     lib.ora_bvh_size.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
     lib.ora_bvh_dump.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
@@ -86,6 +88,13 @@ class RefScene:
         h = np.zeros(r.shape[0], np.uint8)
         secs = self.lib.ora_intersect_world(self.h, _p(r), r.shape[0], _p(t), _p(h), threads)
         return t, h.astype(bool), secs
+
+    def intersect_records(self, rays: np.ndarray, threads: int = 0) -> np.ndarray:
+        """The reference's HitRecord per ray over (0.001f, inf): [n, 13] = hit, t, p, normal, front_face, u, v, id, has_mat."""
+        r = np.ascontiguousarray(rays).view(np.float32).reshape(-1, 8)
+        out = np.zeros((r.shape[0], 13), np.float64)
+        self.lib.ora_intersect_records(self.h, _p(r), r.shape[0], _p(out), threads)
+        return out
 
     def bvh_count(self) -> int:
         return self.lib.ora_bvh_count(self.h)

@@ -246,6 +246,32 @@ void ora_intersect(void* h, const float* rays, size_t n, double* t_out, int32_t*
   }
 }
 
+// The whole HitRecord the reference fills (hittable.h:18-34; sphere.h:44-51, triangle.h:78-84, rect.h:26-38) for the
+// closest hit of each ray over (0.001f, +inf), the interval CPURayIntegrator::IntersectBatch uses
+// (cpu_ray_integrator.h:21-22): out13 = {hit, t, p[3], normal[3], front_face, u, v, id, has_mat}.
+void ora_intersect_records(void* h, const float* rays, size_t n, double* out13, int threads) {
+  const OraScene& s = *static_cast<OraScene*>(h);
+  if (threads > 0) omp_set_num_threads(threads);
+#pragma omp parallel for schedule(dynamic, 1024)
+  for (size_t i = 0; i < n; ++i) {
+    const float* f = rays + 8 * i;
+    geom::HitRecord rec;
+    int id = -1;
+    const bool ok = HitId(s, &s.world, MakeRay(f), core::Interval(0.001f, core::kInfinity), rec, id);
+    double* o = out13 + 13 * i;
+    for (int k = 0; k < 13; ++k) o[k] = 0.0;
+    o[0] = ok;
+    if (!ok) continue;
+    o[1] = rec.t;
+    for (int c = 0; c < 3; ++c) { o[2 + c] = rec.p[c]; o[5 + c] = rec.normal[c]; }
+    o[8] = rec.front_face;
+    o[9] = rec.u;
+    o[10] = rec.v;
+    o[11] = id;
+    o[12] = rec.mat != nullptr;
+  }
+}
+
 // The reference's own entry (scene::Scene::Hit -> Bvh::Hit), no ids: validates ora_intersect.
 // Also what CPURayIntegrator::IntersectBatch does per ray (cpu_ray_integrator.h:25-44).
 double ora_intersect_world(void* h, const float* rays, size_t n, double* t_out, uint8_t* hit_out, int threads) {

@@ -88,3 +88,70 @@ def test_device_build_rejects_too_many_primitives(rt):
     d.n_triangles = (1 << 24) + 1
     h = C.c_void_p()
     assert lib.rtb_scene_create(C.byref(d), C.byref(h)) == rt.RTB_EINVAL
+
+
+def _morton_chain_scene(rt, axes, n_dup):
+    """Spheres whose Morton keys have ONE bit set each (centre E * 2^-i on one axis, i = 1..21, with a far corner fixing the
+    extent), plus n_dup coincident spheres at the origin: the linear BVH over them is a chain, one level per key bit
+    (the depth guard must see the HEIGHT of the tree, not the length of whichever leaf chain finished last)."""
+    R = helpers.Records()
+    m = R.lambertian(0.5, 0.5, 0.5)
+    E = float(2 ** 21)
+    R.begin(helpers.EX_BVH_BEGIN)
+    R.sphere((E, E, E), 0.25, m)
+    for axis in axes:
+        for i in range(1, 22):
+            c = [0.0, 0.0, 0.0]
+            c[axis] = E * 2.0 ** -i
+            R.sphere(c, 0.25, m)
+    for _ in range(n_dup):
+        R.sphere((0.0, 0.0, 0.0), 0.25, m)
+    R.end(helpers.EX_BVH_END)
+    return rt.HostScene.from_records(*R.arrays())
+
+
+def _as_device_build(rt, hs):
+    d = rt.binding.RtbSceneDesc.from_buffer_copy(hs.desc)
+    d.flags |= 1  # RTB_SCENE_DEVICE_BUILD: the tree comes from the primitive tables alone
+    d.compiled, d.nodes, d.prim_refs, d.n_nodes, d.n_prim_refs, d.n_top_nodes = None, None, None, 0, 0, 0
+    return d
+
+
+def test_device_build_measures_the_height_of_a_degenerate_tree(rt):
+    """63 single-bit keys + 64 coincident centres: a chain deeper than the 64-entry traversal stack (bvh.h:80) must be
+    refused, every time (the first version reported the depth of one arbitrary leaf and let such trees through)."""
+    lib = rt.load()
+    hs = _morton_chain_scene(rt, (0, 1, 2), 64)
+    d = _as_device_build(rt, hs)
+    for _ in range(5):
+        h = C.c_void_p()
+        assert lib.rtb_scene_create(C.byref(d), C.byref(h)) == rt.RTB_EINVAL
+        assert b"deeper than the 64-entry" in lib.rtb_last_error()
+
+
+def test_deep_but_legal_device_tree_traces_like_the_host_tree(rt):
+    """Two axes: a 40-odd level chain, inside the stack bound; hits equal the host-built tree's."""
+    lib = rt.load()
+    hs = _morton_chain_scene(rt, (0, 1), 4)
+    d = _as_device_build(rt, hs)
+    h = C.c_void_p()
+    assert lib.rtb_scene_create(C.byref(d), C.byref(h)) == rt.RTB_OK, lib.rtb_last_error()
+    host = rt.DeviceScene(hs)
+    rng = np.random.default_rng(9)
+    n = 20000
+    rays = np.zeros(n, rt.RAY_DTYPE)
+    E = float(2 ** 21)
+    targets = np.concatenate([[[E, E, E], [0, 0, 0]], [[E * 2.0 ** -i, 0, 0] for i in range(1, 22)], [[0, E * 2.0 ** -i, 0] for i in range(1, 22)]])
+    tgt = targets[rng.integers(0, len(targets), n)]
+    rays["o"] = (tgt + rng.normal(size=(n, 3)) * 3 + np.array([0, 0, 40.0])).astype(np.float32)
+    rays["d"] = (tgt + rng.normal(size=(n, 3)) * 0.2 - rays["o"]).astype(np.float32)
+    rays["tmin"], rays["tmax"] = 0.001, np.inf
+    a = host.intersect(rays)
+    b = np.zeros(n, rt.HIT_DTYPE)
+    rt.binding._check(lib, lib.rtb_intersect_batch(h, rays.ctypes.data_as(C.c_void_p), n, b.ctypes.data_as(C.c_void_p)))
+    lib.rtb_scene_destroy(h)
+    assert (a["prim_id"] >= 0).mean() > 0.05
+    # coincident spheres tie exactly: the host tree breaks the tie by the reference's slot order, the device tree by creation order
+    same = a["prim_id"] == b["prim_id"]
+    tie = ~same & (a["t"] == b["t"]) & (a["prim_id"] >= 0) & (b["prim_id"] >= 0)
+    assert (same | tie).all() and np.array_equal(a["t"], b["t"])

@@ -142,7 +142,7 @@ def test_mode_b_renders_and_is_unbiased_on_diffuse_scene(rt, scenes, golden_dir)
 @pytest.mark.parametrize("name", list(SCENES))
 @pytest.mark.parametrize("mode", ["A", "B"])
 def test_wavefront_and_path_kernel_render_the_same_paths(rt, golden_dir, scenes, name, mode):
-    """The default persistent path kernel and the wavefront pipeline (RTB_RENDER_WAVEFRONT: generate /
+    """The default persistent path kernel, the pool kernel (csrc/rtb_pool.cuh) and the wavefront pipeline (RTB_RENDER_WAVEFRONT: generate /
     extend / shade+compact over queues, with and without the drain) follow the SAME paths - Philox keys
     are (pixel, sample, bounce) - so ray counts are identical and images differ only by the order of the
     float atomics."""
@@ -154,6 +154,9 @@ def test_wavefront_and_path_kernel_render_the_same_paths(rt, golden_dir, scenes,
     wave, sw = ds.render(cam, spp=32, max_depth=cfg.max_depth, mode=m, flags=rt.RENDER_WAVEFRONT, pool_size=1 << 16)
     nodrain, sn = ds.render(cam, spp=32, max_depth=cfg.max_depth, mode=m, flags=rt.RENDER_WAVEFRONT | rt.RENDER_NO_DRAIN, pool_size=1 << 16)
     serial, ss = ds.render(cam, spp=32, max_depth=cfg.max_depth, mode=m, flags=rt.RENDER_SERIAL, pool_size=1 << 16)
+    lane, sl = ds.render(cam, spp=32, max_depth=cfg.max_depth, mode=m, flags=rt.RENDER_POOL_PATHS)  # the pool kernel: 64 paths per warp in shared memory
+    assert sl["rays"] == sf["rays"] and sl["launches"] == sf["launches"] == 1
+    assert np.abs(lane - fused).max() <= 1e-5 * max(1.0, float(fused.max()))
     assert sf["rays"] == sw["rays"] == sn["rays"] == ss["rays"] and sf["samples"] == sw["samples"] == cam.width * cam.height * 32
     assert sf["launches"] < sw["launches"] < sn["launches"] and sw["drain_paths"] > 0 and sn["drain_paths"] == 0
     scale = max(1.0, float(fused.max()))

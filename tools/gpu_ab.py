@@ -1,0 +1,58 @@
+"""A/B harness for the render kernels: every BASELINE config (stress at reduced spp) with the default pool kernel and the
+round-1 lane-path kernel, for each library given (make VARIANT=x EXTRA=-D... builds librtb200_x.so).
+  python tools/gpu_ab.py [--configs bunny,rtiow,...] [--stress-spp 4] [librtb200.so librtb200_v1.so ...]
+Each library runs in its own process (RTB_LIB).  Prints one JSON line per (library, config, kernel)."""
+import json, os, subprocess, sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def one(names, stress_spp):
+    sys.path.insert(0, str(ROOT))
+    import numpy as np
+    import bench
+    import __graft_entry__ as g
+    m = g.load_package()
+    for name in names:
+        cfg = bench.CONFIGS[name]
+        dev_tree = name == "stress"
+        ds = m.DeviceScene(m.HostScene.build(*cfg["scene"], device_tree=dev_tree))
+        cam = m.camera_init(bench.camera_for(m, cfg))
+        spp = stress_spp if name == "stress" else cfg["spp"]
+        imgs = {}
+        for label, flags in (("pool", m.RENDER_POOL_PATHS), ("lane", 0)):
+            for mode, mname in ((m.MODE_A, "A"),) + (((m.MODE_B, "B"),) if os.environ.get("AB_MODE_B") else ()):
+                ts = []
+                for rep in range(5):
+                    img, st = ds.render(cam, spp=spp, max_depth=cfg["depth"], flags=flags, mode=mode)
+                    ts.append(st["ms_total"])
+                t = float(np.median(ts[1:]))
+                imgs[(label, mname)] = img
+                print(json.dumps({"lib": os.environ.get("RTB_LIB", "librtb200.so"), "config": name, "kernel": label, "mode": mname, "ms": round(t, 3),
+                                  "min_ms": round(min(ts), 3), "msamples_s": round(st["samples"] / t / 1e3, 1), "mrays_s": round(st["rays"] / t / 1e3, 1),
+                                  "rays": st["rays"]}), flush=True)
+        for mname in ("A", "B"):
+            if ("pool", mname) in imgs:
+                a, b = imgs[("pool", mname)], imgs[("lane", mname)]
+                print(json.dumps({"lib": os.environ.get("RTB_LIB", "librtb200.so"), "config": name, "mode": mname,
+                                  "pool_vs_lane_max_rel_diff": float(np.abs(a - b).max() / max(a.max(), 1e-30))}), flush=True)
+        ds.close()
+
+
+if __name__ == "__main__":
+    args = sys.argv[1:]
+    names, stress_spp = ["rtiow", "cornell", "bunny", "earth", "stress"], 4
+    if "--configs" in args:
+        i = args.index("--configs"); names = args[i + 1].split(","); del args[i:i + 2]
+    if "--stress-spp" in args:
+        i = args.index("--stress-spp"); stress_spp = int(args[i + 1]); del args[i:i + 2]
+    if args and args[0] == "--one":
+        one(names, stress_spp)
+    else:
+        for lib in args or ["librtb200.so"]:
+            r = subprocess.run([sys.executable, __file__, "--configs", ",".join(names), "--stress-spp", str(stress_spp), "--one"],
+                               env=dict(os.environ, RTB_LIB=lib), capture_output=True, text=True)
+            print(r.stdout.strip() or ("FAILED " + lib + ": " + r.stderr[-600:]), flush=True)
+            if r.returncode:
+                print("FAILED " + lib + ": " + r.stderr[-600:], flush=True)
