@@ -104,7 +104,7 @@ assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 16
 
 # Every symbol include/rtb.h and include/rth.h declare (checked by tests/test_abi.py).
 RTB_SYMBOLS = [
-    "rtb_last_error", "rtb_abi_version", "rtb_tree_compile", "rtb_tree_destroy", "rtb_device_count", "rtb_init", "rtb_shutdown", "rtb_scene_create",
+    "rtb_last_error", "rtb_abi_version", "rtb_tree_compile", "rtb_tree_destroy", "rtb_device_count", "rtb_debug_check_failures", "rtb_init", "rtb_shutdown", "rtb_scene_create",
     "rtb_scene_destroy", "rtb_intersect_batch", "rtb_intersect_batch_device", "rtb_render", "rtb_render_device",
     "rtb_render_adaptive", "rtb_render_adaptive_device", "rtb_resolve_counts", "rtb_resolve_counts_device", "rtb_pixel_state_fold", "rtb_render_multi",
     "rtb_resolve_device", "rtb_resolve", "rtb_measure_l2_gbs", "rtb_measure_fp32_tflops", "rtb_measure_fp64_tflops",
@@ -209,6 +209,7 @@ def load(counters: bool = False) -> "_Product":
     lib.rtb_measure_fp32_tflops.argtypes = [C.c_int, C.POINTER(C.c_float)]
     lib.rtb_measure_fp64_tflops.argtypes = [C.c_int, C.POINTER(C.c_float)]
     lib.rtb_init.argtypes = [C.c_int]
+    lib.rtb_debug_check_failures.argtypes = [C.c_void_p]
     prod = _Product(host, lib)
     _LIBS[key] = prod
     return prod
@@ -488,6 +489,16 @@ def resolve(rgb_sum: np.ndarray, spp: int, counters: bool = False) -> np.ndarray
     out = np.zeros(a.shape, np.uint8)
     _check(lib, lib.rtb_resolve(_ptr(a), a.size // 3, spp, _ptr(out)))
     return out
+
+
+def check_failures(counters: bool = False):
+    """(is_checked_build, counts[8]) of the library's own bounds checker (rtb_debug_check_failures)."""
+    lib = load(counters)
+    c = np.zeros(8, np.uint64)
+    rc = lib.rtb_debug_check_failures(_ptr(c))
+    if rc < 0:
+        _check(lib, rc)
+    return rc == 1, c
 
 
 def measure_peaks(counters: bool = False, l2_mib=(64,)) -> dict:

@@ -43,7 +43,25 @@ struct DevScene {
   const cudaTextureObject_t* image_tex;  // one per image (0 when the image failed to load)
   const int2* image_dim;
   uint32_t n_pairs, n_top_pairs;
+  uint32_t n_spheres, n_triangles, n_rects, n_materials, n_textures;  // table sizes: only read by the RTB_CHECKED build
 };
+
+// RTB_CHECKED build (make VARIANT=checked EXTRA=-DRTB_CHECKED): every index the kernels form is compared with the size of what
+// it indexes and violations are COUNTED per class in g_check_fail (read by rtb_debug_check_failures), the access itself is
+// clamped.  This is the library's own bounds checker: compute-sanitizer is not available on the B200 pool this was
+// developed on (profiles/r02_checked_build.txt).
+enum { kChkStack, kChkPair, kChkPrim, kChkPixel, kChkMaterial, kChkChunk, kChkPoolSlot, kChkClasses = 8 };
+#ifdef RTB_CHECKED
+__device__ unsigned long long g_check_fail[kChkClasses];
+#define RTB_CHECK(klass, cond)                          \
+  do {                                                  \
+    if (!(cond)) atomicAdd(&rtb::g_check_fail[klass], 1ull); \
+  } while (0)
+#else
+#define RTB_CHECK(klass, cond) \
+  do {                         \
+  } while (0)
+#endif
 
 constexpr uint32_t kNoHit = 0xffffffffu;
 constexpr uint32_t kLeafBit = 0x80000000u;
@@ -489,6 +507,7 @@ __device__ __forceinline__ void consider_exact(const DevScene& s, float ox, floa
 __device__ __forceinline__ void consider(const DevScene& s, const TravRay& r, uint32_t type, uint32_t idx, Best& b, HitCounters* cnt) {
   float t = 0.f, e = 0.f;
   int cls;
+  RTB_CHECK(kChkPrim, idx < (type == RTB_PRIM_TRIANGLE ? s.n_triangles : type == RTB_PRIM_SPHERE ? s.n_spheres : s.n_rects));
   if (type == RTB_PRIM_TRIANGLE) cls = triangle_filter(s, idx, r, b.hi, t, e);
   else if (type == RTB_PRIM_SPHERE) cls = sphere_filter(s, idx, r, b.hi, t, e);
   else cls = rect_filter(s, idx, r, b.hi, t, e);

@@ -21,6 +21,7 @@ struct RenderConsts {
   int mode;
   int spp_begin;
   uint32_t n_pixels;
+  int tile_major;     // host-side note of the work-item order the launch uses (the kernels take it as a template parameter)
   // adaptive rendering (path_kernel<.., kAdaptive = true>): the per-pixel stop of PixelState::IsConverged
   // (pixel_state.h:53-72) or of a repaired AdaptiveSampler (sampler.h:46-76)
   int spp_max;        // samples per pixel this call may add at most
@@ -86,6 +87,8 @@ constexpr int kSmemStack = RTB_SMEM_STACK;
 #endif
 constexpr int kTraceBlock = RTB_TRACE_BLOCK;  // threads per traversal CTA
 constexpr uint32_t kDoneMark = 0xffffffffu;      // `cur` of a lane whose traversal is finished (leaf bit + the unused type 3)
+constexpr uint32_t kIdleMark = 0xfffffffeu;      // `cur` of a lane that holds no ray.  The lane state lives in `cur` alone: a separate
+                                                 // `active` flag was the register ptxas spilled into the node loop (one LDL per node step)
 
 __device__ __forceinline__ float4 ld_pair_generic(unsigned long long addr) {  // shared or global
   float4 v;
@@ -117,6 +120,10 @@ struct TravStack {
   uint32_t* sm;  // this thread's column
   uint32_t deep[kStackSize - kSmemStack];
   __device__ __forceinline__ void push(int sp, uint32_t v) {
+    RTB_CHECK(kChkStack, sp >= 0 && sp < kStackSize);
+#ifdef RTB_CHECKED
+    sp = min(max(sp, 0), kStackSize - 1);
+#endif
     if (kSmemStack > 0 && sp < kSmemStack) sm[sp * kTraceBlock] = v;
     else deep[sp - kSmemStack] = v;
   }
@@ -136,11 +143,10 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
   int sp = 0;
   TravRay r;
   Best b{kNoHit, 0.f, 0.f, 0.f};
-  uint32_t cur = 0, slot = 0;
+  uint32_t cur = kIdleMark, slot = 0;
 #if RTB_POSTPONE_LEAF
   uint32_t post = 0;  // a leaf descriptor waiting for the leaf phase (0 = none: leaf descriptors have bit 31 set)
 #endif
-  bool active = false;
   unsigned pool_next = 0, pool_end = 0;  // warp-uniform: claimed, not yet assigned ray indices
   bool exhausted = false;                 // warp-uniform: the global cursor ran past n
 #ifdef RTB_COUNTERS
@@ -178,6 +184,7 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
 
   // one node step of this lane (both children of pair `cur`, near one first, far one pushed)
   auto node_step = [&]() {
+    RTB_CHECK(kChkPair, cur < s.n_pairs);
     const unsigned long long addr = ((kUseSmem && cur < n_top) ? base_top : base_all) + (unsigned long long)cur * 64ull;
     // record = {box0 box1 desc0 desc1 - -}, box = {lo.x hi.x lo.y hi.y lo.z hi.z}: six 64-bit (lo, hi) pairs
     f32x2 bx[6];
@@ -245,8 +252,8 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
     // ---- service phase: finished lanes hand their hit to the Io (store it, or shade it and maybe
     // continue with the bounced ray), idle lanes take new work from the global cursor.  Runs when
     // enough lanes are waiting for it to be worth a warp-wide pass, or when nobody is tracing.
-    const bool done = active && cur == kDoneMark;
-    const unsigned wait_mask = __ballot_sync(kFull, !active || done);
+    const bool done = cur == kDoneMark;
+    const unsigned wait_mask = __ballot_sync(kFull, cur >= kIdleMark);
     const unsigned done_mask = __ballot_sync(kFull, done);
     const int n_trace = 32 - __popc(wait_mask);
     const bool more = !(exhausted && pool_next == pool_end);
@@ -255,10 +262,9 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
       bool have = false;
       if (done) {
         have = io.finish(slot, b.ref, b.tf, r, o, d);
-        active = have;
-        cur = 0;
+        cur = have ? 0u : kIdleMark;
       }
-      unsigned need = __ballot_sync(kFull, !active);
+      unsigned need = __ballot_sync(kFull, cur == kIdleMark);
       for (int round = 0; round < 2 && need; ++round) {
         if (pool_next == pool_end) {
           if (exhausted) break;
@@ -274,14 +280,14 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
           exhausted = pool_end == io.n;
         }
         const unsigned mine = pool_next + __popc(need & lt_mask);
-        if (!active && mine < pool_end) {
+        if (cur == kIdleMark && mine < pool_end) {
           io.load(mine, o, d);
           slot = mine;
           have = true;
-          active = true;
+          cur = 0u;
         }
         pool_next = min(pool_next + (unsigned)__popc(need), pool_end);
-        need = __ballot_sync(kFull, !active);
+        need = __ballot_sync(kFull, cur == kIdleMark);
       }
       if (have) {
         prepare_ray(r, o, d);
@@ -306,13 +312,13 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
     const int n_act = n_trace;
     // ---- node phase: descend while the descending lanes are the majority
     for (;;) {
-      bool at_node = active && !(cur & kLeafBit);
+      bool at_node = !(cur & kLeafBit);
       const unsigned nm = __ballot_sync(kFull, at_node);
       if (nm == 0u || RTB_NODE_EXIT_DEN * __popc(nm) < RTB_NODE_EXIT_NUM * n_act) break;
 #if RTB_POSTPONE_LEAF
       // speculative traversal (Aila & Laine 2009): the node phase goes on, so a lane standing at a leaf keeps it for the
       // leaf phase and descends from its stack with the others instead of idling; one leaf per lane can wait
-      if (active && !at_node && post == 0u && cur != kDoneMark) {
+      if (!at_node && post == 0u && cur < kIdleMark) {
         post = cur;
         pop_or_finish();
         at_node = !(cur & kLeafBit);
@@ -321,7 +327,7 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
       if (at_node) node_step();
 #pragma unroll
       for (int extra = 1; extra < RTB_NODE_STEPS_PER_VOTE; ++extra)  // more steps on the same vote: less vote overhead
-        if (active && !(cur & kLeafBit)) node_step();
+        if (!(cur & kLeafBit)) node_step();
     }
     // ---- leaf phase, one primitive type at a time (the types are different code, SIMT would serialise
     // them anyway); each lane works through its whole leaf, the descriptor counting down
@@ -335,8 +341,8 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
 #pragma unroll 1
     for (uint32_t type = 0; type < 3; ++type) {
       const uint32_t want = 4u + type;  // leaf bit + type in the top three bits
-      while (__any_sync(kFull, active && (cur >> 29) == want)) {
-        if (active && (cur >> 29) == want) leaf_step(type);
+      while (__any_sync(kFull, (cur >> 29) == want)) {
+        if ((cur >> 29) == want) leaf_step(type);
       }
     }
   }
@@ -456,6 +462,30 @@ __device__ __forceinline__ void generate_sample(const RenderConsts& rc, const ui
   camera_ray(rc, __ldg(&pixel_order[pl]), (uint32_t)rc.spp_begin + s_local, ro, rd, ps);
 }
 
+// Tile-major work-item order of the persistent path kernel.  Sample-major order (above) hands the GPU's ~150 k lanes a
+// window of consecutive PIXELS at one sample index - 40 % of an 800 x 450 image - so every SM walks the whole tree all the
+// time (bunny C3: 54 % L1 hit rate on node fetches; stress C5: 600 MB of DRAM traffic per spp).  Here 32 consecutive
+// items are still one 8 x 4 tile at one sample index (a coherent warp of primary rays, 32 distinct accumulator pixels),
+// but the NEXT 32 items are the same tile's next sample: the window in flight is ~47 tiles x all their samples, one small
+// image region whose part of the tree stays in the L1s and the L2.  A launch covers samples [sa, sa + cnt) of every
+// pixel; item i -> (group of 32 entries of pixel_order, sample, entry in the group); the < 32 pixels left over when
+// n_pixels is not a multiple of 32 come last, sample-major.  Same (pixel, sample) set, so the same paths and image.
+__device__ __forceinline__ void generate_sample_tiled(const RenderConsts& rc, const uint32_t* __restrict__ pixel_order, uint32_t sa, uint32_t cnt,
+                                                      uint32_t i, float4& ro, float4& rd, PathState& ps) {
+  const uint32_t full = rc.n_pixels & ~31u, n_full_items = full * cnt;  // < 2^30 (host-side chunking)
+  uint32_t pl, sl;
+  if (i < n_full_items) {
+    const uint32_t c = i >> 5, tile = c / cnt;
+    sl = c - tile * cnt;
+    pl = (tile << 5) | (i & 31u);
+  } else {
+    const uint32_t t2 = i - n_full_items, rem = rc.n_pixels - full;
+    sl = t2 / rem;
+    pl = full + (t2 - sl * rem);
+  }
+  camera_ray(rc, __ldg(&pixel_order[pl]), (uint32_t)rc.spp_begin + sa + sl, ro, rd, ps);
+}
+
 // Slot q_offset + k of the queue receives local sample g0 + k, g0 = s0 * n_pixels + p0.
 __global__ void generate_kernel(PathQueue q, uint32_t q_offset, uint32_t count, uint32_t s0, uint32_t p0, RenderConsts rc,
                                 const uint32_t* __restrict__ pixel_order) {
@@ -529,6 +559,7 @@ __device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts
   bool alive = false;
   const f3 d = mk3(rd.x, rd.y, rd.z);
   const uint32_t pixel = ps.pixel;
+  RTB_CHECK(kChkPixel, pixel < rc.n_pixels);
   const f3 thr = mk3(ps.tr, ps.tg, ps.tb);
   const uint32_t bounce = ps.bounce;
   if (rc.cam.depth_camera) {
@@ -547,6 +578,7 @@ __device__ __forceinline__ bool shade_path(const DevScene& s, const RenderConsts
     const bool on_sphere = RTB_REF_TYPE(ref) == RTB_PRIM_SPHERE;
     const bool front = dot3(d, n_out) < 0.0f;  // HitRecord::set_face_normal, hittable.h:31-34
     const f3 nrm = front ? n_out : -n_out;
+    RTB_CHECK(kChkMaterial, mat_id < s.n_materials);
     const RtbMaterial m = s.materials[mat_id];
     const uint4 rnd = philox4x32_10(make_uint4(pixel, ps.sample, bounce, 0u), rc.round_keys);
     f3 atten = mk3(1.0f, 1.0f, 1.0f), dir = nrm;
@@ -695,7 +727,9 @@ struct PathStateRef {
 #endif
 };
 
-template <bool kFromQueue, bool kAdaptive>
+// kTileMajor: the work-item order (generate_sample_tiled vs generate_sample).  A template parameter, not a flag in RenderConsts: a
+// warp-uniform branch on it made ptxas spill one more register into the node loop, which cost more than the order wins.
+template <bool kFromQueue, bool kAdaptive, bool kTileMajor = false>
 struct PathIo {
   static constexpr int kServiceLanes = RTB_PATH_REFILL_LANES;
   uint32_t n;
@@ -722,6 +756,8 @@ struct PathIo {
     } else if (kAdaptive) {
       const uint32_t slot = i / ad.chunk_r, k = i - slot * ad.chunk_r;
       camera_ray(rc, __ldg(&ad.active[slot]), (uint32_t)rc.spp_begin + ad.base + k, o, d, ps);
+    } else if (kTileMajor) {
+      generate_sample_tiled(rc, pixel_order, s0, p0, i, o, d, ps);  // (s0, p0) = (first sample, sample count) of the launch
     } else {
       generate_sample(rc, pixel_order, s0, p0, i, o, d, ps);
     }
@@ -742,13 +778,14 @@ struct PathIo {
       psr.put(ps);
       return true;
     }
+    RTB_CHECK(kChkChunk, i < n);
     float* c = ad.chunk + 3 * (size_t)i;  // work item i = (slot, k): this sample's radiance (0 for an absorbed path)
     c[0] = sink.L.x; c[1] = sink.L.y; c[2] = sink.L.z;
     return false;
   }
 };
 
-template <bool kUseSmem, bool kFromQueue, bool kAdaptive = false>
+template <bool kUseSmem, bool kFromQueue, bool kAdaptive = false, bool kTileMajor = false>
 __global__ void __launch_bounds__(kTraceBlock, RTB_PATH_MIN_BLOCKS) path_kernel(DevScene s, PathQueue q, uint32_t n, uint32_t s0, uint32_t p0,
                                                                                RenderConsts rc, const uint32_t* __restrict__ pixel_order,
                                                                                float* accum, unsigned int* cursor,
@@ -758,9 +795,9 @@ __global__ void __launch_bounds__(kTraceBlock, RTB_PATH_MIN_BLOCKS) path_kernel(
   if (kAdaptive) n = *ad.n_active * ad.chunk_r;  // one work item per (active pixel, sample of the chunk)
 #if RTB_PS_SMEM
   __shared__ uint32_t path_state[6 * kTraceBlock];
-  PathIo<kFromQueue, kAdaptive> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathStateRef{path_state + threadIdx.x}, ad};
+  PathIo<kFromQueue, kAdaptive, kTileMajor> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathStateRef{path_state + threadIdx.x}, ad};
 #else
-  PathIo<kFromQueue, kAdaptive> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathStateRef{PathState{}}, ad};
+  PathIo<kFromQueue, kAdaptive, kTileMajor> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathStateRef{PathState{}}, ad};
 #endif
   trace_loop<kUseSmem>(s, smem_pairs, smem_stack_base(s, smem_pairs, kUseSmem), io, cursor, cnt);
   const unsigned total = __reduce_add_sync(kFull, io.rays);

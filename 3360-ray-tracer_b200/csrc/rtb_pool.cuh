@@ -64,7 +64,9 @@ struct TravLane {
     if (sp > 0) cur = stack.at(--sp);
     else cur = kDoneMark;
   }
-  __device__ __forceinline__ void node_step(unsigned long long base_all) {
+  __device__ __forceinline__ void node_step(unsigned long long base_all, uint32_t n_pairs) {
+    RTB_CHECK(kChkPair, cur < n_pairs);
+    (void)n_pairs;
     const unsigned long long addr = base_all + (unsigned long long)cur * 64ull;
     f32x2 c0[4], c1[4];
     ld256_global(addr, c0);
@@ -129,6 +131,8 @@ struct PoolIo {
     } else if (kAdaptive) {
       const uint32_t slot = i / ad.chunk_r, k = i - slot * ad.chunk_r;
       camera_ray(rc, __ldg(&ad.active[slot]), (uint32_t)rc.spp_begin + ad.base + k, o, d, ps);
+    } else if (rc.tile_major) {
+      generate_sample_tiled(rc, pixel_order, s0, p0, i, o, d, ps);
     } else {
       generate_sample(rc, pixel_order, s0, p0, i, o, d, ps);
     }
@@ -258,6 +262,7 @@ __device__ __forceinline__ void pool_loop(const DevScene& s, const RenderConsts&
       const int rank = __popc(wait_mask & lt_mask);
       if (!active && rank < n_ready) {
         slot = ready_q[n_ready - 1 - rank];
+        RTB_CHECK(kChkPoolSlot, slot < (uint32_t)kPoolSlots);
         t.start(s, __uint_as_float(fld(F_OX, slot)), __uint_as_float(fld(F_OY, slot)), __uint_as_float(fld(F_OZ, slot)),
                 __uint_as_float(fld(F_DX, slot)), __uint_as_float(fld(F_DY, slot)), __uint_as_float(fld(F_DZ, slot)));
         active = true;
@@ -273,10 +278,10 @@ __device__ __forceinline__ void pool_loop(const DevScene& s, const RenderConsts&
       const bool at_node = active && !(t.cur & kLeafBit);
       const unsigned nm = __ballot_sync(kFull, at_node);
       if (nm == 0u || RTB_NODE_EXIT_DEN * __popc(nm) < RTB_NODE_EXIT_NUM * n_trace) break;
-      if (at_node) t.node_step(base_all);
+      if (at_node) t.node_step(base_all, s.n_pairs);
 #pragma unroll
       for (int extra = 1; extra < RTB_NODE_STEPS_PER_VOTE; ++extra)
-        if (active && !(t.cur & kLeafBit)) t.node_step(base_all);
+        if (active && !(t.cur & kLeafBit)) t.node_step(base_all, s.n_pairs);
     }
     // ---- leaf phase, one primitive type at a time
 #pragma unroll 1

@@ -92,6 +92,7 @@ __device__ __forceinline__ void sphere_uv(f3 n, float& u, float& v) {
 // normal (sphere_n, valid when on_sphere) instead of for every sphere hit as the reference does (sphere.h:50).
 __device__ __forceinline__ f3 texture_value(const DevScene& s, int tex, float u, float v, f3 p, bool on_sphere, f3 sphere_n) {
   for (int guard = 0; guard < 8; ++guard) {
+    RTB_CHECK(kChkMaterial, tex >= 0 && (uint32_t)tex < s.n_textures);
     const RtbTexture t = s.textures[tex];
     if (t.type == RTB_TEX_SOLID) return mk3(t.color[0], t.color[1], t.color[2]);
     if (t.type == RTB_TEX_CHECKER) {

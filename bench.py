@@ -183,6 +183,8 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--lean", action="store_true", help="skip the per-kernel (serial wavefront) and other-pipeline measurements and shorten e2e: "
+                                                        "for the C1-C5 x N matrix (tools/gpu_matrix.sh), where only the headline numbers are wanted")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -280,14 +282,14 @@ def main():
     # per-kernel times: the same step with ONE wavefront in flight and an event pair around every launch
     # (RTB_RENDER_SERIAL); in the timed steps above several wavefronts overlap, so kernels cannot be timed singly
     serial_stats = []
-    for _ in range(min(K, 3)):
+    for _ in range(0 if args.lean and args.pipeline == "path" else min(K, 3)):
         flush.fill_(1)
         barrier()
         serial_stats.append(step(rt.RENDER_SERIAL)[1])
     # the other pipeline, for the record (not the headline)
     other_flags = 0 if args.pipeline == "wavefront" else rt.RENDER_WAVEFRONT
     other_ms = []
-    for k in range(1 + min(K, 5)):
+    for k in range(0 if args.lean else 1 + min(K, 5)):
         flush.fill_(1)
         barrier()
         ms_o = step(other_flags)[0]
@@ -321,7 +323,7 @@ def main():
     e2e_ms = []
     import ctypes as C
     host_img = torch.empty(n_pix * 3, dtype=torch.float32).pin_memory()
-    KE = min(K, 10)
+    KE = min(K, 3 if args.lean else 10)
     e2e_parts = []
     for k in range(min(W, 1) + KE):
         barrier()
@@ -374,19 +376,20 @@ def main():
                     "ms_parts_rank0": dict(zip(("scene_create", "render_and_readback", "scene_destroy"), (float(x) for x in np.mean(e2e_parts, axis=0)))),
                     "what": "rtb_scene_create (all scene arrays H2D) + rtb_render with a host rgb buffer (D2H) + rtb_scene_destroy, wall clock"},
             "gpu_launches": int(sum(s["launches"] for s in stats) + K),
-            "other_pipeline": {"name": "path" if args.pipeline == "wavefront" else "wavefront", "ms_per_step": float(np.mean(other_ms)),
-                               "msamples_per_s": stats[-1]["samples"] / float(np.mean(other_ms)) / 1e3},
+            "other_pipeline": None if not other_ms else {"name": "path" if args.pipeline == "wavefront" else "wavefront", "ms_per_step": float(np.mean(other_ms)),
+                                                          "msamples_per_s": samples_per_step / float(np.mean(other_ms)) / 1e3},
             "reduce_and_resolve_ms_rank0": float(np.mean(reduce_ms)),
             "weak": None if world == 1 else {"what": f"every rank renders the full {spp} spp ({world}x the samples), one reduce", "ms_per_step": weak_ms,
                                               "msamples_per_s": weak_samples / (weak_ms * 1e-3) / 1e6, "spp_total": spp * world},
             "clocks": clk,
             "kernel_ms_per_step": {"path_kernel": float(np.mean([s["ms_total"] for s in stats])) if args.pipeline == "path" else None,
-                                   "wavefront_serial": {k: float(np.mean([s[k] for s in serial_stats])) for k in ("ms_generate", "ms_extend", "ms_shade", "ms_drain", "ms_total")},
+                                   "wavefront_serial": None if not serial_stats else {k: float(np.mean([s[k] for s in serial_stats])) for k in ("ms_generate", "ms_extend", "ms_shade", "ms_drain", "ms_total")},
                                    "how": "path_kernel: CUDA events around the one launch of each timed step; wavefront_serial: the wavefront pipeline re-run with one "
                                           "wavefront in flight (RTB_RENDER_SERIAL) and events around every launch"},
         }
         if not args.no_roofline and world == 1:
-            line["roofline"] = roofline(rt, hs, cam, cfg, stats if args.pipeline == "path" else serial_stats, mode, args.pool, args.pipeline, device_tree)
+            line["roofline"] = roofline(rt, hs, cam, cfg, stats if args.pipeline == "path" else serial_stats, mode, args.pool, args.pipeline, device_tree,
+                                        sm_mhz=(clk or {}).get("sm_mhz"))
         elif not args.no_roofline:
             line["roofline"] = {"note": "measured at N=1 only (one process, one GPU)"}
         if not args.no_cpu_baseline and world == 1:
@@ -413,16 +416,29 @@ def scene_bytes(d):
                + d.n_materials * 32 + d.n_textures * 32)
 
 
-def roofline(rt, hs, cam, cfg, stats, mode, pool, pipeline, device_tree=False):
+def roofline(rt, hs, cam, cfg, stats, mode, pool, pipeline, device_tree=False, sm_mhz=None):
     """The dominant kernel - path_kernel (default pipeline: one launch per step) or extend_kernel (wavefront pipeline) -
-    against the HBM roof the contract asks for and against the roof that actually binds an L2-resident scene.
-    Algorithmic bytes / flops per ray are SURVEY 8(d)'s per-unit figures with the traversal counts of this workload
-    taken from the instrumented build (librtb200_counters.so); the path kernel adds its accumulator read-modify-write."""
+    against three roofs; `bound` / `achieved` / `peak` / `frac` at the top level are those of the roof that BINDS (the
+    largest model time), the HBM form the bench contract describes stays under roofs.hbm:
+      hbm    algorithmic bytes (SURVEY 8d per-ray figure x rays of the launch + accumulator RMW) / launch time against
+             MEASURED_PEAKS.json hbm_gbs.  For C1-C4 the scene is L2-resident and this roof does not bind (`traffic`,
+             the DRAM bytes ncu measured for the launch, is ~1000x below the algorithmic bytes);
+      l2     the same bytes against the L2 read bandwidth measured in this run with an ld.global.cg sweep of 64 MiB
+             (cannot hit the L1s; round 1 used __ldg over 32 MiB = 221 KB per SM, which partly measured the L1);
+      issue  executed thread-instructions of the launch against 4 warp-instructions x 32 lanes per clock per SM: the
+             fraction of the SMs' lane-issue slots that did work = (issue-slot use) x (active lanes / 32).  Instruction
+             counts per ray come from the committed ncu capture of this kernel on this config
+             (profiles/r02_kernel_counts.json, from profiles/r02_path_kernel_<config>.txt - NOT measured in-run).
+    Traversal counts per ray are measured in this run with the instrumented build (librtb200_counters.so)."""
+    import torch
     peaks_file = ROOT / "MEASURED_PEAKS.json"
-    hbm_peak, src = 6650.0, "fallback (B200_PROFILING.md)"
+    hbm_peak, src, sm_max = 6650.0, "fallback (B200_PROFILING.md)", 1965.0
     if peaks_file.exists():
-        hbm_peak, src = float(json.loads(peaks_file.read_text())["hbm_gbs"]), "MEASURED_PEAKS.json"
+        mpj = json.loads(peaks_file.read_text())
+        hbm_peak, src, sm_max = float(mpj["hbm_gbs"]), "MEASURED_PEAKS.json", float(mpj.get("sm_max_mhz", sm_max))
     mp = rt.measure_peaks()
+    n_sm = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
+    f_sm = 1e6 * float(sm_mhz or sm_max)
     # per-ray traversal counts from the instrumented build on the same workload at reduced spp (counts per ray are spp-invariant)
     hs_c = rt.HostScene.build(*cfg["scene"], counters=True, device_tree=device_tree)
     ds_c = rt.DeviceScene(hs_c)
@@ -447,19 +463,40 @@ def roofline(rt, hs, cam, cfg, stats, mode, pool, pipeline, device_tree=False):
         k_ms = float(np.mean([s["ms_extend"] for s in stats]))
         extra = 0.0
     total_bytes = bytes_ray * rays + extra
-    gbs = total_bytes / (k_ms * 1e-3) / 1e9
-    t_l2 = total_bytes / (mp["l2_gbs"] * 1e9)
-    t_alu = f32_ray * rays / (mp["fp32_tflops"] * 1e12) + f64_ray * rays / (mp["fp64_tflops"] * 1e12)
-    traffic = None
-    tf = ROOT / "profiles" / "traffic.json"  # dram bytes per launch from the committed ncu --set full capture of this kernel
-    if tf.exists():
-        traffic = json.loads(tf.read_text()).get(f"{pipeline}:{cfg['scene'][0]}")
-    return {"kernel": kernel, "bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
-            "frac": gbs / hbm_peak, "peak_source": src, "traffic": traffic,
-            "note": "scene (<=10 MB) is L2-resident: HBM is not the binding roof; binding model below",
-            "binding": {"bound": "l2" if t_l2 > t_alu else "fp32+fp64 issue", "model_ms": 1e3 * max(t_l2, t_alu), "measured_ms": k_ms,
-                        "frac": 1e3 * max(t_l2, t_alu) / k_ms, "l2_ms": 1e3 * t_l2, "alu_ms": 1e3 * t_alu,
-                        "measured_peaks": mp},
+    secs = k_ms * 1e-3
+    gbs = total_bytes / secs / 1e9
+    roofs = {"hbm": {"achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak, "model_ms": 1e3 * total_bytes / (hbm_peak * 1e9),
+                     "peak_source": src},
+             "l2": {"achieved": gbs, "peak": mp["l2_gbs"], "unit": "GB/s", "frac": gbs / mp["l2_gbs"], "model_ms": 1e3 * total_bytes / (mp["l2_gbs"] * 1e9),
+                    "peak_source": "ld.global.cg read sweep of 64 MiB, this run (rtb_measure_l2_gbs)"},
+             "fp": {"achieved": (f32_ray + f64_ray) * rays / secs / 1e12, "unit": "TFLOP/s", "fp32_peak": mp["fp32_tflops"], "fp64_peak": mp["fp64_tflops"],
+                    "model_ms": 1e3 * (f32_ray * rays / (mp["fp32_tflops"] * 1e12) + f64_ray * rays / (mp["fp64_tflops"] * 1e12))}}
+    roofs["fp"]["frac"] = roofs["fp"]["model_ms"] / k_ms
+    traffic, counts_note = None, None
+    cf = ROOT / "profiles" / "r02_kernel_counts.json"  # ncu --set full capture of this kernel per config (committed; not measured in-run)
+    if cf.exists():
+        scene_key = {"earth_bubbles": "earth"}.get(cfg["scene"][0], cfg["scene"][0])
+        kc = json.loads(cf.read_text()).get(f"{pipeline}:{scene_key}")
+        if kc:
+            traffic = kc["dram_bytes_per_ray"] * rays / max(launches, 1)
+            lane_peak = 128.0 * n_sm * f_sm  # 4 schedulers x 32 lanes per clock per SM
+            tinst = kc["thread_inst_per_ray"] * rays
+            roofs["issue"] = {"achieved": tinst / secs / 1e12, "peak": lane_peak / 1e12, "unit": "T thread-instructions/s", "frac": tinst / secs / lane_peak,
+                              "model_ms": 1e3 * tinst / lane_peak, "warp_issue_frac": kc["warp_inst_per_ray"] * rays / secs / (4.0 * n_sm * f_sm),
+                              "lanes_per_instruction": kc["lanes_per_inst"], "thread_inst_per_ray": kc["thread_inst_per_ray"],
+                              "warp_inst_per_ray": kc["warp_inst_per_ray"], "sm_count": n_sm, "sm_mhz": f_sm / 1e6,
+                              "counts_source": "profiles/r02_kernel_counts.json (ncu capture " + str(kc.get("source")) + "; from profiles/, not measured in-run)"}
+            roofs["hbm"]["dram_traffic_bytes_per_launch"] = traffic
+            roofs["hbm"]["traffic_model_ms"] = 1e3 * traffic * max(launches, 1) / (hbm_peak * 1e9)  # what HBM actually has to deliver
+            counts_note = "traffic = dram__bytes_read.sum + dram__bytes_write.sum per ray from the committed ncu capture x rays of this launch"
+    # which roof binds: the largest model time, where HBM is charged with the DRAM traffic the launch really causes (ncu) when that
+    # is known - an L2-resident scene does not move its algorithmic bytes through HBM
+    binding = max(roofs, key=lambda k: roofs[k].get("traffic_model_ms", roofs[k]["model_ms"]))
+    b = roofs[binding]
+    return {"kernel": kernel, "bound": binding, "achieved": b["achieved"], "peak": b.get("peak", b.get("fp32_peak")), "unit": b["unit"], "frac": b["frac"],
+            "traffic": traffic, "traffic_note": counts_note,
+            "note": "bound = the roof with the largest model time; every roof is listed under roofs (hbm = the bench contract's form)",
+            "roofs": roofs, "measured_peaks": mp,
             "per_ray": {**per_ray, "bytes": bytes_ray, "fp32_flops": f32_ray, "fp64_flops": f64_ray},
             "rays_per_step": rays, "launches_per_step": launches, "kernel_ms_per_step": k_ms,
             "avg_launch_ms": k_ms / max(launches, 1), "algorithmic_bytes_per_launch": total_bytes / max(launches, 1)}

@@ -251,6 +251,11 @@ const char* rtb_last_error(void);
 int rtb_abi_version(void);
 /* Number of visible CUDA devices (0 if none); never fails. */
 int rtb_device_count(void);
+/* The library's own bounds checker.  A build with -DRTB_CHECKED (make VARIANT=checked EXTRA=-DRTB_CHECKED) compares every index
+ * its kernels form (traversal stack, pair, primitive, accumulator pixel, material / texture, adaptive chunk, pool slot) with
+ * the size of what it indexes, clamps the access and counts violations per class on the current device since the library was
+ * loaded.  Returns 1 and the eight counters from such a build, 0 (RTB_OK) and zeros from a normal build, < 0 on error. */
+int rtb_debug_check_failures(uint64_t* counts8);
 /* Bind the calling thread to `device` and create the library's stream on it. */
 int rtb_init(int device);
 int rtb_shutdown(void);

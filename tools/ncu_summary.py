@@ -20,6 +20,27 @@ raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_outpu
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, units, data = rows[0], rows[1], rows[2:]
 print("kernel:", [d[hdr.index("Kernel Name")][:60] for d in data])
+if "--json" in sys.argv:  # machine-readable counters of the FIRST launch in the report (bench.py reads profiles/r02_kernel_counts.json)
+    import json
+    def val(k):
+        if k not in hdr:
+            return None
+        i = hdr.index(k)
+        v = float(data[0][i].replace(",", ""))
+        u = units[i].lower()
+        if k.startswith("dram__bytes"):
+            v *= {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9}.get(u, 1)
+        if k == "gpu__time_duration.sum":
+            v *= {"ns": 1e-6, "us": 1e-3, "usecond": 1e-3, "ms": 1, "msecond": 1, "s": 1e3, "second": 1e3, "nsecond": 1e-6}.get(u, 1)
+        return v
+    out = {"kernel": data[0][hdr.index("Kernel Name")][:80], "ms_under_ncu": val("gpu__time_duration.sum"),
+           "warp_inst": val("smsp__inst_executed.sum"), "lanes_per_inst": val("smsp__thread_inst_executed_per_inst_executed.ratio"),
+           "issue_active_pct": val("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+           "dram_bytes": (val("dram__bytes_read.sum") or 0) + (val("dram__bytes_write.sum") or 0),
+           "l1_global_ld_hit_pct": val("l1tex__t_sector_pipe_lsu_mem_global_op_ld_hit_rate.pct"), "l2_hit_pct": val("lts__t_sector_hit_rate.pct"),
+           "local_ld": val("smsp__sass_inst_executed_op_local_ld.sum"), "local_st": val("smsp__sass_inst_executed_op_local_st.sum"),
+           "registers": val("launch__registers_per_thread"), "source": rep.split("/")[-1]}
+    print("JSON " + json.dumps(out))
 for k in KEYS:
     if k in hdr:
         i = hdr.index(k)
