@@ -170,6 +170,10 @@ static int CompileTree(const RtbSceneDesc& d, rtbc::Compiled* out) {
 }
 
 static int ValidateDesc(const RtbSceneDesc* d);
+// per-primitive material / axis checks move to the device above this many primitives (a host pass over 5 M records is 22 ms)
+static bool ValidatesPrimitivesOnDevice(const RtbSceneDesc* d) {
+  return (uint64_t)d->n_spheres + d->n_triangles + d->n_rects > (1u << 18) && !std::getenv("RTB_HOST_VALIDATE");
+}
 
 // Pinned staging for scene uploads, per host thread, grow-only: rtb_scene_create copies every array into it and
 // issues one asynchronous H2D copy per array into ONE device arena (one cudaMalloc / cudaFree per scene).
@@ -520,7 +524,15 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
   PUT(s->Put(reinterpret_cast<const double2*>(d->spheres), 2 * (size_t)d->n_spheres, &v.spheres));
   PUT(s->Put(reinterpret_cast<const double2*>(d->triangles), 5 * (size_t)d->n_triangles, &v.triangles));
   PUT(s->Put(reinterpret_cast<const double2*>(d->rects), 3 * (size_t)d->n_rects, &v.rects));
-  {  // float shadows of the double tables (shading frame + pre-filter)
+  // float shadows of the double tables (shading frame + pre-filter): part of the pinned arena image where the scene has one;
+  // otherwise (device-built trees, scenes above 256 MB) written by three small kernels after the upload - no host pass, no H2D
+  const bool device_shadows = img == nullptr && !std::getenv("RTB_HOST_SHADOWS");
+  size_t shadow_off[3] = {0, 0, 0};
+  if (device_shadows) {
+    shadow_off[0] = s->Reserve((size_t)d->n_spheres * 16);
+    shadow_off[1] = s->Reserve((size_t)d->n_triangles * 48);
+    shadow_off[2] = s->Reserve((size_t)d->n_rects * 32);
+  } else {
     sf.resize(cached ? 0 : d->n_spheres);
     for (uint32_t i = 0; i < (cached ? 0u : d->n_spheres); ++i)
       sf[i] = make_float4((float)d->spheres[i].c[0], (float)d->spheres[i].c[1], (float)d->spheres[i].c[2], (float)d->spheres[i].r);
@@ -552,9 +564,10 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
   PUT(s->Put(d->sphere_gid, d->n_spheres, &v.sphere_gid));
   PUT(s->Put(d->triangle_gid, d->n_triangles, &v.triangle_gid));
   PUT(s->Put(d->rect_gid, d->n_rects, &v.rect_gid));
-  PUT(s->Put(d->sphere_rank ? d->sphere_rank : d->sphere_gid, d->n_spheres, &v.sphere_rank));
-  PUT(s->Put(d->triangle_rank ? d->triangle_rank : d->triangle_gid, d->n_triangles, &v.triangle_rank));
-  PUT(s->Put(d->rect_rank ? d->rect_rank : d->rect_gid, d->n_rects, &v.rect_rank));
+  // no slot ranks (device-built tree: creation order breaks exact-t ties): the rank tables ARE the id tables, uploaded once
+  if (d->sphere_rank || img) PUT(s->Put(d->sphere_rank ? d->sphere_rank : d->sphere_gid, d->n_spheres, &v.sphere_rank));
+  if (d->triangle_rank || img) PUT(s->Put(d->triangle_rank ? d->triangle_rank : d->triangle_gid, d->n_triangles, &v.triangle_rank));
+  if (d->rect_rank || img) PUT(s->Put(d->rect_rank ? d->rect_rank : d->rect_gid, d->n_rects, &v.rect_rank));
   PUT(s->Put(d->materials, d->n_materials, &v.materials));
   PUT(s->Put(d->textures, d->n_textures, &v.textures));
   {  // images -> point-sampled texture objects over RGBA8 arrays
@@ -605,9 +618,47 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
   lap("tables");
   PUT(s->Commit(g_stream, img, counts_now));
   lap("commit");
+  if (!cached && ValidatesPrimitivesOnDevice(d) && n_prims > 0) {
+    unsigned bad = 0;
+    cudaError_t ve = cudaMemsetAsync(s->cursor, 0, 4, g_stream);  // the work cursor doubles as the error counter before the first launch
+    if (ve == cudaSuccess) {
+      rtb::validate_materials_kernel<<<(n_prims + 255) / 256, 256, 0, g_stream>>>(v, d->n_spheres, d->n_triangles, d->n_rects, d->n_materials, s->cursor);
+      ve = cudaMemcpyAsync(&bad, s->cursor, 4, cudaMemcpyDeviceToHost, g_stream);
+    }
+    if (ve == cudaSuccess) ve = cudaStreamSynchronize(g_stream);
+    if (ve == cudaSuccess) ve = cudaMemsetAsync(s->cursor, 0, 4, g_stream);
+    if (ve != cudaSuccess || bad) {
+      rtb_scene_destroy(s);
+      return ve != cudaSuccess ? Fail(RTB_ECUDA, std::string("scene validation kernel: ") + cudaGetErrorString(ve))
+                               : Fail(RTB_EINVAL, std::to_string(bad) + " primitives with a material index (or rect axis) out of range");
+    }
+    lap("validate2");
+  }
+  if (!d->sphere_rank && !img) v.sphere_rank = v.sphere_gid;
+  if (!d->triangle_rank && !img) v.triangle_rank = v.triangle_gid;
+  if (!d->rect_rank && !img) v.rect_rank = v.rect_gid;
+  if (device_shadows) {
+    auto* sph = reinterpret_cast<float4*>(s->arena + shadow_off[0]);
+    auto* tri = reinterpret_cast<float4*>(s->arena + shadow_off[1]);
+    auto* rec = reinterpret_cast<float4*>(s->arena + shadow_off[2]);
+    if (d->n_spheres) rtb::shadow_spheres_kernel<<<(d->n_spheres + 255) / 256, 256, 0, g_stream>>>(v.spheres, d->n_spheres, sph);
+    if (d->n_triangles) rtb::shadow_triangles_kernel<<<(d->n_triangles + 255) / 256, 256, 0, g_stream>>>(v.triangles, d->n_triangles, tri);
+    if (d->n_rects) rtb::shadow_rects_kernel<<<(d->n_rects + 255) / 256, 256, 0, g_stream>>>(v.rects, d->n_rects, rec);
+    v.sphere_f = d->n_spheres ? sph : nullptr;
+    v.triangle_f = d->n_triangles ? tri : nullptr;
+    v.rect_f = d->n_rects ? rec : nullptr;
+    cudaError_t se = cudaGetLastError();
+    if (se == cudaSuccess && !(device_build && n_prims > 0)) se = cudaStreamSynchronize(g_stream);  // (the tree build below synchronises anyway)
+    if (se != cudaSuccess) {
+      rtb_scene_destroy(s);
+      return Fail(RTB_ECUDA, std::string("float shadow kernels: ") + cudaGetErrorString(se));
+    }
+    lap("shadows");
+  }
   if (device_build && n_prims > 0) {
     v.pairs = reinterpret_cast<const float4*>(s->arena + built_pairs_off);
     PUT(BuildTreeOnDevice(s, d->n_spheres, d->n_triangles, n_prims, reinterpret_cast<float*>(s->arena + built_pairs_off)));
+    lap("build");
   }
   // opt in to large dynamic shared memory for the two traversal kernels
   {
@@ -662,9 +713,11 @@ static int ValidateDesc(const RtbSceneDesc* d) {
     if (idx >= lim || (ty == RTB_PRIM_SUBTREE && (idx & 1u))) return Fail(RTB_EINVAL, "leaf entry out of range");
   }
   auto mat_ok = [&](uint32_t m) { return m < d->n_materials; };
-  for (uint32_t i = 0; i < d->n_spheres; ++i) if (!mat_ok(d->sphere_mat[i])) return Fail(RTB_EINVAL, "sphere material out of range");
-  for (uint32_t i = 0; i < d->n_triangles; ++i) if (!mat_ok(d->triangles[i].mat)) return Fail(RTB_EINVAL, "triangle material out of range");
-  for (uint32_t i = 0; i < d->n_rects; ++i) if (!mat_ok(d->rects[i].mat) || d->rects[i].axis < 0 || d->rects[i].axis > 2) return Fail(RTB_EINVAL, "bad rect");
+  if (!ValidatesPrimitivesOnDevice(d)) {  // large scenes: the same checks run as a kernel after the upload (rtb_scene_create)
+    for (uint32_t i = 0; i < d->n_spheres; ++i) if (!mat_ok(d->sphere_mat[i])) return Fail(RTB_EINVAL, "sphere material out of range");
+    for (uint32_t i = 0; i < d->n_triangles; ++i) if (!mat_ok(d->triangles[i].mat)) return Fail(RTB_EINVAL, "triangle material out of range");
+    for (uint32_t i = 0; i < d->n_rects; ++i) if (!mat_ok(d->rects[i].mat) || d->rects[i].axis < 0 || d->rects[i].axis > 2) return Fail(RTB_EINVAL, "bad rect");
+  }
   for (uint32_t i = 0; i < d->n_materials; ++i) {
     const RtbMaterial& m = d->materials[i];
     if ((m.type == RTB_MAT_LAMBERTIAN || m.type == RTB_MAT_DIFFUSE_LIGHT) && (m.tex < 0 || (uint32_t)m.tex >= d->n_textures))

@@ -24,6 +24,56 @@ struct BuildBox {
   float lo[3], hi[3];
 };
 
+// Float shadows of the exact double tables (what the FP32 filters and shading read: rtb_device.cuh DevScene), computed on the
+// device for scenes that are not served from a pinned arena image: the stress scene's 4 M triangles would otherwise cost a
+// host pass over 320 MB and another 192 MB of H2D traffic per rtb_scene_create.  Bit-identical to the host loop in
+// rtb_scene_create: round to nearest for the values, round UP for the max |component| bounds of the triangle filter.
+__global__ void __launch_bounds__(256) shadow_spheres_kernel(const double2* __restrict__ spheres, uint32_t n, float4* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double2 q0 = spheres[2 * (size_t)i], q1 = spheres[2 * (size_t)i + 1];
+  out[i] = make_float4((float)q0.x, (float)q0.y, (float)q1.x, (float)q1.y);
+}
+__global__ void __launch_bounds__(256) shadow_triangles_kernel(const double2* __restrict__ tris, uint32_t n, float4* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double2* p = tris + 5 * (size_t)i;
+  const double2 q0 = p[0], q1 = p[1], q2 = p[2], q3 = p[3], q4 = p[4];
+  const float mat = __uint_as_float((uint32_t)(__double_as_longlong(q4.y) & 0xffffffffll));
+  const double m1 = fmax(fabs(q1.y), fmax(fabs(q2.x), fabs(q2.y))), m2 = fmax(fabs(q3.x), fmax(fabs(q3.y), fabs(q4.x)));
+  out[3 * (size_t)i] = make_float4((float)q0.x, (float)q0.y, (float)q1.x, mat);
+  out[3 * (size_t)i + 1] = make_float4((float)q1.y, (float)q2.x, (float)q2.y, __double2float_ru(m1));
+  out[3 * (size_t)i + 2] = make_float4((float)q3.x, (float)q3.y, (float)q4.x, __double2float_ru(m2));
+}
+__global__ void __launch_bounds__(256) shadow_rects_kernel(const double2* __restrict__ rects, uint32_t n, float4* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double2* p = rects + 3 * (size_t)i;
+  const double2 q0 = p[0], q1 = p[1], q2 = p[2];  // (k,a0) (a1,b0) (b1, axis|mat)
+  const long long bits = __double_as_longlong(q2.y);
+  out[2 * (size_t)i] = make_float4((float)q0.x, (float)q0.y, (float)q1.x, (float)q1.y);
+  out[2 * (size_t)i + 1] = make_float4((float)q2.x, __uint_as_float((uint32_t)(bits & 0xffffffffll)), __uint_as_float((uint32_t)((unsigned long long)bits >> 32)), 0.f);
+}
+
+// ValidateDesc's material-index checks for large scenes, on the device (a host pass over the stress scene's 5 M primitives is
+// 22 ms of every rtb_scene_create): bad[0] counts primitives whose material index is out of range, rects also their axis.
+__global__ void __launch_bounds__(256) validate_materials_kernel(DevScene s, uint32_t n_spheres, uint32_t n_triangles, uint32_t n_rects, uint32_t n_materials,
+                                                                 unsigned* bad) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  bool ok = true;
+  if (i < n_spheres) {
+    ok = s.sphere_mat[i] < n_materials;
+  } else if (i < n_spheres + n_triangles) {
+    const double2 q4 = s.triangles[5 * (size_t)(i - n_spheres) + 4];
+    ok = (uint32_t)(__double_as_longlong(q4.y) & 0xffffffffll) < n_materials;
+  } else if (i < n_spheres + n_triangles + n_rects) {
+    const long long bits = __double_as_longlong(s.rects[3 * (size_t)(i - n_spheres - n_triangles) + 2].y);
+    const int axis = (int)(bits & 0xffffffffll);
+    ok = (uint32_t)((unsigned long long)bits >> 32) < n_materials && axis >= 0 && axis <= 2;
+  }
+  if (!ok) atomicAdd(bad, 1u);
+}
+
 // float <-> unsigned with the same order (for atomicMin / atomicMax on floats of any sign)
 __device__ __forceinline__ unsigned ordered_bits(float f) {
   const unsigned u = __float_as_uint(f);

@@ -18,11 +18,17 @@ import argparse
 import json
 import os
 
-# The CPU legs (oracle/_ref: the reference's OpenMP pixel loop) wandered between 6.5 and 9.3 Msamples/s for the same render
-# in round 1 (threads migrating between cores, a cold first pass): pin them before libgomp reads its environment.
-HOST_CORES = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)  # before libgomp binds this thread to one place
-os.environ.setdefault("OMP_PROC_BIND", "close")
-os.environ.setdefault("OMP_PLACES", "cores")
+HOST_CORES = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+
+
+def pin_openmp():
+    """The CPU legs (oracle/_ref: the reference's OpenMP pixel loop) wandered between 6.5 and 9.3 Msamples/s for the same render in
+    round 1 (threads migrating between cores, a cold first pass).  OMP_PROC_BIND / OMP_PLACES must be in the environment BEFORE
+    libgomp initialises, and they also bind the calling thread to the first place - fatal for a GPU rank (two torchrun ranks
+    pinned to core 0 made a 0.15 ms NCCL reduce take 4 ms) - so only the process that runs a CPU leg calls this: `--impl reference`
+    itself, and the b200 arm's cpu_baseline by running `bench.py --impl reference` as a child process."""
+    os.environ.setdefault("OMP_PROC_BIND", "close")
+    os.environ.setdefault("OMP_PLACES", "cores")
 import subprocess
 import sys
 import threading
@@ -147,6 +153,19 @@ def cpu_reference_leg(rt, cfg_name, budget_s, steps=1, warmup=0):
                       f"{len(out)} pass(es), {secs:.1f} s", "seconds": secs, "ms_per_step": 1e3 * secs / max(1, len(out))}
 
 
+def cpu_baseline_child(cfg_name, budget_s):
+    """cpu_baseline of the b200 arm: the reference arm of this script as a child process (pinned OpenMP threads, librth.so only,
+    no CUDA library mapped), one bounded pass; returns its cpu_baseline object."""
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "OMP_NUM_THREADS")}
+    r = subprocess.run([sys.executable, str(ROOT / "bench.py"), "--impl", "reference", "--config", cfg_name, "--steps", "1", "--warmup", "0",
+                        "--cpu-step-budget", str(budget_s)], capture_output=True, text=True, env=env, timeout=900)
+    for ln in reversed(r.stdout.strip().split("\n")):
+        if ln.startswith("{"):
+            d = json.loads(ln)
+            return dict(d["cpu_baseline"], mrays_per_s=d.get("mrays_per_s"))
+    return {"value": None, "unit": "Msamples/s", "cores": HOST_CORES, "kind": "reference", "sample": "cpu leg failed: " + r.stderr[-300:]}
+
+
 def _cpu_model():
     try:
         for line in Path("/proc/cpuinfo").read_text().split("\n"):
@@ -182,6 +201,7 @@ def main():
                          "(RTB_SCENE_DEVICE_BUILD); auto = device for the stress scene (faster to build AND to traverse there), host otherwise")
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-step-budget", type=float, default=0.0, help="--impl reference: seconds of CPU work per step (0 = sized from --steps)")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--lean", action="store_true", help="skip the per-kernel (serial wavefront) and other-pipeline measurements and shorten e2e: "
                                                         "for the C1-C5 x N matrix (tools/gpu_matrix.sh), where only the headline numbers are wanted")
@@ -198,7 +218,8 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return 0
-        per_step = min(12.0, 150.0 / (K + W))
+        pin_openmp()
+        per_step = args.cpu_step_budget if args.cpu_step_budget > 0 else min(12.0, 150.0 / (K + W))
         leg = cpu_reference_leg(rt, args.config, per_step, steps=K, warmup=W)
         line = {"metric": "msamples_per_s", "value": leg["value"], "unit": "Msamples/s", "n_gpus": args.gpus, "steps": K, "warmup": W,
                 "ms_per_step": leg["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
@@ -393,8 +414,7 @@ def main():
         elif not args.no_roofline:
             line["roofline"] = {"note": "measured at N=1 only (one process, one GPU)"}
         if not args.no_cpu_baseline and world == 1:
-            line["cpu_baseline"] = {k: v for k, v in cpu_reference_leg(rt, args.config, args.cpu_budget).items()
-                                    if k in ("value", "unit", "cores", "kind", "sample", "build", "mrays_per_s", "host")}
+            line["cpu_baseline"] = cpu_baseline_child(args.config, args.cpu_budget)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

@@ -155,3 +155,20 @@ def test_deep_but_legal_device_tree_traces_like_the_host_tree(rt):
     same = a["prim_id"] == b["prim_id"]
     tie = ~same & (a["t"] == b["t"]) & (a["prim_id"] >= 0) & (b["prim_id"] >= 0)
     assert (same | tie).all() and np.array_equal(a["t"], b["t"])
+
+
+def test_large_scene_material_indices_are_validated_on_the_device(rt):
+    """Above 2^18 primitives ValidateDesc's per-primitive checks run as a kernel after the upload (22 ms of host time per
+    rtb_scene_create on the stress scene otherwise): a bad index must still be refused with RTB_EINVAL."""
+    lib = rt.load()
+    hs = rt.HostScene.build("stress", (400, 400, 60, 150, 2), device_tree=True)
+    d = rt.binding.RtbSceneDesc.from_buffer_copy(hs.desc)
+    assert d.n_triangles + d.n_spheres > (1 << 18)
+    h = C.c_void_p()
+    assert lib.rtb_scene_create(C.byref(d), C.byref(h)) == rt.RTB_OK, lib.rtb_last_error()
+    lib.rtb_scene_destroy(h)
+    mats = np.ctypeslib.as_array(C.cast(d.sphere_mat, C.POINTER(C.c_uint32)), shape=(d.n_spheres,)).copy()
+    mats[mats.size // 2] = d.n_materials + 7
+    d.sphere_mat = mats.ctypes.data
+    assert lib.rtb_scene_create(C.byref(d), C.byref(h)) == rt.RTB_EINVAL
+    assert b"out of range" in lib.rtb_last_error()

@@ -50,6 +50,15 @@ run("secondary (parent order)", sec)
 run("secondary random order", sec[rng.permutation(len(sec))])
 k = np.lexsort((sec["d"][:, 2] > 0, sec["d"][:, 0] > 0))
 run("secondary sorted by octant", sec[k])
+# The bound on what ANY regrouping of rays between lanes / warps could buy: the same ray population, but every warp's 32 lanes
+# trace one and the same ray (chunks of 32 consecutive batch entries are what a warp claims), i.e. zero SIMT divergence and
+# 32 identical addresses per load.  time(x32) / time(as is) is the floor a perfectly coherent scheduler could reach.
+run("primary, each ray x32", np.repeat(rays[::32], 32)[:n])
+run("secondary, each ray x32", np.repeat(sec[::32], 32)[:len(sec)])
+mix = np.concatenate([rays[: len(rays) // 2], sec[: len(sec) // 2]])
+mix = mix[rng.permutation(len(mix))]
+run("primary+secondary shuffled", mix)
+run("primary+secondary, x32", np.repeat(mix[::32], 32)[:len(mix)])
 print("--- launch floor: small batches")
 for k in (32, 1024, 32768):
     run("primary first %d" % k, rays[n // 2:n // 2 + k])
