@@ -1,11 +1,17 @@
 // rt::scene::Image implementation (reference: src/scene/image.cc:16-73).
 #include "image.h"
 
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <fstream>
 #include <iostream>
 
+#include "jpeg_baseline.h"
+
+// Optional: other formats (PNG, progressive JPEG ...) through stb_image when the embedder points RT_STB_INCLUDE at a copy
+// (make RT_STB_INCLUDE=dir).  The product does not need it: baseline JPEG - what the reference ships - is decoded by
+// jpeg_baseline.h, and nothing is taken from the reference tree at build time.
 #ifdef RT_HAVE_STB
 #define STB_IMAGE_IMPLEMENTATION
 #define STBI_NO_HDR_WRITE
@@ -36,9 +42,38 @@ bool LoadTable(const std::string& path, int& w, int& h, std::vector<unsigned cha
   return static_cast<size_t>(f.gcount()) == out.size();
 }
 
+// The float image stbi_loadf returns for an 8-bit file (the reference's loader, image.cc:31): pow(byte / 255, 2.2) evaluated in
+// double on the float quotient, times the scale 1, rounded to float - then the reference's own x 255.999 re-quantisation.
+unsigned char LinearisedByte(unsigned char v) {
+  const float lin = static_cast<float>(std::pow(static_cast<double>(v / 255.0f), static_cast<double>(2.2f)) * static_cast<double>(1.0f));
+  return QuantiseLinear(lin);
+}
+
+bool LoadJpeg(const std::string& path, int& w, int& h, std::vector<unsigned char>& out, bool& is_jpeg) {
+  is_jpeg = false;
+  std::ifstream f(path, std::ios::binary);
+  if (!f) return false;
+  std::vector<unsigned char> bytes((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+  if (bytes.size() < 4 || bytes[0] != 0xff || bytes[1] != 0xd8) return false;
+  is_jpeg = true;
+  std::vector<uint8_t> rgb;
+  std::string why;
+  if (!jpeg::Decode(bytes.data(), bytes.size(), w, h, rgb, why)) {
+    std::cerr << "ERROR: '" << path << "': " << why << "\n";
+    return false;
+  }
+  unsigned char table[256];
+  for (int v = 0; v < 256; ++v) table[v] = LinearisedByte(static_cast<unsigned char>(v));
+  out.resize(rgb.size());
+  for (size_t i = 0; i < rgb.size(); ++i) out[i] = table[rgb[i]];
+  return true;
+}
+
 bool LoadOne(const std::string& path, int& w, int& h, std::vector<unsigned char>& out) {
   if (LoadTable(path + ".rgbtab", w, h, out)) return true;
   if (path.size() > 7 && path.compare(path.size() - 7, 7, ".rgbtab") == 0 && LoadTable(path, w, h, out)) return true;
+  bool is_jpeg = false;
+  if (LoadJpeg(path, w, h, out, is_jpeg)) return true;
 #ifdef RT_HAVE_STB
   int n = 3;
   float* lin = stbi_loadf(path.c_str(), &w, &h, &n, 3);  // gamma-2.2 linearised floats
