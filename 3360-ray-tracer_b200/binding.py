@@ -19,7 +19,7 @@ ASSET_DIR = REPO_ROOT / "assets"
 RTB_OK, RTB_EINVAL, RTB_ENODEVICE, RTB_ECUDA, RTB_ENOMEM = 0, -1, -2, -3, -4
 PRIM_SPHERE, PRIM_TRIANGLE, PRIM_RECT, PRIM_SUBTREE = 0, 1, 2, 3
 MODE_A, MODE_B = 0, 1
-RENDER_SMEM_TOP, RENDER_KEEP_ACCUM, RENDER_SERIAL, RENDER_WAVEFRONT, RENDER_NO_DRAIN, RENDER_POOL_PATHS = 1, 2, 4, 8, 16, 32
+RENDER_SMEM_TOP, RENDER_KEEP_ACCUM, RENDER_SERIAL, RENDER_WAVEFRONT, RENDER_NO_DRAIN, RENDER_POOL_PATHS, RENDER_COST_ORDER = 1, 2, 4, 8, 16, 32, 64
 ADAPT_PIXEL_STATE, ADAPT_LUMINANCE = 0, 1
 EX_SPHERE, EX_TRIANGLE, EX_RECT, EX_BVH_BEGIN, EX_BVH_END, EX_LIST_BEGIN, EX_LIST_END = 0, 1, 2, 10, 11, 12, 13
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_DIFFUSE_LIGHT = 0, 1, 2, 3

@@ -92,6 +92,9 @@ struct RenderCtx {
   size_t accum_bytes = 0;
   char* adapt = nullptr;   // adaptive renders: two active-pixel lists, their counts, one chunk of sample radiances; grow-only
   size_t adapt_bytes = 0;
+  char* sched = nullptr;   // cost-ordered schedule: per-pixel path lengths, the re-ordered pixel list, sort keys / values / scratch; grow-only
+  size_t sched_bytes = 0;
+  uint32_t sched_pixels = 0;  // the pixel list in `sched` was sorted for an image of this many pixels (RTB_COST_ORDER_REUSE experiment)
 };
 thread_local RenderCtx g_ctx;
 
@@ -436,6 +439,9 @@ int rtb_shutdown(void) {
     if (g_ctx.adapt) cudaFree(g_ctx.adapt);
     g_ctx.adapt = nullptr;
     g_ctx.adapt_bytes = 0;
+    if (g_ctx.sched) cudaFree(g_ctx.sched);
+    g_ctx.sched = nullptr;
+    g_ctx.sched_bytes = 0;
     if (g_staging.host) cudaFreeHost(g_staging.host);
     g_staging = Staging{};
     cudaStreamDestroy(g_stream);
@@ -894,13 +900,29 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   uint32_t n_groups = ad ? 1u : 0u;
   if (const char* e = std::getenv("RTB_ADAPT_GROUPS")) n_groups = ad ? (uint32_t)std::min(4, std::max(1, std::atoi(e))) : 0u;
   for (uint32_t g = 0; g < n_groups && rc == RTB_OK; ++g) rc = EnsureLight(ctx->groups[g]);
+  // Cost-ordered schedule of the persistent path kernel (RTB_RENDER_COST_ORDER; MEASURED, OFF BY DEFAULT).  A launch ends on the paths
+  // that happen to be long and start late: on bunny C3 0.75 ms of an 8.8 ms step, and most of the step once the spp are split over
+  // 8 GPUs (a 20-bounce path running alone takes ~0.8 ms).  Here the first samples of every pixel also record the length of their
+  // paths, the tiles are sorted by it, and the rest of the render starts with the tiles that grow long paths; while the measuring
+  // launch drains, a second stream renders the next samples in the plain order.  B200 (profiles/r02_cost_ordered_schedule.txt):
+  // the ordering itself is worth 4 % at 100 spp and 15 % at 12 spp on the bunny (one launch in the order a PREVIOUS render measured:
+  // 8.81 -> 8.46 ms, 1.66 -> 1.41 ms; nothing on RTIOW / Cornell), but measuring inside the render costs more than that - the ordered
+  // launch has to wait for the measuring launch's own tail: 9.06 ms and 2.16 ms.  Long paths are rare events spread over many tiles;
+  // a tile's history only predicts them partly.
+  const uint32_t spp_all_ = (uint32_t)(prm->spp_end - prm->spp_begin);
+  const bool cost_order = fused && !ad && spp_all_ >= 8 && n_pixels >= 4096 && !(prm->flags & (RTB_RENDER_SMEM_TOP | RTB_RENDER_POOL_PATHS)) &&
+                          !std::getenv("RTB_SMEM_TOP") && !std::getenv("RTB_POOL_PATHS") &&
+                          ((prm->flags & RTB_RENDER_COST_ORDER) || std::getenv("RTB_COST_ORDER")) && (prm->max_depth > 4 || prm->mode == RTB_MODE_B);
+  if (cost_order && rc == RTB_OK) rc = EnsureLight(ctx->groups[0]);
   if (rc != RTB_OK) return rc;
   cudaStream_t st = g_stream;
   std::vector<Wave*> waves;  // the first n_waves of the context (it may hold more from an earlier call)
   if (ad)
     for (uint32_t g = 0; g < n_groups; ++g) waves.push_back(&ctx->groups[g]);
-  else if (fused) waves.push_back(&ctx->fused);
-  else
+  else if (fused) {
+    waves.push_back(&ctx->fused);
+    if (cost_order) waves.push_back(&ctx->groups[0]);
+  } else
     for (size_t k = 0; k < n_waves; ++k) waves.push_back(&ctx->waves[k]);
   rtb::RenderConsts rcst{};
   rcst.cam = *cam;
@@ -1030,44 +1052,88 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
       ++iterations;
     }
   } else if (trace && fused) {
-    Wave& w = *waves[0];
-    // tile-major: a launch covers samples [sa, sa + cnt) of every pixel (< 2^30 items); sample-major: 2^30 consecutive items
+    // tile-major: a launch covers samples [sa, sa + cnt) of every pixel (< 2^30 items); sample-major: the same range, sample index outermost
     const uint32_t spp_all = (uint32_t)(prm->spp_end - prm->spp_begin);
     const uint32_t spp_per_launch = std::max(1u, (1u << 30) / n_pixels);
-    uint32_t sa = 0;
-    while (generated < total) {
-      uint32_t chunk, s0, p0;
-      if (rcst.tile_major) {
-        const uint32_t cnt = std::min(spp_per_launch, spp_all - sa);
-        chunk = n_pixels * cnt;
-        s0 = sa;
-        p0 = cnt;
+    // samples [sa, sb) of every pixel of `order` on wave w; cost != nullptr: the launch also records path lengths per pixel
+    auto launch_range = [&](Wave& w, uint32_t sa, uint32_t sb, const uint32_t* order, uint32_t* cost) -> int {
+      while (sa < sb) {
+        const uint32_t cnt = std::min(spp_per_launch, sb - sa);
+        const uint32_t chunk = n_pixels * cnt, s0 = sa, p0 = tile_major ? cnt : 0u;
+        RTB_CUDA(cudaMemsetAsync(w.counts, 0, 4, w.stream));
+        auto* rc64 = reinterpret_cast<unsigned long long*>(w.counts + 2);
+        rtb::AdaptivePlanes pl = planes;
+        pl.count = cost;
+        if (use_pool)
+          rtb::pool_kernel<false, false><<<pool_grid, kTraceBlock, 0, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order, d_rgb_sum, w.counts, rc64,
+                                                                                s->counters, pl);
+        else if (use_smem && tile_major)
+          rtb::path_kernel<true, false, false, true><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order, d_rgb_sum,
+                                                                                                 w.counts, rc64, s->counters, pl);
+        else if (use_smem)
+          rtb::path_kernel<true, false><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order, d_rgb_sum, w.counts,
+                                                                                    rc64, s->counters, pl);
+        else if (cost && tile_major)
+          rtb::path_kernel<false, false, false, true, true><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order,
+                                                                                                        d_rgb_sum, w.counts, rc64, s->counters, pl);
+        else if (cost)
+          rtb::path_kernel<false, false, false, false, true><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order,
+                                                                                                         d_rgb_sum, w.counts, rc64, s->counters, pl);
+        else if (tile_major)
+          rtb::path_kernel<false, false, false, true><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order, d_rgb_sum,
+                                                                                                  w.counts, rc64, s->counters, pl);
+        else
+          rtb::path_kernel<false, false><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order, d_rgb_sum, w.counts,
+                                                                                     rc64, s->counters, pl);
         sa += cnt;
-      } else {
-        chunk = (uint32_t)std::min<unsigned long long>(total - generated, 1ull << 30);
-        s0 = (uint32_t)(generated / n_pixels);
-        p0 = (uint32_t)(generated % n_pixels);
+        generated += chunk;
+        ++launches;
+        ++iterations;
       }
-      RTB_CUDA(cudaMemsetAsync(w.counts, 0, 4, w.stream));
-      auto* rc64 = reinterpret_cast<unsigned long long*>(w.counts + 2);
-      if (use_pool)
-        rtb::pool_kernel<false, false><<<pool_grid, kTraceBlock, 0, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, ctx->pixel_order, d_rgb_sum,
-                                                                              w.counts, rc64, s->counters, planes);
-      else if (use_smem && tile_major)
-        rtb::path_kernel<true, false, false, true><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, ctx->pixel_order,
-                                                                                               d_rgb_sum, w.counts, rc64, s->counters, planes);
-      else if (use_smem)
-        rtb::path_kernel<true, false><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, ctx->pixel_order,
-                                                                                  d_rgb_sum, w.counts, rc64, s->counters, planes);
-      else if (tile_major)
-        rtb::path_kernel<false, false, false, true><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, ctx->pixel_order,
-                                                                                                d_rgb_sum, w.counts, rc64, s->counters, planes);
-      else
-        rtb::path_kernel<false, false><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, ctx->pixel_order,
-                                                                                   d_rgb_sum, w.counts, rc64, s->counters, planes);
-      generated += chunk;
-      ++launches;
-      ++iterations;
+      return RTB_OK;
+    };
+    if (!cost_order) {
+      RTB_TRY(launch_range(*waves[0], 0u, spp_all, ctx->pixel_order, nullptr));
+    } else {
+      Wave &wa = *waves[0], &wb = *waves[1];
+      const uint32_t n_groups32 = n_pixels / 32u;  // complete groups of 32 entries of pixel_order (the < 32 left-over pixels keep their place)
+      const uint32_t a = spp_all >= 32 ? 2u : 1u, b0 = std::max(1u, spp_all / 10u);
+      auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
+      size_t cub_bytes = 0;
+      RTB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const uint32_t*)nullptr, (uint32_t*)nullptr,
+                                               (int)n_groups32, 0, 24, wa.stream));
+      const size_t o_cost = 0, o_order = o_cost + up((size_t)n_pixels * 4), o_k0 = o_order + up((size_t)n_pixels * 4), o_k1 = o_k0 + up((size_t)n_groups32 * 4),
+                   o_v0 = o_k1 + up((size_t)n_groups32 * 4), o_v1 = o_v0 + up((size_t)n_groups32 * 4), o_cub = o_v1 + up((size_t)n_groups32 * 4),
+                   need = o_cub + up(cub_bytes);
+      if (ctx->sched_bytes < need) {
+        if (ctx->sched) cudaFree(ctx->sched);
+        ctx->sched = nullptr;
+        ctx->sched_bytes = 0;
+        RTB_CUDA(cudaMalloc(reinterpret_cast<void**>(&ctx->sched), need));
+        ctx->sched_bytes = need;
+      }
+      auto* cost = reinterpret_cast<uint32_t*>(ctx->sched + o_cost);
+      auto* order2 = reinterpret_cast<uint32_t*>(ctx->sched + o_order);
+      auto* k0 = reinterpret_cast<uint32_t*>(ctx->sched + o_k0);
+      auto* k1 = reinterpret_cast<uint32_t*>(ctx->sched + o_k1);
+      auto* v0 = reinterpret_cast<uint32_t*>(ctx->sched + o_v0);
+      auto* v1 = reinterpret_cast<uint32_t*>(ctx->sched + o_v1);
+      if (std::getenv("RTB_COST_ORDER_REUSE") && ctx->sched_pixels == n_pixels) {
+        // experiment: the whole render in ONE launch in the order the previous render of this image measured - what the ordering
+        // itself is worth, without the cost of measuring
+        RTB_TRY(launch_range(wa, 0u, spp_all, order2, nullptr));
+        goto cost_order_done;
+      }
+      RTB_CUDA(cudaMemsetAsync(cost, 0, (size_t)n_pixels * 4, wa.stream));
+      RTB_TRY(launch_range(wa, 0u, a, ctx->pixel_order, cost));              // measures while it renders
+      RTB_TRY(launch_range(wb, a, a + b0, ctx->pixel_order, nullptr));      // fills the GPU while the measuring launch drains
+      rtb::group_cost_kernel<<<(n_groups32 + 7) / 8, 256, 0, wa.stream>>>(ctx->pixel_order, cost, n_groups32, k0, v0);
+      RTB_CUDA(cub::DeviceRadixSort::SortPairs(ctx->sched + o_cub, cub_bytes, k0, k1, v0, v1, (int)n_groups32, 0, 24, wa.stream));
+      rtb::permute_groups_kernel<<<(n_pixels + 255) / 256, 256, 0, wa.stream>>>(ctx->pixel_order, v1, n_groups32, n_pixels, order2);
+      launches += 3;
+      RTB_TRY(launch_range(wa, a + b0, spp_all, order2, nullptr));          // long-path tiles first
+      ctx->sched_pixels = n_pixels;
+    cost_order_done:;
     }
   }
   while (any) {

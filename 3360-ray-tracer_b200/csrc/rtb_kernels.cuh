@@ -729,7 +729,9 @@ struct PathStateRef {
 
 // kTileMajor: the work-item order (generate_sample_tiled vs generate_sample).  A template parameter, not a flag in RenderConsts: a
 // warp-uniform branch on it made ptxas spill one more register into the node loop, which cost more than the order wins.
-template <bool kFromQueue, bool kAdaptive, bool kTileMajor = false>
+// kCostMap: a finished path leaves its length in cost[pixel] (atomicMax; the pointer travels in AdaptivePlanes::count): the first
+// samples of a render measure where the long paths are, the rest of the render is scheduled by it (rtb_api.cu, CostOrder).
+template <bool kFromQueue, bool kAdaptive, bool kTileMajor = false, bool kCostMap = false>
 struct PathIo {
   static constexpr int kServiceLanes = RTB_PATH_REFILL_LANES;
   uint32_t n;
@@ -771,6 +773,7 @@ struct PathIo {
       AtomicSink sink{accum};
       const bool alive = shade_path(s, rc, sink, o, d, ps, tf, ref);
       if (alive) psr.put(ps);
+      else if (kCostMap) atomicMax(&ad.count[ps.pixel], ps.bounce + 1u);  // rays this path traced
       return alive;
     }
     LocalSink sink{mk3(0.0f, 0.0f, 0.0f)};
@@ -785,7 +788,7 @@ struct PathIo {
   }
 };
 
-template <bool kUseSmem, bool kFromQueue, bool kAdaptive = false, bool kTileMajor = false>
+template <bool kUseSmem, bool kFromQueue, bool kAdaptive = false, bool kTileMajor = false, bool kCostMap = false>
 __global__ void __launch_bounds__(kTraceBlock, RTB_PATH_MIN_BLOCKS) path_kernel(DevScene s, PathQueue q, uint32_t n, uint32_t s0, uint32_t p0,
                                                                                RenderConsts rc, const uint32_t* __restrict__ pixel_order,
                                                                                float* accum, unsigned int* cursor,
@@ -795,9 +798,9 @@ __global__ void __launch_bounds__(kTraceBlock, RTB_PATH_MIN_BLOCKS) path_kernel(
   if (kAdaptive) n = *ad.n_active * ad.chunk_r;  // one work item per (active pixel, sample of the chunk)
 #if RTB_PS_SMEM
   __shared__ uint32_t path_state[6 * kTraceBlock];
-  PathIo<kFromQueue, kAdaptive, kTileMajor> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathStateRef{path_state + threadIdx.x}, ad};
+  PathIo<kFromQueue, kAdaptive, kTileMajor, kCostMap> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathStateRef{path_state + threadIdx.x}, ad};
 #else
-  PathIo<kFromQueue, kAdaptive, kTileMajor> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathStateRef{PathState{}}, ad};
+  PathIo<kFromQueue, kAdaptive, kTileMajor, kCostMap> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathStateRef{PathState{}}, ad};
 #endif
   trace_loop<kUseSmem>(s, smem_pairs, smem_stack_base(s, smem_pairs, kUseSmem), io, cursor, cnt);
   const unsigned total = __reduce_add_sync(kFull, io.rays);
@@ -939,6 +942,28 @@ __global__ void __launch_bounds__(256) peer_sum_kernel(float* __restrict__ root,
     for (int k = 0; k < n_peers; ++k) a += peers.p[k][t];
     root[t] = a;
   }
+}
+
+// ---- cost-ordered schedule (rtb_api.cu CostOrder): groups of 32 consecutive entries of pixel_order (one 8 x 4 tile) are the unit the
+// persistent kernel hands to a warp; their order is free.  key[g] = 255 - (longest path seen in the group), so that an ascending
+// sort puts the groups with the longest paths FIRST and the launch ends on groups whose paths are short.
+__global__ void __launch_bounds__(256) group_cost_kernel(const uint32_t* __restrict__ pixel_order, const uint32_t* __restrict__ cost, uint32_t n_groups,
+                                                         uint32_t* __restrict__ key, uint32_t* __restrict__ group) {
+  const uint32_t g = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (g >= n_groups) return;
+  const uint32_t c = cost[__ldg(&pixel_order[32u * g + (threadIdx.x & 31u)])];
+  const uint32_t mx = __reduce_max_sync(0xffffffffu, c), sum = __reduce_add_sync(0xffffffffu, c);
+  if ((threadIdx.x & 31u) == 0u) {
+    key[g] = ((255u - min(mx, 255u)) << 16) | (0xffffu - min(sum, 0xffffu));  // longest path first, then the most rays
+    group[g] = g;
+  }
+}
+__global__ void __launch_bounds__(256) permute_groups_kernel(const uint32_t* __restrict__ pixel_order, const uint32_t* __restrict__ sorted_group, uint32_t n_groups,
+                                                             uint32_t n_pixels, uint32_t* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_pixels) return;
+  const uint32_t g = i >> 5;
+  out[i] = g < n_groups ? __ldg(&pixel_order[32u * __ldg(&sorted_group[g]) + (i & 31u)]) : __ldg(&pixel_order[i]);  // the < 32 left-over pixels stay last
 }
 
 __global__ void iota_kernel(uint32_t* v, uint32_t n) {

@@ -207,6 +207,8 @@ typedef struct RtbRenderParams {
 #define RTB_RENDER_WAVEFRONT 8u    /* generate / extend / shade+compact kernels over path queues instead of the default persistent path kernel
                                       (generate + traverse + shade per lane, no queues; measured 13-53 % faster) */
 #define RTB_RENDER_NO_DRAIN 16u    /* wavefront mode: do not hand the last few live paths to the path kernel */
+#define RTB_RENDER_COST_ORDER 64u  /* cost-ordered schedule: the first samples measure where the long paths are, the rest of the render starts with
+                                      those tiles (three overlapping launches).  Same image; measured slower than one launch */
 #define RTB_RENDER_POOL_PATHS 32u  /* the pool kernel (64 paths per warp in shared memory, traversal and shading decoupled: csrc/rtb_pool.cuh)
                                       instead of the default persistent kernel (one path per lane, shaded in place: path_kernel).  Same paths, same
                                       image; measured 16-58 % slower (profiles/r02_pool_vs_lane_ab.jsonl) - kept as the evidence */

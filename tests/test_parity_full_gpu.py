@@ -88,6 +88,41 @@ def test_full_size_band_matches_reference_render(rt, name):
     ds.close()
 
 
+@pytest.mark.parametrize("name", ["rtiow", "cornell", "bunny", "earth"])
+def test_hit_volume_per_config_matches_reference_bvh(rt, name):
+    """SURVEY 8c's hit KAT volume: >= 1 M primary rays of the configuration's own camera + >= 1 M secondary rays (two bounce
+    generations off the reference's own hit points) per config, ids bit-exact and t bit-equal to geom::Bvh::Hit."""
+    from oracle import checker
+    cfg = bench.CONFIGS[name]
+    hs = rt.HostScene.build(*cfg["scene"])
+    ora = checker.make_oracle(hs, fast=False)
+    if ora.kind != "reference":
+        pytest.skip("oracle/_ref was not built (no /root/reference at build time)")
+    ds = rt.DeviceScene(hs)
+    cam = rt.camera_init(bench.camera_for(rt, cfg))
+    primary = helpers.camera_rays(rt, cam, 1_200_000, 61)
+    t0, g0 = ora.intersect(primary)
+    assert helpers.check_hits(ds.intersect(primary), t0, g0), f"{name}: primary t not bit-equal"
+    b1 = helpers.secondary_rays(rt, primary, t0, g0 >= 0, 62)
+    t1, g1 = ora.intersect(b1)
+    assert helpers.check_hits(ds.intersect(b1), t1, g1), f"{name}: first-bounce t not bit-equal"
+    b2 = helpers.secondary_rays(rt, b1, t1, g1 >= 0, 63)
+    t2, g2 = ora.intersect(b2)
+    assert helpers.check_hits(ds.intersect(b2), t2, g2), f"{name}: second-bounce t not bit-equal"
+    n_sec = len(b1) + len(b2)
+    if n_sec < 1_000_000:  # open scenes lose rays to the sky: top the secondary set up with a third generation from more primaries
+        more = helpers.camera_rays(rt, cam, 2_000_000, 64)
+        tm, gm = ora.intersect(more)
+        b3 = helpers.secondary_rays(rt, more, tm, gm >= 0, 65)[: 1_050_000 - n_sec]
+        t3, g3 = ora.intersect(b3)
+        assert helpers.check_hits(ds.intersect(b3), t3, g3), f"{name}: top-up bounce t not bit-equal"
+        n_sec += len(b3)
+    assert len(primary) >= 1_000_000 and n_sec >= 1_000_000, (len(primary), n_sec)
+    _record(f"hits:{name}", {"primary": int(len(primary)), "secondary": int(n_sec), "primary_hit_fraction": float((g0 >= 0).mean()),
+                             "ids": "bit-exact", "t": "bit-equal"})
+    ds.close()
+
+
 # ---- C5: the 5 M-primitive stress scene ------------------------------------------------------------------------------
 @pytest.fixture(scope="module")
 def stress(rt):

@@ -16,6 +16,24 @@ def one(names, stress_spp):
     m = g.load_package()
     for name in names:
         cfg = bench.CONFIGS[name]
+        if os.environ.get("AB_COST_ORDER"):  # the default kernel with and without the cost-ordered schedule, same library
+            ds = m.DeviceScene(m.HostScene.build(*cfg["scene"], device_tree=name == "stress"))
+            cam = m.camera_init(bench.camera_for(m, cfg))
+            spp = stress_spp if name == "stress" else cfg["spp"]
+            for label, env in (("cost_order", "1"), ("plain", None)):
+                os.environ.pop("RTB_COST_ORDER", None)
+                if env:
+                    os.environ["RTB_COST_ORDER"] = env
+                for div in (1, 8):  # the configuration's spp, and 1/8 of it (what one of 8 GPUs renders in the spp split)
+                    ts = []
+                    for rep in range(6):
+                        img, st = ds.render(cam, spp=max(1, spp // div), max_depth=cfg["depth"])
+                        ts.append(st["ms_total"])
+                    print(json.dumps({"config": name, "schedule": label, "spp": max(1, spp // div), "ms": round(float(np.median(ts[1:])), 3), "min_ms": round(min(ts), 3),
+                                      "rays": st["rays"], "launches": st["launches"], "checksum": float(img.astype(np.float64).sum())}), flush=True)
+            os.environ.pop("RTB_COST_ORDER", None)
+            ds.close()
+            continue
         dev_tree = name == "stress"
         ds = m.DeviceScene(m.HostScene.build(*cfg["scene"], device_tree=dev_tree))
         cam = m.camera_init(bench.camera_for(m, cfg))
