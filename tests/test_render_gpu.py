@@ -157,7 +157,7 @@ def test_wavefront_and_path_kernel_render_the_same_paths(rt, golden_dir, scenes,
     lane, sl = ds.render(cam, spp=32, max_depth=cfg.max_depth, mode=m, flags=rt.RENDER_POOL_PATHS)  # the pool kernel: 64 paths per warp in shared memory
     assert sl["rays"] == sf["rays"] and sl["launches"] == sf["launches"] == 1
     ordered, so = ds.render(cam, spp=32, max_depth=cfg.max_depth, mode=m, flags=rt.RENDER_COST_ORDER)  # measuring + filler + cost-ordered launch, sort kernels
-    assert so["rays"] == sf["rays"] and so["launches"] == 6
+    assert so["rays"] == sf["rays"] and so["launches"] == (6 if cam.width * cam.height >= 4096 else 1)  # (tiny images keep the single launch)
     assert np.abs(ordered - fused).max() <= 1e-5 * max(1.0, float(fused.max()))
     assert np.abs(lane - fused).max() <= 1e-5 * max(1.0, float(fused.max()))
     assert sf["rays"] == sw["rays"] == sn["rays"] == ss["rays"] and sf["samples"] == sw["samples"] == cam.width * cam.height * 32
