@@ -61,6 +61,13 @@ F32_NODE = 18
 F64_SPHERE, F64_TRI, F64_RECT = 22, 44, 8
 
 
+def common_config(cfg, width, height, spp, depth, estimator="A", overridden=False):
+    """The `config` object of the bench line: identical in both arms (--impl b200 / reference) for the same workload, so that the driver can
+    see that the two lines measure one thing; what differs between the arms goes under `arm`."""
+    return {"workload": cfg["label"] + ("" if not overridden else f" [OVERRIDDEN: width {width}, spp {spp}]"), "image": [int(width), int(height)],
+            "spp_total": int(spp), "max_depth": int(depth), "estimator": estimator}
+
+
 def camera_for(rt, cfg, width=None, spp=None):
     if "preset" in cfg:
         c = rt.camera_preset(rt.ASSET_DIR / cfg["cameras"], cfg["preset"])
@@ -147,7 +154,7 @@ def cpu_reference_leg(rt, cfg_name, budget_s, steps=1, warmup=0):
     samples = sum(o[0] for o in out); rays = sum(o[1] for o in out); secs = sum(o[2] for o in out)
     host = {"nproc": os.cpu_count(), "affinity": cores, "cpu_model": _cpu_model(), "omp_proc_bind": os.environ.get("OMP_PROC_BIND"),
             "omp_places": os.environ.get("OMP_PLACES"), "warm_passes": 2 + warmup}
-    return {"value": samples / secs / 1e6, "unit": "Msamples/s", "mrays_per_s": rays / secs / 1e6, "cores": cores, "host": host,
+    return {"value": samples / secs / 1e6, "unit": "Msamples/s", "mrays_per_s": rays / secs / 1e6, "cores": cores, "host": host, "image": [cam.width, cam.height],
             "kind": ora.kind, "build": "-O3 -mavx2 -mfma -fopenmp" if fast else "-O2 -fopenmp (strict IEEE)",
             "sample": f"{cfg_name} {cam.width}x{cam.height} at {spp} of {cfg['spp']} spp, maxDepth {cfg['depth']}, estimator A, "
                       f"{len(out)} pass(es), {secs:.1f} s", "seconds": secs, "ms_per_step": 1e3 * secs / max(1, len(out))}
@@ -224,7 +231,8 @@ def main():
         line = {"metric": "msamples_per_s", "value": leg["value"], "unit": "Msamples/s", "n_gpus": args.gpus, "steps": K, "warmup": W,
                 "ms_per_step": leg["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic", "impl": "reference", "mrays_per_s": leg["mrays_per_s"],
-                "config": {"workload": cfg["label"], "estimator": "A (MegaKernel + DefaultSampler + Camera::GetPixel)", "sample": leg["sample"]},
+                "config": common_config(cfg, leg["image"][0], leg["image"][1], cfg["spp"], cfg["depth"]),
+                "arm": {"what": "the reference's own CPU path: MegaKernel + DefaultSampler + Camera::GetPixel (estimator A), all host threads", "sample": leg["sample"]},
                 "cpu_baseline": {k: leg[k] for k in ("value", "unit", "cores", "kind", "sample", "build", "host")},
                 "e2e": {"value": leg["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
@@ -381,17 +389,16 @@ def main():
             "dtype": "f32 shading / f64 exact hit replay", "data": "synthetic", "impl": "b200",
             "mrays_per_s": rays_per_step / (ms_per_step * 1e-3) / 1e6,
             "wall_ms_per_step": total_wall_ms / K,
-            "config": {"workload": cfg["label"] + ("" if not (args.spp or args.width) else f" [OVERRIDDEN: width {cam.width}, spp {spp}]"),
-                       "why_this_config": "north_star quotes its headline target (>=100x CPU, traversal roofline) on the bunny mesh scene",
-                       "image": [cam.width, cam.height], "spp_total": spp, "spp_per_gpu": [list(rt.multigpu.spp_slice(spp, r, world)) for r in range(world)],
-                       "max_depth": depth, "estimator": args.mode,
-                       "parallelism": f"spp SPLIT x{world} (one image of {spp} spp), scene replicated, 1 NCCL reduce(sum,f32) of {n_pix * 12} B onto rank 0, resolve there",
-                       "l2": "384 MiB buffer written between timed steps (L2 flushed); scene itself is L2-resident by design",
-                       "pipeline": "persistent path kernel (generate + traverse + shade per lane, one launch per step)" if args.pipeline == "path"
-                       else f"wavefront: generate / extend / shade+compact over queues, pool {args.pool or (1 << 21)} paths x {os.environ.get('RTB_WAVES', '4')} wavefronts in flight",
-                       "tree": "linear BVH built on the GPU inside rtb_scene_create (RTB_SCENE_DEVICE_BUILD)" if device_tree
-                       else "host SAH tree (the reference's algorithm) compiled to sibling pairs",
-                       "scene_build_s_untimed": round(t_build, 3)},
+            "config": common_config(cfg, cam.width, cam.height, spp, depth, args.mode, overridden=bool(args.spp or args.width)),
+            "arm": {"why_this_config": "north_star quotes its headline target (>=100x CPU, traversal roofline) on the bunny mesh scene",
+                    "spp_per_gpu": [list(rt.multigpu.spp_slice(spp, r, world)) for r in range(world)],
+                    "parallelism": f"spp SPLIT x{world} (one image of {spp} spp), scene replicated, 1 NCCL reduce(sum,f32) of {n_pix * 12} B onto rank 0, resolve there",
+                    "l2": "384 MiB buffer written between timed steps (L2 flushed); scene itself is L2-resident by design",
+                    "pipeline": "persistent path kernel (generate + traverse + shade per lane, one launch per step)" if args.pipeline == "path"
+                    else f"wavefront: generate / extend / shade+compact over queues, pool {args.pool or (1 << 21)} paths x {os.environ.get('RTB_WAVES', '4')} wavefronts in flight",
+                    "tree": "linear BVH built on the GPU inside rtb_scene_create (RTB_SCENE_DEVICE_BUILD)" if device_tree
+                    else "host SAH tree (the reference's algorithm) compiled to sibling pairs",
+                    "scene_build_s_untimed": round(t_build, 3)},
             "e2e": {"value": samples_per_step / (e2e_tot.item() / KE * 1e-3) / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_tot.item() / KE, "steps": KE,
                     "ms_parts_rank0": dict(zip(("scene_create", "render_and_readback", "scene_destroy"), (float(x) for x in np.mean(e2e_parts, axis=0)))),

@@ -98,3 +98,28 @@ def test_adaptive_reduce_sums_radiance_and_counts(rt, tmp_path):
     # the image is sum / count: a count-weighted mean of the per-rank means
     mean = got["sum"].reshape(-1, 3)[:, 0] / got["count"]
     assert np.all((mean >= 1.0) & (mean <= world))
+
+
+def test_bench_reference_arm_line_has_the_contract_keys_and_the_common_config():
+    """bench.py --impl reference on the host cores: one JSON line with the contract's keys; `config` is the object the b200 arm prints for
+    the same workload (bench.common_config), so that the driver can see both arms measure one thing."""
+    import json
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parents[1]
+    from oracle import ref
+    if not ref.available(fast=True) and not ref.available():
+        pytest.skip("oracle/_ref not built")
+    r = subprocess.run([sys.executable, str(root / "bench.py"), "--impl", "reference", "--config", "rtiow", "--steps", "1", "--warmup", "0",
+                        "--cpu-step-budget", "1"], capture_output=True, text=True, timeout=600, cwd=root)
+    assert r.returncode == 0, r.stderr[-500:]
+    line = json.loads([ln for ln in r.stdout.split("\n") if ln.startswith("{")][-1])
+    for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline", "dtype", "data", "config",
+              "impl", "cpu_baseline", "e2e"):
+        assert k in line, k
+    assert line["impl"] == "reference" and line["unit"] == "Msamples/s" and line["scaling"] == "strong" and line["value"] > 0
+    assert line["e2e"] == {"value": line["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert line["cpu_baseline"]["kind"] in ("reference", "port") and line["cpu_baseline"]["cores"] >= 1
+    import bench
+    assert line["config"] == bench.common_config(bench.CONFIGS["rtiow"], 1000, 562, 44, 10)
