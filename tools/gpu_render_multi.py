@@ -9,12 +9,13 @@ m = g.load_package()
 lib = m.load()
 name = sys.argv[1] if len(sys.argv) > 1 else "bunny"
 cfg = bench.CONFIGS[name]
-hs = m.HostScene.build(*cfg["scene"])
+hs = m.HostScene.build(*cfg["scene"], device_tree=name == "stress")
 cam = m.camera_init(bench.camera_for(m, cfg))
+base_spp = 8 if name == "stress" else cfg["spp"]  # (stress: 8 of 1024 spp per unit, the full config takes 5.6 s per render)
 n_dev = lib.rtb_device_count()
 base = None
 for n in [k for k in (1, 2, 4, 8) if k <= n_dev]:
-    for label, spp in (("weak", cfg["spp"] * n), ("strong", cfg["spp"] * 8)):
+    for label, spp in (("weak", base_spp * n), ("strong", base_spp * 8)):
         wall, dev, red = [], [], []
         for rep in range(5):
             t0 = time.perf_counter()
