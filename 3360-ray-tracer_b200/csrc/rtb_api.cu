@@ -937,6 +937,13 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   bool tile_major = s->arena_bytes > (1u << 20);
   if (const char* e = std::getenv("RTB_WORK_ORDER")) tile_major = e[0] == 't';
   rcst.tile_major = tile_major ? 1 : 0;
+  // Per-scene schedule of the traversal loop (PathIo::kTune, rtb_kernels.cuh): speculative leaf postponement for trees of spheres only,
+  // a later service phase for scenes that do not fit the L2.  RTB_TUNE=0|1|2 overrides.
+  int tune = 0;
+  if (s->dev.n_triangles == 0 && s->dev.n_rects == 0 && s->dev.n_spheres >= 64) tune = 1;
+  else if (tile_major && s->arena_bytes > (256u << 20)) tune = 2;
+  if (const char* e = std::getenv("RTB_TUNE")) tune = std::atoi(e);
+  if (tune == 2 && !tile_major) tune = 0;
   rcst.spp_max = prm->spp_end - prm->spp_begin;
   rcst.min_samples = ad ? ad->min_samples : 0;
   rcst.criterion = ad ? ad->criterion : 0;
@@ -1079,6 +1086,15 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
         else if (cost)
           rtb::path_kernel<false, false, false, false, true><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order,
                                                                                                          d_rgb_sum, w.counts, rc64, s->counters, pl);
+        else if (tune == 2 && tile_major)
+          rtb::path_kernel<false, false, false, true, false, 2><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order,
+                                                                                                            d_rgb_sum, w.counts, rc64, s->counters, pl);
+        else if (tune == 1 && tile_major)
+          rtb::path_kernel<false, false, false, true, false, 1><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order,
+                                                                                                            d_rgb_sum, w.counts, rc64, s->counters, pl);
+        else if (tune == 1)
+          rtb::path_kernel<false, false, false, false, false, 1><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order,
+                                                                                                             d_rgb_sum, w.counts, rc64, s->counters, pl);
         else if (tile_major)
           rtb::path_kernel<false, false, false, true><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order, d_rgb_sum,
                                                                                                   w.counts, rc64, s->counters, pl);

@@ -144,9 +144,7 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
   TravRay r;
   Best b{kNoHit, 0.f, 0.f, 0.f};
   uint32_t cur = kIdleMark, slot = 0;
-#if RTB_POSTPONE_LEAF
-  uint32_t post = 0;  // a leaf descriptor waiting for the leaf phase (0 = none: leaf descriptors have bit 31 set)
-#endif
+  uint32_t post = 0;  // Io::kPostpone: a leaf descriptor waiting for the leaf phase (0 = none: leaf descriptors have bit 31 set)
   unsigned pool_next = 0, pool_end = 0;  // warp-uniform: claimed, not yet assigned ray indices
   bool exhausted = false;                 // warp-uniform: the global cursor ran past n
 #ifdef RTB_COUNTERS
@@ -315,7 +313,7 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
       bool at_node = !(cur & kLeafBit);
       const unsigned nm = __ballot_sync(kFull, at_node);
       if (nm == 0u || RTB_NODE_EXIT_DEN * __popc(nm) < RTB_NODE_EXIT_NUM * n_act) break;
-#if RTB_POSTPONE_LEAF
+      if (Io::kPostpone) {
       // speculative traversal (Aila & Laine 2009): the node phase goes on, so a lane standing at a leaf keeps it for the
       // leaf phase and descends from its stack with the others instead of idling; one leaf per lane can wait
       if (!at_node && post == 0u && cur < kIdleMark) {
@@ -323,7 +321,7 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
         pop_or_finish();
         at_node = !(cur & kLeafBit);
       }
-#endif
+      }
       if (at_node) node_step();
 #pragma unroll
       for (int extra = 1; extra < RTB_NODE_STEPS_PER_VOTE; ++extra)  // more steps on the same vote: less vote overhead
@@ -331,13 +329,11 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
     }
     // ---- leaf phase, one primitive type at a time (the types are different code, SIMT would serialise
     // them anyway); each lane works through its whole leaf, the descriptor counting down
-#if RTB_POSTPONE_LEAF
-    if (post != 0u) {  // the waiting leaf first; where the lane stands now (pair, leaf or DONE) goes back on the stack
+    if (Io::kPostpone && post != 0u) {  // the waiting leaf first; where the lane stands now (pair, leaf or DONE) goes back on the stack
       stack.push(sp++, cur);
       cur = post;
       post = 0u;
     }
-#endif
 #pragma unroll 1
     for (uint32_t type = 0; type < 3; ++type) {
       const uint32_t want = 4u + type;  // leaf bit + type in the top three bits
@@ -360,6 +356,7 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
 // ---- seam 2: RayIntegrator::IntersectBatch (src/integrator/cpu_ray_integrator.h:18-46) --------
 struct BatchIo {
   static constexpr int kServiceLanes = RTB_REFILL_LANES;
+  static constexpr bool kPostpone = RTB_POSTPONE_LEAF != 0;
   uint32_t n;
   unsigned rays;
   const float4* in;
@@ -504,6 +501,7 @@ __global__ void generate_kernel(PathQueue q, uint32_t q_offset, uint32_t count, 
 // ---- extend: Bvh::Hit for every live path (src/geom/bvh.h:71-119) ------------------------------
 struct ExtendIo {
   static constexpr int kServiceLanes = RTB_REFILL_LANES;
+  static constexpr bool kPostpone = RTB_POSTPONE_LEAF != 0;
   uint32_t n;
   unsigned rays;
   const float4* ro;
@@ -731,9 +729,15 @@ struct PathStateRef {
 // warp-uniform branch on it made ptxas spill one more register into the node loop, which cost more than the order wins.
 // kCostMap: a finished path leaves its length in cost[pixel] (atomicMax; the pointer travels in AdaptivePlanes::count): the first
 // samples of a render measure where the long paths are, the rest of the render is scheduled by it (rtb_api.cu, CostOrder).
-template <bool kFromQueue, bool kAdaptive, bool kTileMajor = false, bool kCostMap = false>
+// kTune: per-scene schedule of the traversal loop, chosen by rtb_api.cu from the scene (each measured on the config it is for,
+// profiles/r02_path_kernel_variants.jsonl): 0 default; 1 = speculative leaf postponement (Aila & Laine: a lane that reaches a leaf keeps it
+// for the leaf phase and goes on descending) for trees of spheres only, RTIOW 7.40 -> 7.00 ms - in closed boxes the first leaf's hit would
+// have culled what the speculating lane visits instead (Cornell +9 %); 2 = service phase at 24 waiting lanes instead of 16 for scenes that
+// do not fit the L2 (stress 46.3 -> 44.0 ms per 8 spp: fewer, fuller shading passes between DRAM-latency-bound traversal stretches).
+template <bool kFromQueue, bool kAdaptive, bool kTileMajor = false, bool kCostMap = false, int kTune = 0>
 struct PathIo {
-  static constexpr int kServiceLanes = RTB_PATH_REFILL_LANES;
+  static constexpr int kServiceLanes = kTune == 2 ? 24 : RTB_PATH_REFILL_LANES;
+  static constexpr bool kPostpone = RTB_POSTPONE_LEAF != 0 || kTune == 1;
   uint32_t n;
   unsigned rays;
   const DevScene& s;
@@ -788,7 +792,7 @@ struct PathIo {
   }
 };
 
-template <bool kUseSmem, bool kFromQueue, bool kAdaptive = false, bool kTileMajor = false, bool kCostMap = false>
+template <bool kUseSmem, bool kFromQueue, bool kAdaptive = false, bool kTileMajor = false, bool kCostMap = false, int kTune = 0>
 __global__ void __launch_bounds__(kTraceBlock, RTB_PATH_MIN_BLOCKS) path_kernel(DevScene s, PathQueue q, uint32_t n, uint32_t s0, uint32_t p0,
                                                                                RenderConsts rc, const uint32_t* __restrict__ pixel_order,
                                                                                float* accum, unsigned int* cursor,
@@ -798,9 +802,9 @@ __global__ void __launch_bounds__(kTraceBlock, RTB_PATH_MIN_BLOCKS) path_kernel(
   if (kAdaptive) n = *ad.n_active * ad.chunk_r;  // one work item per (active pixel, sample of the chunk)
 #if RTB_PS_SMEM
   __shared__ uint32_t path_state[6 * kTraceBlock];
-  PathIo<kFromQueue, kAdaptive, kTileMajor, kCostMap> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathStateRef{path_state + threadIdx.x}, ad};
+  PathIo<kFromQueue, kAdaptive, kTileMajor, kCostMap, kTune> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathStateRef{path_state + threadIdx.x}, ad};
 #else
-  PathIo<kFromQueue, kAdaptive, kTileMajor, kCostMap> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathStateRef{PathState{}}, ad};
+  PathIo<kFromQueue, kAdaptive, kTileMajor, kCostMap, kTune> io{n, 0u, s, rc, accum, q, s0, p0, pixel_order, PathStateRef{PathState{}}, ad};
 #endif
   trace_loop<kUseSmem>(s, smem_pairs, smem_stack_base(s, smem_pairs, kUseSmem), io, cursor, cnt);
   const unsigned total = __reduce_add_sync(kFull, io.rays);

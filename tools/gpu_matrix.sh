@@ -1,12 +1,12 @@
 #!/bin/bash
 # The measurement matrix north_star asks for: C1-C5 x N GPUs (this call: N = $1), Msamples/s, Mrays/s, roofline, CPU baseline at N = 1.
-#   gpurun --gpus N -- bash tools/gpu_matrix.sh N   ->   gpurun_out/r02_matrix_nN.jsonl (one bench line per config)
+#   gpurun --gpus N -- bash tools/gpu_matrix.sh N   ->   gpurun_out/r02_matrix_nN.jsonl (one bench line per config; CFGS="rtiow stress" = a subset)
 cd "$GRAFT_REPO_ROOT" || exit 1
 N=${1:-1}
 mkdir -p gpurun_out
 OUT=gpurun_out/r02_matrix_n$N.jsonl
 : > $OUT
-for cfg in rtiow cornell bunny earth stress; do
+for cfg in ${CFGS:-rtiow cornell bunny earth stress}; do
   if [ "$cfg" = stress ]; then K=2; W=3; else K=10; W=3; fi
   if [ "$N" = 1 ]; then
     timeout 900 python bench.py --gpus 1 --steps $K --warmup $W --config $cfg --lean >> $OUT 2> gpurun_out/r02_matrix_n${N}_$cfg.err
