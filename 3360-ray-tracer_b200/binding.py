@@ -20,6 +20,7 @@ RTB_OK, RTB_EINVAL, RTB_ENODEVICE, RTB_ECUDA, RTB_ENOMEM = 0, -1, -2, -3, -4
 PRIM_SPHERE, PRIM_TRIANGLE, PRIM_RECT, PRIM_SUBTREE = 0, 1, 2, 3
 MODE_A, MODE_B = 0, 1
 RENDER_SMEM_TOP, RENDER_KEEP_ACCUM, RENDER_SERIAL, RENDER_WAVEFRONT, RENDER_NO_DRAIN, RENDER_POOL_PATHS, RENDER_COST_ORDER = 1, 2, 4, 8, 16, 32, 64
+RENDER_WIDE4 = 128  # the 4-wide tree (scenes built with RTB_WIDE4=1 in the environment): an experiment, DESIGN.md 3.9
 ADAPT_PIXEL_STATE, ADAPT_LUMINANCE = 0, 1
 EX_SPHERE, EX_TRIANGLE, EX_RECT, EX_BVH_BEGIN, EX_BVH_END, EX_LIST_BEGIN, EX_LIST_END = 0, 1, 2, 10, 11, 12, 13
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_DIFFUSE_LIGHT = 0, 1, 2, 3
@@ -104,7 +105,7 @@ assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 16
 
 # Every symbol include/rtb.h and include/rth.h declare (checked by tests/test_abi.py).
 RTB_SYMBOLS = [
-    "rtb_last_error", "rtb_abi_version", "rtb_tree_compile", "rtb_tree_destroy", "rtb_device_count", "rtb_debug_check_failures", "rtb_init", "rtb_shutdown", "rtb_scene_create",
+    "rtb_last_error", "rtb_abi_version", "rtb_tree_compile", "rtb_tree_destroy", "rtb_tree_info", "rtb_device_count", "rtb_debug_check_failures", "rtb_init", "rtb_shutdown", "rtb_scene_create",
     "rtb_scene_destroy", "rtb_intersect_batch", "rtb_intersect_batch_device", "rtb_render", "rtb_render_device",
     "rtb_render_adaptive", "rtb_render_adaptive_device", "rtb_resolve_counts", "rtb_resolve_counts_device", "rtb_pixel_state_fold", "rtb_render_multi",
     "rtb_resolve_device", "rtb_resolve", "rtb_measure_l2_gbs", "rtb_measure_fp32_tflops", "rtb_measure_fp64_tflops",
@@ -285,6 +286,18 @@ class HostScene:
     @property
     def desc(self) -> RtbSceneDesc:
         return self._lib.rth_scene_desc(self._h).contents
+
+    def tree_info(self) -> dict:
+        """rtb_tree_info of the scene's compiled device tree (host work, no GPU): sizes, stack bounds and the self-check counts."""
+        if not self.desc.compiled:
+            raise RuntimeError("the scene carries no compiled device tree (host_only / device_tree build)")
+        info = (C.c_uint32 * 8)()
+        cuda = self._lib._cuda
+        cuda.rtb_tree_info.argtypes = [C.c_void_p, C.POINTER(C.c_uint32)]
+        if cuda.rtb_tree_info(self.desc.compiled, info) != 0:
+            raise RuntimeError("rtb_tree_info failed")
+        keys = ("pairs", "pair_depth", "pair_prims", "pair_box_escapes", "quads", "quad_stack", "quad_prims", "quad_box_escapes")
+        return dict(zip(keys, (int(v) for v in info)))
 
     def export(self):
         """(prims[n,16], mats[n,8], texs[n,8], image_paths) — the oracle's input."""

@@ -163,7 +163,9 @@ static int CompileTree(const RtbSceneDesc& d, rtbc::Compiled* out) {
     }
     bool rebuild = RTB_TREE_REBUILD_DEFAULT;
     if (const char* e = std::getenv("RTB_TREE_REBUILD")) rebuild = std::atoi(e) != 0;
-    *out = rtbc::Compiler(dd, leaf_max, prim_cost).Run(rebuild);
+    const char* wide = std::getenv("RTB_WIDE4");  // the 4-wide tree next to the pairs (RTB_RENDER_WIDE4; an experiment)
+    *out = rtbc::Compiler(dd, leaf_max, prim_cost).Run(rebuild, wide && std::atoi(wide) != 0);
+    if (out->quad_stack + 2 > (uint32_t)rtb::kStackSize) out->quads.clear();  // RTB_RENDER_WIDE4 is refused for this scene
   } catch (const std::exception& e) {
     return Fail(RTB_EINVAL, std::string("scene compile: ") + e.what());
   }
@@ -373,6 +375,51 @@ int rtb_tree_compile(const RtbSceneDesc* d, RtbCompiledTree** out) {
 }
 void rtb_tree_destroy(RtbCompiledTree* t) { delete t; }
 
+// Walks a compiled tree (pairs: width 2, quads: width 4) from record 0: primitives reachable through leaf descriptors, and
+// child boxes that stick out of the slot box that leads to them by more than 1e-5 relative (boxes of re-split leaves are recomputed
+// from the primitives with a 2e-6 pad, the reference's own carry 1e-6: triangle.h:18-39; anything beyond that is a layout bug).
+static void WalkTree(const std::vector<rtbc::Pair>& rec, int width, uint64_t* prims, uint32_t* escapes) {
+  *prims = 0;
+  *escapes = 0;
+  if (rec.empty()) return;
+  struct Item { uint32_t node; const float* box; };
+  std::vector<Item> todo{{0u, nullptr}};
+  while (!todo.empty()) {
+    const Item it = todo.back();
+    todo.pop_back();
+    for (int k = 0; k < width; ++k) {
+      const rtbc::Pair& p = rec[(size_t)it.node * (width / 2) + k / 2];
+      const uint32_t d = (k & 1) ? p.d1 : p.d0;
+      const float* box = (k & 1) ? p.box1 : p.box0;
+      if (d == rtbc::kEmptyQuadSlot) continue;
+      if (it.box)
+        for (int a = 0; a < 3; ++a)
+          if (box[2 * a] < it.box[2 * a] - 1e-5f * (1.f + std::fabs(it.box[2 * a])) ||
+              box[2 * a + 1] > it.box[2 * a + 1] + 1e-5f * (1.f + std::fabs(it.box[2 * a + 1])))
+            ++*escapes;
+      if (d & rtbc::kLeafBit) *prims += ((d >> 24) & 31u) + 1u;
+      else todo.push_back({d, box});
+    }
+  }
+}
+
+int rtb_tree_info(const RtbCompiledTree* t, uint32_t info[8]) {
+  if (!t || !info) return Fail(RTB_EINVAL, "null argument");
+  uint64_t prims2 = 0, prims4 = 0;
+  uint32_t esc2 = 0, esc4 = 0;
+  WalkTree(t->tree.pairs, 2, &prims2, &esc2);
+  WalkTree(t->tree.quads, 4, &prims4, &esc4);
+  info[0] = (uint32_t)t->tree.pairs.size();
+  info[1] = t->tree.depth;
+  info[2] = (uint32_t)prims2;
+  info[3] = esc2;
+  info[4] = (uint32_t)(t->tree.quads.size() / 2);
+  info[5] = t->tree.quad_stack;
+  info[6] = (uint32_t)prims4;
+  info[7] = esc4;
+  return RTB_OK;
+}
+
 int rtb_debug_check_failures(uint64_t* counts8) {
   if (!counts8) return Fail(RTB_EINVAL, "null argument");
   const bool selftest = counts8[7] == 0x5e1f7e57ull;  // the caller asks for one deliberate violation of class 7 (proves the counting path)
@@ -522,6 +569,8 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
     PUT(s->Put(reinterpret_cast<const float4*>(tree->pairs.data()), 4 * tree->pairs.size(), &v.pairs));
     v.n_pairs = (uint32_t)tree->pairs.size();
     v.n_top_pairs = tree->top_pairs;
+    PUT(s->Put(reinterpret_cast<const float4*>(tree->quads.data()), 4 * tree->quads.size(), &v.quads));
+    v.n_quads = (uint32_t)(tree->quads.size() / 2);
     if (device_build && n_prims > 0) {
       v.n_pairs = n_prims > 1 ? n_prims - 1 : 1;
       built_pairs_off = s->Reserve((size_t)v.n_pairs * 64);
@@ -768,6 +817,9 @@ int rtb_intersect_batch_device(RtbScene* s, const RtbRay* d_rays, size_t n, RtbH
     const size_t smem = s->smem_bytes + kStackSmem;
     const int grid = PersistentGrid(rtb::intersect_batch_kernel<true>, kTraceBlock, smem);
     rtb::intersect_batch_kernel<true><<<grid, kTraceBlock, smem, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->cursor, s->counters);
+  } else if (s->dev.quads && std::getenv("RTB_WIDE4_BATCH")) {  // the 4-wide tree (an experiment: DESIGN.md 3.9)
+    const int grid = PersistentGrid(rtb::intersect_batch_kernel<false, true>, kTraceBlock, kStackSmem);
+    rtb::intersect_batch_kernel<false, true><<<grid, kTraceBlock, kStackSmem, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->cursor, s->counters);
   } else {
     const int grid = PersistentGrid(rtb::intersect_batch_kernel<false>, kTraceBlock, kStackSmem);
     rtb::intersect_batch_kernel<false><<<grid, kTraceBlock, kStackSmem, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->cursor, s->counters);
@@ -944,6 +996,11 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   else if (tile_major && s->arena_bytes > (256u << 20)) tune = 2;
   if (const char* e = std::getenv("RTB_TUNE")) tune = std::atoi(e);
   if (tune == 2 && !tile_major) tune = 0;
+  // RTB_RENDER_WIDE4: the 4-wide tree (a scene created with RTB_WIDE4=1 carries it); RTB_TUNE=12 runs it at 3 CTAs x 80 registers
+  if ((prm->flags & RTB_RENDER_WIDE4) || tune == 4 || tune == 12) {
+    if (!s->dev.quads) return Fail(RTB_EINVAL, "RTB_RENDER_WIDE4: the scene has no 4-wide tree (create it with RTB_WIDE4=1; host-compiled trees only)");
+    if (tune != 12) tune = 4;
+  }
   rcst.spp_max = prm->spp_end - prm->spp_begin;
   rcst.min_samples = ad ? ad->min_samples : 0;
   rcst.criterion = ad ? ad->criterion : 0;
@@ -958,6 +1015,8 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   if (const char* e = std::getenv("RTB_DRAIN_MAX")) drain_max = (uint32_t)std::max(0, std::atoi(e));
   const int path_grid = use_smem ? PersistentGrid(fused ? rtb::path_kernel<true, false> : rtb::path_kernel<true, true>, kTraceBlock, ext_smem)
                                  : PersistentGrid(fused ? rtb::path_kernel<false, false> : rtb::path_kernel<false, true>, kTraceBlock, ext_smem);
+
+  const int wide3_grid = tune == 12 ? PersistentGrid(rtb::path_kernel<false, false, false, true, false, 12>, kTraceBlock, ext_smem) : 0;
 
   Events events;  // destroyed on every return path
   // on request: the pool kernel (64 paths per warp in shared memory, rtb_pool.cuh) instead of one path per lane
@@ -1086,6 +1145,18 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
         else if (cost)
           rtb::path_kernel<false, false, false, false, true><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order,
                                                                                                          d_rgb_sum, w.counts, rc64, s->counters, pl);
+        else if (tune == 4 && !use_smem && tile_major)
+          rtb::path_kernel<false, false, false, true, false, 4><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order,
+                                                                                                            d_rgb_sum, w.counts, rc64, s->counters, pl);
+        else if (tune == 4 && !use_smem)
+          rtb::path_kernel<false, false, false, false, false, 4><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order,
+                                                                                                             d_rgb_sum, w.counts, rc64, s->counters, pl);
+        else if (tune == 12 && !use_smem && tile_major)
+          rtb::path_kernel<false, false, false, true, false, 12><<<wide3_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order,
+                                                                                                              d_rgb_sum, w.counts, rc64, s->counters, pl);
+        else if (tune == 12 && !use_smem)
+          rtb::path_kernel<false, false, false, false, false, 12><<<wide3_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order,
+                                                                                                               d_rgb_sum, w.counts, rc64, s->counters, pl);
         else if (tune == 2 && tile_major)
           rtb::path_kernel<false, false, false, true, false, 2><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order,
                                                                                                             d_rgb_sum, w.counts, rc64, s->counters, pl);

@@ -80,7 +80,12 @@ struct Compiled {
   std::vector<Pair> pairs;  // pairs[0] = the root's children; empty for an empty scene
   uint32_t top_pairs = 0;
   uint32_t depth = 0;       // deepest chain of pairs (stack bound)
+  // 4-wide form of the same tree (Run(.., wide = true); the round-2 experiment of DESIGN.md 3.9): quad q = records
+  // quads[2q], quads[2q + 1] (128 bytes, four child slots); an internal slot's descriptor is a quad index
+  std::vector<Pair> quads;
+  uint32_t quad_stack = 0;  // most entries a traversal of the quads can have on its stack
 };
+constexpr uint32_t kEmptyQuadSlot = 0xfffffffdu;  // descriptor of an unused quad slot (never a leaf: type bits 3; never a quad index)
 
 class Compiler {
  public:
@@ -95,7 +100,7 @@ class Compiler {
   // rebuild = true: ignore the interchange topology and build the device tree from the primitive tables alone with a
   // surface-area heuristic over all three axes (32 bins; every split position for small sets) and the device's costs.
   // The reference's builder bins the longest centroid axis only (bvh.h:232-250) and stops at 4 primitives.
-  Compiled Run(bool rebuild = false) {
+  Compiled Run(bool rebuild = false, bool wide = false) {
     int root = rebuild ? Rebuild() : FromNode(0, 0);
     Compiled out;
     if (root < 0) return out;  // nothing to hit: no pairs, the kernels report a miss for every ray
@@ -109,6 +114,7 @@ class Compiler {
       root = NewInternal(l, r);
     }
     Layout(root, out);
+    if (wide) LayoutWide(root, out);
     return out;
   }
 
@@ -529,6 +535,61 @@ class Compiler {
         SetChild(out.pairs[p], side++, c.box, c.left >= 0 ? pair_of_left_.at(c.left) : c.desc);
       }
     }
+  }
+
+  // The binary tree collapsed to 4-wide nodes: a quad holds a node's two children, the child with the largest box replaced by
+  // ITS two children while slots are free (so a quad's slots are 2-4 descendants that partition the node's primitives).
+  // Quads in depth-first order, slot order irrelevant (the traversal sorts the slots a ray enters by entry distance).
+  void LayoutWide(int root, Compiled& out) {
+    struct Quad { int slot[4]; int n; };
+    auto collapse = [&](int node) {
+      Quad q{{nodes_[node].left, nodes_[node].right, -1, -1}, 2};
+      while (q.n < 4) {
+        int best = -1;
+        float best_area = -1.f;
+        for (int k = 0; k < q.n; ++k)
+          if (nodes_[q.slot[k]].left >= 0 && Area(nodes_[q.slot[k]].box) > best_area) {
+            best = k;
+            best_area = Area(nodes_[q.slot[k]].box);
+          }
+        if (best < 0) break;
+        const int opened = q.slot[best];
+        q.slot[best] = nodes_[opened].left;
+        q.slot[q.n++] = nodes_[opened].right;
+      }
+      return q;
+    };
+    std::vector<Quad> order;
+    std::vector<int> todo{root};
+    IntMap quad_of;
+    while (!todo.empty()) {
+      const int node = todo.back();
+      todo.pop_back();
+      quad_of[node] = static_cast<uint32_t>(order.size());
+      order.push_back(collapse(node));
+      const Quad q = order.back();
+      for (int k = q.n - 1; k >= 0; --k)
+        if (nodes_[q.slot[k]].left >= 0) todo.push_back(q.slot[k]);
+    }
+    if (order.size() >= (1u << 28)) throw std::runtime_error("too many BVH nodes");
+    out.quads.assign(2 * order.size(), Pair{});
+    std::vector<uint32_t> need(order.size(), 0);  // stack entries a traversal below quad q can hold: children come after parents
+    for (size_t p = order.size(); p-- > 0;) {
+      const Quad& q = order[p];
+      uint32_t below = 0;
+      for (int k = 0; k < 4; ++k) {
+        Pair& rec = out.quads[2 * p + k / 2];
+        if (k >= q.n) {
+          SetChild(rec, k & 1, Box{{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}}, kEmptyQuadSlot);
+          continue;
+        }
+        const CNode& c = nodes_[q.slot[k]];
+        if (c.left >= 0) below = std::max(below, need[quad_of.at(q.slot[k])]);
+        SetChild(rec, k & 1, c.box, c.left >= 0 ? quad_of.at(q.slot[k]) : c.desc);
+      }
+      need[p] = static_cast<uint32_t>(q.n - 1) + below;
+    }
+    out.quad_stack = need.empty() ? 0 : need[0];
   }
 
   const RtbSceneDesc& d_;

@@ -44,6 +44,8 @@ struct DevScene {
   const int2* image_dim;
   uint32_t n_pairs, n_top_pairs;
   uint32_t n_spheres, n_triangles, n_rects, n_materials, n_textures;  // table sizes: only read by the RTB_CHECKED build
+  uint32_t n_quads;
+  const float4* quads;        // the 4-wide form of the tree, 8 x float4 per quad (RTB_WIDE4 at compile time; nullptr otherwise)
 };
 
 // RTB_CHECKED build (make VARIANT=checked EXTRA=-DRTB_CHECKED): every index the kernels form is compared with the size of what
@@ -65,6 +67,7 @@ __device__ unsigned long long g_check_fail[kChkClasses];
 
 constexpr uint32_t kNoHit = 0xffffffffu;
 constexpr uint32_t kLeafBit = 0x80000000u;
+constexpr uint32_t kEmptyQuadSlot = 0xfffffffdu;  // unused slot of a quad (rtb_compile.h)
 constexpr int kStackSize = 64;  // the reference's own bound (bvh.h:80); rtb_scene_create enforces it
 constexpr float kU = 5.9604645e-8f;  // 2^-24, FP32 unit roundoff
 

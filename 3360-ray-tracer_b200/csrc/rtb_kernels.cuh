@@ -150,7 +150,7 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
 #ifdef RTB_COUNTERS
   unsigned n_pairs = 0, n_sph = 0, n_tri = 0, n_rect = 0, n_rays = 0, steps = 0;
 #endif
-  const unsigned long long base_all = (unsigned long long)s.pairs;
+  const unsigned long long base_all = (unsigned long long)(Io::kWide ? s.quads : s.pairs);
   const unsigned long long base_top = kUseSmem ? (unsigned long long)smem_pairs : 0ull;  // generic address of the staged prefix
   const uint32_t n_top = kUseSmem ? s.n_top_pairs : 0u;
 
@@ -235,6 +235,52 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
       pop_or_finish();
     }
 #endif
+  };
+  // Io::kWide: one step through a 4-wide node (rtb_compile.h LayoutWide: two pair records side by side, 128 bytes, `cur` counts quads).
+  // All four boxes are tested, the entered ones sorted by entry distance (a 5-comparator network, misses at +inf), the
+  // nearest is descended, the others pushed far to near.  Half the dependent fetches per ray of the pair loop.
+  auto node_step4 = [&]() {
+    RTB_CHECK(kChkPair, cur < s.n_quads);
+    const unsigned long long addr = base_all + (unsigned long long)cur * 128ull;
+    f32x2 c0[4], c1[4], c2[4], c3[4];
+    ld256_global(addr, c0);
+    ld256_global(addr + 32, c1);
+    ld256_global(addr + 64, c2);
+    ld256_global(addr + 96, c3);
+#ifdef RTB_COUNTERS
+    n_pairs += 2;
+    ++steps;
+#endif
+    const float inf = __int_as_float(0x7f800000);
+    float t0, t1, t2, t3;
+    uint32_t d0 = (uint32_t)c1[2], d1 = (uint32_t)(c1[2] >> 32), d2 = (uint32_t)c3[2], d3 = (uint32_t)(c3[2] >> 32);
+    const bool h0 = slab(r, c0[0], c0[1], c0[2], b.hi, t0);
+    const bool h1 = slab(r, c0[3], c1[0], c1[1], b.hi, t1);
+    const bool h2 = slab(r, c2[0], c2[1], c2[2], b.hi, t2) && d2 != kEmptyQuadSlot;  // slots 0 and 1 are always in use
+    const bool h3 = slab(r, c2[3], c3[0], c3[1], b.hi, t3) && d3 != kEmptyQuadSlot;
+    const int n_hit = (int)h0 + (int)h1 + (int)h2 + (int)h3;
+    t0 = h0 ? t0 : inf; t1 = h1 ? t1 : inf; t2 = h2 ? t2 : inf; t3 = h3 ? t3 : inf;
+#define RTB_CSWAP(ta, da, tb, db)                        \
+  {                                                      \
+    const bool sw = tb < ta;                             \
+    const float tx = sw ? tb : ta, ty = sw ? ta : tb;    \
+    const uint32_t dx = sw ? db : da, dy = sw ? da : db; \
+    ta = tx; tb = ty; da = dx; db = dy;                  \
+  }
+    RTB_CSWAP(t0, d0, t1, d1)
+    RTB_CSWAP(t2, d2, t3, d3)
+    RTB_CSWAP(t0, d0, t2, d2)
+    RTB_CSWAP(t1, d1, t3, d3)
+    RTB_CSWAP(t1, d1, t2, d2)
+#undef RTB_CSWAP
+    if (n_hit > 3) stack.push(sp, d3);
+    sp += n_hit > 3 ? 1 : 0;
+    if (n_hit > 2) stack.push(sp, d2);
+    sp += n_hit > 2 ? 1 : 0;
+    if (n_hit > 1) stack.push(sp, d1);
+    sp += n_hit > 1 ? 1 : 0;
+    if (n_hit > 0) cur = d0;
+    else pop_or_finish();
   };
   // one primitive of the leaf this lane stands at; the descriptor itself is the loop counter
   auto leaf_step = [&](uint32_t type) {
@@ -322,6 +368,10 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
         at_node = !(cur & kLeafBit);
       }
       }
+      if (Io::kWide) {
+        if (at_node) node_step4();
+        continue;
+      }
       if (at_node) node_step();
 #pragma unroll
       for (int extra = 1; extra < RTB_NODE_STEPS_PER_VOTE; ++extra)  // more steps on the same vote: less vote overhead
@@ -354,9 +404,11 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
 }
 
 // ---- seam 2: RayIntegrator::IntersectBatch (src/integrator/cpu_ray_integrator.h:18-46) --------
-struct BatchIo {
+template <bool kWide_ = false>
+struct BatchIoT {
   static constexpr int kServiceLanes = RTB_REFILL_LANES;
   static constexpr bool kPostpone = RTB_POSTPONE_LEAF != 0;
+  static constexpr bool kWide = kWide_;
   uint32_t n;
   unsigned rays;
   const float4* in;
@@ -383,12 +435,14 @@ __device__ __forceinline__ uint32_t* smem_stack_base(const DevScene& s, float4* 
   return reinterpret_cast<uint32_t*>(smem + (use_top ? 4 * (size_t)s.n_top_pairs : 0));
 }
 
-template <bool kUseSmem>
+using BatchIo = BatchIoT<false>;
+
+template <bool kUseSmem, bool kWide = false>
 __global__ void __launch_bounds__(kTraceBlock, RTB_TRACE_MIN_BLOCKS) intersect_batch_kernel(DevScene s, const float4* __restrict__ rays, uint32_t n,
                                                               RtbHit* __restrict__ hits, unsigned int* cursor, HitCounters* cnt) {
   extern __shared__ float4 smem_pairs[];
   if (kUseSmem) stage_top(s, smem_pairs);
-  BatchIo io{n, 0u, rays, hits, &s};
+  BatchIoT<kWide> io{n, 0u, rays, hits, &s};
   trace_loop<kUseSmem>(s, smem_pairs, smem_stack_base(s, smem_pairs, kUseSmem), io, cursor, cnt);
 }
 
@@ -502,6 +556,7 @@ __global__ void generate_kernel(PathQueue q, uint32_t q_offset, uint32_t count, 
 struct ExtendIo {
   static constexpr int kServiceLanes = RTB_REFILL_LANES;
   static constexpr bool kPostpone = RTB_POSTPONE_LEAF != 0;
+  static constexpr bool kWide = false;
   uint32_t n;
   unsigned rays;
   const float4* ro;
@@ -738,6 +793,7 @@ template <bool kFromQueue, bool kAdaptive, bool kTileMajor = false, bool kCostMa
 struct PathIo {
   static constexpr int kServiceLanes = kTune == 2 ? 24 : RTB_PATH_REFILL_LANES;
   static constexpr bool kPostpone = RTB_POSTPONE_LEAF != 0 || kTune == 1;
+  static constexpr bool kWide = (kTune & 4) != 0;  // 4: the 4-wide tree (DevScene.quads), 12: the same at 3 CTAs x 80 registers
   uint32_t n;
   unsigned rays;
   const DevScene& s;
@@ -793,7 +849,7 @@ struct PathIo {
 };
 
 template <bool kUseSmem, bool kFromQueue, bool kAdaptive = false, bool kTileMajor = false, bool kCostMap = false, int kTune = 0>
-__global__ void __launch_bounds__(kTraceBlock, RTB_PATH_MIN_BLOCKS) path_kernel(DevScene s, PathQueue q, uint32_t n, uint32_t s0, uint32_t p0,
+__global__ void __launch_bounds__(kTraceBlock, kTune == 12 ? 3 : RTB_PATH_MIN_BLOCKS) path_kernel(DevScene s, PathQueue q, uint32_t n, uint32_t s0, uint32_t p0,
                                                                                RenderConsts rc, const uint32_t* __restrict__ pixel_order,
                                                                                float* accum, unsigned int* cursor,
                                                                                unsigned long long* ray_count, HitCounters* cnt, AdaptivePlanes ad) {

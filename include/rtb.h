@@ -209,6 +209,8 @@ typedef struct RtbRenderParams {
 #define RTB_RENDER_NO_DRAIN 16u    /* wavefront mode: do not hand the last few live paths to the path kernel */
 #define RTB_RENDER_COST_ORDER 64u  /* cost-ordered schedule: the first samples measure where the long paths are, the rest of the render starts with
                                       those tiles (three overlapping launches).  Same image; measured slower than one launch */
+#define RTB_RENDER_WIDE4 128u      /* traverse the 4-wide form of the tree (only scenes created with RTB_WIDE4=1 in the environment carry it;
+                                      RTB_EINVAL otherwise).  A measured experiment, not the default: DESIGN.md 3.9 */
 #define RTB_RENDER_POOL_PATHS 32u  /* the pool kernel (64 paths per warp in shared memory, traversal and shading decoupled: csrc/rtb_pool.cuh)
                                       instead of the default persistent kernel (one path per lane, shaded in place: path_kernel).  Same paths, same
                                       image; measured 16-58 % slower (profiles/r02_pool_vs_lane_ab.jsonl) - kept as the evidence */
@@ -270,6 +272,10 @@ int rtb_shutdown(void);
  * at a time. */
 int rtb_tree_compile(const RtbSceneDesc* desc, RtbCompiledTree** out);
 void rtb_tree_destroy(RtbCompiledTree* tree);
+/* Host only.  info = { pairs, deepest chain of pairs, primitives reachable through the pairs' leaves, child boxes outside their
+ * parent slot by more than 1e-5 relative (0 in a valid tree), quads (0 unless compiled with RTB_WIDE4=1), stack bound of the quad
+ * traversal, primitives reachable through the quads, child boxes outside their parent slot }. */
+int rtb_tree_info(const RtbCompiledTree* tree, uint32_t info[8]);
 
 int rtb_scene_create(const RtbSceneDesc* desc, RtbScene** out);
 int rtb_scene_destroy(RtbScene* scene);
