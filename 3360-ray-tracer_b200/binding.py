@@ -22,6 +22,7 @@ MODE_A, MODE_B = 0, 1
 RENDER_SMEM_TOP, RENDER_KEEP_ACCUM, RENDER_SERIAL, RENDER_WAVEFRONT, RENDER_NO_DRAIN, RENDER_POOL_PATHS, RENDER_COST_ORDER = 1, 2, 4, 8, 16, 32, 64
 RENDER_WIDE4 = 128  # the 4-wide tree (scenes built with RTB_WIDE4=1 in the environment): an experiment, DESIGN.md 3.9
 ADAPT_PIXEL_STATE, ADAPT_LUMINANCE = 0, 1
+STATIC_BATCH_MAX = 65536  # RTB_STATIC_BATCH_MAX: most rays of one rtb_intersect_batch_static call
 EX_SPHERE, EX_TRIANGLE, EX_RECT, EX_BVH_BEGIN, EX_BVH_END, EX_LIST_BEGIN, EX_LIST_END = 0, 1, 2, 10, 11, 12, 13
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_DIFFUSE_LIGHT = 0, 1, 2, 3
 TEX_SOLID, TEX_CHECKER, TEX_IMAGE = 0, 1, 2
@@ -106,7 +107,7 @@ assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 16
 # Every symbol include/rtb.h and include/rth.h declare (checked by tests/test_abi.py).
 RTB_SYMBOLS = [
     "rtb_last_error", "rtb_abi_version", "rtb_tree_compile", "rtb_tree_destroy", "rtb_tree_info", "rtb_device_count", "rtb_debug_check_failures", "rtb_init", "rtb_shutdown", "rtb_scene_create",
-    "rtb_scene_destroy", "rtb_intersect_batch", "rtb_intersect_batch_device", "rtb_render", "rtb_render_device",
+    "rtb_scene_destroy", "rtb_intersect_batch", "rtb_intersect_batch_static", "rtb_intersect_batch_device", "rtb_render", "rtb_render_device",
     "rtb_render_adaptive", "rtb_render_adaptive_device", "rtb_resolve_counts", "rtb_resolve_counts_device", "rtb_pixel_state_fold", "rtb_render_multi",
     "rtb_resolve_device", "rtb_resolve", "rtb_measure_l2_gbs", "rtb_measure_fp32_tflops", "rtb_measure_fp64_tflops",
 ]
@@ -412,6 +413,14 @@ class DeviceScene:
         rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
         hits = np.zeros(rays.shape[0], HIT_DTYPE)
         _check(self._lib, self._lib.rtb_intersect_batch(self._h, _ptr(rays), rays.shape[0], _ptr(hits)))
+        return hits
+
+    def intersect_static(self, rays: np.ndarray) -> np.ndarray:
+        """rtb_intersect_batch_static: seam 2 without any allocation on the device (at most STATIC_BATCH_MAX rays)."""
+        rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+        hits = np.zeros(rays.shape[0], HIT_DTYPE)
+        self._lib.rtb_intersect_batch_static.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        _check(self._lib, self._lib.rtb_intersect_batch_static(self._h, _ptr(rays), rays.shape[0], _ptr(hits)))
         return hits
 
     def intersect_device(self, d_rays_ptr: int, n: int, d_hits_ptr: int, stream: int = 0):

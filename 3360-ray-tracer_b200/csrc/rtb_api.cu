@@ -830,6 +830,64 @@ int rtb_intersect_batch_device(RtbScene* s, const RtbRay* d_rays, size_t n, RtbH
   return RTB_OK;
 }
 
+// ---- rtb_intersect_batch_static: seam 2 for callers that must not allocate ------------------------------------------------
+// The scratch of the closest-hit kernels - the persistent threads' work cursor and the device copies of the caller's host
+// buffers - lives in ONE file-scope device array instead of cudaMalloc'ed memory.  Every GPU that loads the library holds
+// these 3 MiB + 256 bytes until the process exits.  Layout: [cursor, 256 bytes][RtbRay x MAX][RtbHit x MAX].
+constexpr size_t kStaticBatchMax = RTB_STATIC_BATCH_MAX;
+constexpr size_t kStaticRaysOff = 256, kStaticHitsOff = kStaticRaysOff + kStaticBatchMax * sizeof(RtbRay);
+constexpr size_t kStaticBatchBytes = kStaticHitsOff + kStaticBatchMax * sizeof(RtbHit);
+static __device__ __align__(256) unsigned char g_static_batch[kStaticBatchBytes];
+
+// In host code `g_static_batch` is only a stand-in for the symbol: the device address is asked for once per device, with that
+// device current (each device has its own copy of the array), and cached.
+constexpr int kMaxStaticDevices = 64;
+static std::mutex g_static_mu;
+static unsigned char* g_static_ptr[kMaxStaticDevices] = {};
+static int StaticBatchScratch(int device, unsigned char** out) {
+  if (device < 0 || device >= kMaxStaticDevices) return Fail(RTB_EINVAL, "rtb_intersect_batch_static: device index beyond 63");
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_ptr[device]) {
+    int current = -1;
+    RTB_CUDA(cudaGetDevice(&current));
+    if (current != device) return Fail(RTB_EINVAL, "rtb_intersect_batch_static: the scene's device is not the current device");
+    void* p = nullptr;
+    RTB_CUDA(cudaGetSymbolAddress(&p, g_static_batch));
+    if (!p) return Fail(RTB_ECUDA, "rtb_intersect_batch_static: cudaGetSymbolAddress returned no address");
+    g_static_ptr[device] = static_cast<unsigned char*>(p);
+  }
+  *out = g_static_ptr[device];
+  return RTB_OK;
+}
+
+int rtb_intersect_batch_static(RtbScene* s, const RtbRay* rays, size_t n, RtbHit* hits) {
+  if (!s || (!rays && n) || (!hits && n)) return Fail(RTB_EINVAL, "null argument");
+  if (n > kStaticBatchMax)
+    return Fail(RTB_EINVAL, "rtb_intersect_batch_static: " + std::to_string(n) + " rays exceed RTB_STATIC_BATCH_MAX (" + std::to_string(kStaticBatchMax) +
+                                "): split the batch or use rtb_intersect_batch");
+  if (n == 0) return RTB_OK;
+  int rc = EnsureInit();
+  if (rc != RTB_OK) return rc;
+  RTB_TRY(CheckSceneDevice(s));
+  unsigned char* scratch = nullptr;
+  RTB_TRY(StaticBatchScratch(s->device, &scratch));
+  unsigned int* cursor = reinterpret_cast<unsigned int*>(scratch);
+  RtbRay* d_rays = reinterpret_cast<RtbRay*>(scratch + kStaticRaysOff);
+  RtbHit* d_hits = reinterpret_cast<RtbHit*>(scratch + kStaticHitsOff);
+  cudaStream_t st = g_stream;
+  // the array keeps the last call's contents: the cursor must start at zero; rays [0, n) are overwritten, hits [0, n) are all written
+  RTB_CUDA(cudaMemsetAsync(cursor, 0, 8, st));
+  RTB_CUDA(cudaMemcpyAsync(d_rays, rays, n * sizeof(RtbRay), cudaMemcpyHostToDevice, st));
+  const float4* rays4 = reinterpret_cast<const float4*>(d_rays);
+  const int grid = PersistentGrid(rtb::intersect_batch_kernel<false>, kTraceBlock, kStackSmem);
+  rtb::intersect_batch_kernel<false><<<grid, kTraceBlock, kStackSmem, st>>>(s->dev, rays4, (uint32_t)n, d_hits, cursor, s->counters);
+  rtb::exact_t_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->counters);
+  RTB_CUDA(cudaGetLastError());
+  RTB_CUDA(cudaMemcpyAsync(hits, d_hits, n * sizeof(RtbHit), cudaMemcpyDeviceToHost, st));
+  RTB_CUDA(cudaStreamSynchronize(st));
+  return RTB_OK;
+}
+
 int rtb_intersect_batch(RtbScene* s, const RtbRay* rays, size_t n, RtbHit* hits) {
   if (!s || (!rays && n) || (!hits && n)) return Fail(RTB_EINVAL, "null argument");
   if (n == 0) return RTB_OK;

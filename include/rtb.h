@@ -289,6 +289,16 @@ int rtb_scene_destroy(RtbScene* scene);
  * Non-finite components are outside it too: the reference lets NaN through its comparisons and reports hits at t = NaN
  * (sphere.h:34-45); here the call returns normally and every ray reports a miss or some primitive of the scene. */
 int rtb_intersect_batch(RtbScene* scene, const RtbRay* rays, size_t n, RtbHit* hits);
+/* The same call for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  Host buffers in and out like
+ * rtb_intersect_batch and the same answers bit for bit, but the call performs NO cudaMalloc / cudaFree / allocating library call:
+ * the kernels' scratch (work cursor, device copies of rays and hits) is a file-scope device array of RTB_STATIC_BATCH_MAX
+ * entries - 3 MiB + 256 bytes that every GPU which loads the library holds until the process exits.  n > RTB_STATIC_BATCH_MAX is
+ * refused with RTB_EINVAL.  All calls on one GPU share that array (it keeps the last call's contents; the call clears what must
+ * start at zero): calls that overlap on the same GPU - from several host threads - race and must be serialised by the caller.
+ * The scene itself is created beforehand (rtb_scene_create allocates); returns after the hits are in `hits`. */
+#define RTB_STATIC_BATCH_MAX 65536u
+int rtb_intersect_batch_static(RtbScene* scene, const RtbRay* rays, size_t n, RtbHit* hits);
 /* same, device buffers, asynchronous on `stream` (a cudaStream_t, 0 = library stream). */
 int rtb_intersect_batch_device(RtbScene* scene, const RtbRay* d_rays, size_t n, RtbHit* d_hits,
                                void* stream);
