@@ -1,7 +1,8 @@
 """The 4-wide tree experiment (rtb_compile.h LayoutWide, trace_loop node_step4): C1-C4 rendered with the pair loop and
 with the quad loop (4 CTAs x 64 registers, and 3 x 80), at the configuration's spp and at 1 spp (the launch floor), the images and ray
 counts compared, and the closest hits of a ray batch through both trees compared bit for bit.
-  python tools/gpu_wide4.py [--configs bunny,rtiow,cornell,earth] [--reps 5]
+  python tools/gpu_wide4.py [--configs bunny,rtiow,cornell,earth] [--reps 5] [--spp 12,13: these sample counts instead (what one of 8 GPUs
+  renders in the spp split of section 6), no hit comparison]
 With RTB_LIB=librtb200_counters.so the per-ray step counts are printed as well (timings are then meaningless)."""
 import json, os, sys
 from pathlib import Path
@@ -16,6 +17,9 @@ def main():
     names, reps = ["bunny", "rtiow", "cornell", "earth"], 5
     if "--configs" in args:
         i = args.index("--configs"); names = args[i + 1].split(","); del args[i:i + 2]
+    spp_list = None
+    if "--spp" in args:
+        i = args.index("--spp"); spp_list = [int(v) for v in args[i + 1].split(",")]; del args[i:i + 2]
     if "--reps" in args:
         i = args.index("--reps"); reps = int(args[i + 1]); del args[i:i + 2]
     os.environ["RTB_WIDE4"] = "1"  # read when the tree is compiled
@@ -42,7 +46,7 @@ def main():
         print(json.dumps({"config": name, "hits_identical": bool(same), "rays": int(len(rays) + len(bounce)),
                           "hit_fraction": float((h2["prim_id"] >= 0).mean()), "tree": hs.tree_info()}), flush=True)
         ref_img = None
-        for spp in (cfg["spp"], 1):
+        for spp in spp_list or (cfg["spp"], 1):
             for label, tune in (("pairs", None), ("quads 4x64", "4"), ("quads 3x80", "12")):
                 os.environ.pop("RTB_TUNE", None)
                 if tune:
