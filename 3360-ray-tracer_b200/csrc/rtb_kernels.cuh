@@ -64,6 +64,12 @@ __device__ __forceinline__ void stage_top(const DevScene& s, float4* smem_pairs)
 #define RTB_NODE_EXIT_NUM 1
 #define RTB_NODE_EXIT_DEN 4
 #endif
+#ifndef RTB_PREFETCH_FAR
+#define RTB_PREFETCH_FAR 0
+#endif
+#ifndef RTB_PREFETCH_LEAF
+#define RTB_PREFETCH_LEAF 0
+#endif
 #ifndef RTB_NODE_STEPS_PER_VOTE
 #define RTB_NODE_STEPS_PER_VOTE 2
 #endif
@@ -214,6 +220,12 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
     const bool hl = slab(r, bx[0], bx[1], bx[2], b.hi, tl);
     const bool hr = slab(r, bx[3], bx[4], bx[5], b.hi, tr);
     const uint32_t dl = dd.x, dr = dd.y;
+#if RTB_PREFETCH_FAR  // experiment: the record of a pushed internal child is asked for now, popped many steps later
+    if (hl && hr) {
+      const uint32_t far = tl <= tr ? dr : dl;
+      if (!(far & kLeafBit)) asm volatile("prefetch.global.L1 [%0];" ::"l"(base_all + (unsigned long long)far * 64ull));
+    }
+#endif
 #if RTB_NODE_BRANCHLESS && RTB_STACK_SENTINEL && !defined(RTB_COUNTERS)
     // straight-line form: selects and predicated stack accesses instead of a three-way branch (each arm of which
     // costs a BRA and its own arrival at the reconvergence barrier)
@@ -233,6 +245,13 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
       cur = hl ? dl : dr;
     } else {
       pop_or_finish();
+    }
+#endif
+#if RTB_PREFETCH_LEAF  // experiment: a lane that arrives at a triangle leaf waits for the leaf phase - fetch its first triangle meanwhile
+    if ((cur >> 29) == 4u + RTB_PRIM_TRIANGLE) {
+      const unsigned long long ta = (unsigned long long)(s.triangle_f + 3 * (size_t)desc_first(cur));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(ta));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(ta + 32));
     }
 #endif
   };
