@@ -123,6 +123,13 @@ void FreeFused(RenderCtx* s) {
 
 }  // namespace
 
+// Device-built scenes of at most this many primitives are rendered without the tree (trace_loop's flat loop: every lane tests every
+// primitive in lock step); host-built ones when the reference's tree is a single leaf.  profiles/r02_flat_loop_ab.jsonl, DESIGN.md 3.9.
+#ifndef RTB_FLAT_MAX_PRIMS
+#define RTB_FLAT_MAX_PRIMS 16
+#endif
+constexpr uint32_t kFlatMaxPrims = RTB_FLAT_MAX_PRIMS;
+
 // shared memory of the traversal kernels besides the staged top of the tree: the stack columns
 constexpr size_t kStackSmem = (size_t)rtb::kSmemStack * rtb::kTraceBlock * sizeof(uint32_t);
 
@@ -205,6 +212,7 @@ struct RtbScene {
   unsigned int* cursor = nullptr;  // persistent-thread work cursor + shade output counter (2 words)
   size_t smem_bytes = 0;
   int device = 0;
+  bool flat_ok = false;  // rendered without the tree (set by rtb_scene_create)
   size_t Reserve(size_t bytes) {
     const size_t off = (arena_bytes + 255) & ~(size_t)255;
     arena_bytes = off + bytes;
@@ -541,6 +549,10 @@ int rtb_scene_create(const RtbSceneDesc* d, RtbScene** out) {
   rtb::DevScene& v = s->dev;
   const bool device_build = (d->flags & RTB_SCENE_DEVICE_BUILD) != 0;
   const uint32_t n_prims = d->n_spheres + d->n_triangles + d->n_rects;
+  // The flat loop (trace_loop, Io::kFlat) renders this scene when the reference's own tree is ONE leaf - its Bvh::Hit then tests every
+  // primitive (bvh.h:84-116; Cornell: 9 primitives in a leaf the SAH refused to split, earth: 4) - or when there is no interchange tree
+  // and the scene has a handful of primitives.
+  s->flat_ok = n_prims > 0 && (device_build ? n_prims <= kFlatMaxPrims : (d->nodes && d->n_nodes >= 1 && d->nodes[0].b > 0 && n_prims <= RTB_MAX_LEAF));
   size_t built_pairs_off = 0;
 #define PUT(expr)            \
   do {                       \
@@ -817,6 +829,10 @@ int rtb_intersect_batch_device(RtbScene* s, const RtbRay* d_rays, size_t n, RtbH
     const size_t smem = s->smem_bytes + kStackSmem;
     const int grid = PersistentGrid(rtb::intersect_batch_kernel<true>, kTraceBlock, smem);
     rtb::intersect_batch_kernel<true><<<grid, kTraceBlock, smem, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->cursor, s->counters);
+  } else if ((s->flat_ok && !std::getenv("RTB_TREE_BATCH")) ||
+             (std::getenv("RTB_FLAT_BATCH") && s->dev.n_spheres + s->dev.n_triangles + s->dev.n_rects <= 4096u)) {  // no tree: every primitive
+    const int grid = PersistentGrid(rtb::intersect_batch_kernel<false, false, true>, kTraceBlock, kStackSmem);
+    rtb::intersect_batch_kernel<false, false, true><<<grid, kTraceBlock, kStackSmem, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->cursor, s->counters);
   } else if (s->dev.quads && std::getenv("RTB_WIDE4_BATCH")) {  // the 4-wide tree (an experiment: DESIGN.md 3.9)
     const int grid = PersistentGrid(rtb::intersect_batch_kernel<false, true>, kTraceBlock, kStackSmem);
     rtb::intersect_batch_kernel<false, true><<<grid, kTraceBlock, kStackSmem, st>>>(s->dev, rays4, (uint32_t)n, d_hits, s->cursor, s->counters);
@@ -1041,6 +1057,9 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   rcst.mode = prm->mode;
   rcst.spp_begin = prm->spp_begin;
   rcst.n_pixels = n_pixels;
+  rcst.div_width = rtb::make_fast_div((uint32_t)cam->width);
+  rcst.div_pixels = rtb::make_fast_div(n_pixels);
+  rcst.div_count = rtb::make_fast_div(1u);
   // Work-item order of the persistent path kernel (rtb_kernels.cuh, generate_sample_tiled): tile-major keeps the GPU on one small
   // image region at a time, which pays when the scene does not fit the L1s (bunny C3 -3.7 %, stress C5 -3 % and 4x less DRAM
   // traffic) and costs 2-4 % when it does (Cornell, earth: 99 % L1 hit rate either way).  RTB_WORK_ORDER=tile|sample overrides.
@@ -1048,12 +1067,18 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   if (const char* e = std::getenv("RTB_WORK_ORDER")) tile_major = e[0] == 't';
   rcst.tile_major = tile_major ? 1 : 0;
   // Per-scene schedule of the traversal loop (PathIo::kTune, rtb_kernels.cuh): speculative leaf postponement for trees of spheres only,
-  // a later service phase for scenes that do not fit the L2.  RTB_TUNE=0|1|2 overrides.
+  // a later service phase for scenes that do not fit the L2, no tree at all for a handful of primitives.  RTB_TUNE=0|1|2|3 overrides.
   int tune = 0;
   if (s->dev.n_triangles == 0 && s->dev.n_rects == 0 && s->dev.n_spheres >= 64) tune = 1;
   else if (tile_major && s->arena_bytes > (256u << 20)) tune = 2;
+  // scenes of a handful of primitives: the flat loop (trace_loop, Io::kFlat) instead of the tree - Cornell, earth
+  const uint32_t n_prims_all = s->dev.n_spheres + s->dev.n_triangles + s->dev.n_rects;
+  if (s->flat_ok) tune = 3;
   if (const char* e = std::getenv("RTB_TUNE")) tune = std::atoi(e);
   if (tune == 2 && !tile_major) tune = 0;
+  if ((tune == 3 || tune == 11) && (n_prims_all == 0 || n_prims_all > 4096u)) tune = 0;  // RTB_TUNE=3 on a large scene would run for minutes
+  if (tune == 3 || tune == 11) tile_major = false;
+  rcst.tile_major = tile_major ? 1 : 0;
   // RTB_RENDER_WIDE4: the 4-wide tree (a scene created with RTB_WIDE4=1 carries it); RTB_TUNE=12 runs it at 3 CTAs x 80 registers
   if ((prm->flags & RTB_RENDER_WIDE4) || tune == 4 || tune == 12) {
     if (!s->dev.quads) return Fail(RTB_EINVAL, "RTB_RENDER_WIDE4: the scene has no 4-wide tree (create it with RTB_WIDE4=1; host-compiled trees only)");
@@ -1074,8 +1099,16 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   const int path_grid = use_smem ? PersistentGrid(fused ? rtb::path_kernel<true, false> : rtb::path_kernel<true, true>, kTraceBlock, ext_smem)
                                  : PersistentGrid(fused ? rtb::path_kernel<false, false> : rtb::path_kernel<false, true>, kTraceBlock, ext_smem);
 
+  const int flat_grid = tune == 3    ? PersistentGrid(rtb::path_kernel<false, false, false, false, false, 3>, kTraceBlock, ext_smem)
+                        : tune == 11 ? PersistentGrid(rtb::path_kernel<false, false, false, false, false, 11>, kTraceBlock, ext_smem)
+                                     : 0;
   const int wide3_grid = tune == 12 ? PersistentGrid(rtb::path_kernel<false, false, false, true, false, 12>, kTraceBlock, ext_smem) : 0;
 
+  rtb::LoopMismatch* dbg_mismatch = nullptr;
+  if (!fused && std::getenv("RTB_DEBUG_FLAT_VS_TREE") && n_prims_all <= 4096u) {
+    RTB_CUDA(cudaMalloc(reinterpret_cast<void**>(&dbg_mismatch), sizeof(rtb::LoopMismatch)));
+    RTB_CUDA(cudaMemset(dbg_mismatch, 0, sizeof(rtb::LoopMismatch)));
+  }
   Events events;  // destroyed on every return path
   // on request: the pool kernel (64 paths per warp in shared memory, rtb_pool.cuh) instead of one path per lane
   const bool use_pool = fused && !use_smem && ((prm->flags & RTB_RENDER_POOL_PATHS) || std::getenv("RTB_POOL_PATHS"));
@@ -1168,7 +1201,7 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
           rtb::path_kernel<true, false, true><<<grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, 0u, 0u, 0u, rcst, ctx->pixel_order,
                                                                                      d_rgb_sum, w.counts, rc64, s->counters, pl);
         else
-          rtb::path_kernel<false, false, true><<<grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, 0u, 0u, 0u, rcst, ctx->pixel_order,
+          (tune == 3 ? rtb::path_kernel<false, false, true, false, false, 3> : rtb::path_kernel<false, false, true>)<<<grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, 0u, 0u, 0u, rcst, ctx->pixel_order,
                                                                                       d_rgb_sum, w.counts, rc64, s->counters, pl);
         rtb::adaptive_replay_kernel<<<(n_g + 255) / 256, 256, 0, w.stream>>>(rcst, d_rgb_sum, pl, list[(pass + 1) & 1] + p0, cnt + ((pass + 1) & 1));
         launches += 2;
@@ -1184,6 +1217,7 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
       while (sa < sb) {
         const uint32_t cnt = std::min(spp_per_launch, sb - sa);
         const uint32_t chunk = n_pixels * cnt, s0 = sa, p0 = tile_major ? cnt : 0u;
+        rcst.div_count = rtb::make_fast_div(cnt);  // kernel parameters are copied at launch
         RTB_CUDA(cudaMemsetAsync(w.counts, 0, 4, w.stream));
         auto* rc64 = reinterpret_cast<unsigned long long*>(w.counts + 2);
         rtb::AdaptivePlanes pl = planes;
@@ -1215,6 +1249,12 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
         else if (tune == 12 && !use_smem)
           rtb::path_kernel<false, false, false, false, false, 12><<<wide3_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order,
                                                                                                                d_rgb_sum, w.counts, rc64, s->counters, pl);
+        else if (tune == 3 && !use_smem)
+          rtb::path_kernel<false, false, false, false, false, 3><<<flat_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order,
+                                                                                                             d_rgb_sum, w.counts, rc64, s->counters, pl);
+        else if (tune == 11 && !use_smem)
+          rtb::path_kernel<false, false, false, false, false, 11><<<flat_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order,
+                                                                                                              d_rgb_sum, w.counts, rc64, s->counters, pl);
         else if (tune == 2 && tile_major)
           rtb::path_kernel<false, false, false, true, false, 2><<<path_grid, kTraceBlock, ext_smem, w.stream>>>(s->dev, rtb::PathQueue{}, chunk, s0, p0, rcst, order,
                                                                                                             d_rgb_sum, w.counts, rc64, s->counters, pl);
@@ -1317,7 +1357,7 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
             rtb::path_kernel<true, true><<<path_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, 0u, 0u, rcst, ctx->pixel_order, d_rgb_sum,
                                                                                w.counts, rc64, s->counters, planes);
           else
-            rtb::path_kernel<false, true><<<path_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, 0u, 0u, rcst, ctx->pixel_order, d_rgb_sum,
+            (tune == 3 ? rtb::path_kernel<false, true, false, false, false, 3> : rtb::path_kernel<false, true>)<<<path_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, 0u, 0u, rcst, ctx->pixel_order, d_rgb_sum,
                                                                                 w.counts, rc64, s->counters, planes);
           if (serial) RTB_CUDA(cudaEventRecord(d1, ws));
           if (trace_iters) std::fprintf(stderr, "[rtb drain] %u paths\n", w.live);
@@ -1342,8 +1382,24 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
       if (serial) RTB_CUDA(cudaEventRecord(ek[1], ws));
       if (use_smem)
         rtb::extend_kernel<true><<<ext_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, w.hit_t, w.hit_ref, w.counts, s->counters);
+      else if (tune == 3)
+        rtb::extend_kernel<false, true><<<ext_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, w.hit_t, w.hit_ref, w.counts, s->counters);
       else
         rtb::extend_kernel<false><<<ext_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, w.hit_t, w.hit_ref, w.counts, s->counters);
+      if (dbg_mismatch && !use_smem) {  // RTB_DEBUG_FLAT_VS_TREE: the OTHER loop on the same queue, hits compared (debugging aid, allocates)
+        float* t_b = nullptr;
+        uint32_t* ref_b = nullptr;
+        RTB_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&t_b), (size_t)w.live * 4, ws));
+        RTB_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&ref_b), (size_t)w.live * 4, ws));
+        RTB_CUDA(cudaMemsetAsync(w.counts, 0, 4, ws));
+        if (tune == 3)
+          rtb::extend_kernel<false><<<ext_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, t_b, ref_b, w.counts, s->counters);
+        else
+          rtb::extend_kernel<false, true><<<ext_grid, kTraceBlock, ext_smem, ws>>>(s->dev, w.q[w.cur], w.live, t_b, ref_b, w.counts, s->counters);
+        rtb::compare_hits_kernel<<<(w.live + 255) / 256, 256, 0, ws>>>(w.q[w.cur], w.live, w.hit_t, w.hit_ref, t_b, ref_b, dbg_mismatch);
+        RTB_CUDA(cudaFreeAsync(t_b, ws));
+        RTB_CUDA(cudaFreeAsync(ref_b, ws));
+      }
       if (serial) RTB_CUDA(cudaEventRecord(ek[2], ws));
       rtb::shade_kernel<<<(w.live + 255) / 256, 256, 0, ws>>>(s->dev, w.q[w.cur], w.live, w.hit_t, w.hit_ref, w.q[w.cur ^ 1], w.counts + 1, d_rgb_sum, rcst);
       if (serial) RTB_CUDA(cudaEventRecord(ek[3], ws));
@@ -1364,6 +1420,16 @@ static int RenderImpl(RtbScene* s, const RtbCamera* cam, const RtbRenderParams* 
   RTB_CUDA(cudaEventRecord(ev1, st));
   RTB_CUDA(cudaEventSynchronize(ev1));
   RTB_CUDA(cudaGetLastError());
+  if (dbg_mismatch) {  // one JSON line per disagreeing ray on stderr
+    rtb::LoopMismatch h;
+    RTB_CUDA(cudaDeviceSynchronize());
+    RTB_CUDA(cudaMemcpy(&h, dbg_mismatch, sizeof(h), cudaMemcpyDeviceToHost));
+    cudaFree(dbg_mismatch);
+    std::fprintf(stderr, "{\"flat_vs_tree_mismatches\": %llu, \"rays\": %llu}\n", h.count, (unsigned long long)rays);
+    for (unsigned k = 0; k < 16 && k < h.count; ++k)
+      std::fprintf(stderr, "{\"mismatch_ray\": [%.9g, %.9g, %.9g, %.9g, %.9g, %.9g, %.9g, %.9g], \"ref_main\": %u, \"ref_other\": %u}\n", h.ro[k].x, h.ro[k].y,
+                   h.ro[k].z, h.ro[k].w, h.rd[k].x, h.rd[k].y, h.rd[k].z, h.rd[k].w, h.ref_a[k], h.ref_b[k]);
+  }
   for (Wave* wp : waves) {  // rays traced inside the path kernel (it bounces on the device)
     unsigned long long c[2] = {0, 0};
     RTB_CUDA(cudaMemcpy(c, wp->counts + 2, 16, cudaMemcpyDeviceToHost));

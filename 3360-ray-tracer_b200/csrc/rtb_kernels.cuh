@@ -14,6 +14,34 @@ struct PathQueue {
   uint2* meta;   // global sample index, bounce count
 };
 
+// Division of a 32-bit index by a number that is fixed per launch (image width, pixels per image, samples per launch): the
+// round-up multiply-shift form of Granlund & Montgomery, exact for every 32-bit numerator, 5 instructions instead of the ~20
+// of the emulated 32-bit division (ncu: the divisions of the sample generator were 3 % of Cornell's warp instructions).
+#ifndef RTB_FAST_DIV
+#define RTB_FAST_DIV 1
+#endif
+struct FastDiv {
+  uint32_t m, s1, s2, d;
+};
+inline FastDiv make_fast_div(uint32_t d) {  // d >= 1
+  uint32_t l = 0;
+  while (l < 32u && (1ull << l) < (unsigned long long)d) ++l;  // ceil(log2 d)
+  FastDiv f;
+  f.m = (uint32_t)(((1ull << 32) * ((1ull << l) - d)) / d + 1ull);
+  f.s1 = l < 1u ? l : 1u;
+  f.s2 = l ? l - 1u : 0u;
+  f.d = d;
+  return f;
+}
+__device__ __forceinline__ uint32_t fast_div(uint32_t n, const FastDiv& f) {
+#if RTB_FAST_DIV
+  const uint32_t t = __umulhi(f.m, n);
+  return (t + ((n - t) >> f.s1)) >> f.s2;
+#else
+  return n / f.d;
+#endif
+}
+
 struct RenderConsts {
   RtbCamera cam;
   PhiloxKeys round_keys;  // Philox4x32 key schedule of the seed (philox_key_schedule)
@@ -28,6 +56,8 @@ struct RenderConsts {
   int min_samples;
   int criterion;      // RTB_ADAPT_*
   float rel_threshold;
+  FastDiv div_width, div_pixels;  // cam.width, n_pixels
+  FastDiv div_count;              // tile-major launches: the samples per pixel of THIS launch (set per launch)
 };
 
 // Stage the breadth-first top of the tree in shared memory (one copy per CTA per launch).
@@ -372,6 +402,26 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
       continue;
     }
     if (n_trace == 0) break;  // nobody tracing, nothing to hand over, nothing left to claim
+    if (Io::kFlat) {
+      // Scenes of a handful of primitives (Cornell: 9, earth: 4): no tree.  Every lane that holds a ray tests EVERY primitive, all
+      // lanes in lock step - no stack, no votes, no node / leaf alternation - and all of them finish together, so the service
+      // phase (shading) runs on full warps too.  The closest hit is a function of the exact tests and the tie rule only
+      // (rtb_device.cuh), so it is the one the tree gives, bit for bit.
+      const bool tracing = cur < kIdleMark;
+      if (tracing) {  // one loop per primitive type: the type is a compile-time constant inside consider()
+#pragma unroll 1
+        for (uint32_t idx = 0; idx < s.n_spheres; ++idx) consider(s, r, RTB_PRIM_SPHERE, idx, b, cnt);
+#pragma unroll 1
+        for (uint32_t idx = 0; idx < s.n_rects; ++idx) consider(s, r, RTB_PRIM_RECT, idx, b, cnt);
+#pragma unroll 1
+        for (uint32_t idx = 0; idx < s.n_triangles; ++idx) consider(s, r, RTB_PRIM_TRIANGLE, idx, b, cnt);
+#ifdef RTB_COUNTERS
+        n_sph += s.n_spheres; n_rect += s.n_rects; n_tri += s.n_triangles;
+#endif
+      }
+      if (tracing) finish();
+      continue;
+    }
     const int n_act = n_trace;
     // ---- node phase: descend while the descending lanes are the majority
     for (;;) {
@@ -423,11 +473,12 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
 }
 
 // ---- seam 2: RayIntegrator::IntersectBatch (src/integrator/cpu_ray_integrator.h:18-46) --------
-template <bool kWide_ = false>
+template <bool kWide_ = false, bool kFlat_ = false>
 struct BatchIoT {
   static constexpr int kServiceLanes = RTB_REFILL_LANES;
   static constexpr bool kPostpone = RTB_POSTPONE_LEAF != 0;
   static constexpr bool kWide = kWide_;
+  static constexpr bool kFlat = kFlat_;
   uint32_t n;
   unsigned rays;
   const float4* in;
@@ -456,12 +507,12 @@ __device__ __forceinline__ uint32_t* smem_stack_base(const DevScene& s, float4* 
 
 using BatchIo = BatchIoT<false>;
 
-template <bool kUseSmem, bool kWide = false>
+template <bool kUseSmem, bool kWide = false, bool kFlat = false>
 __global__ void __launch_bounds__(kTraceBlock, RTB_TRACE_MIN_BLOCKS) intersect_batch_kernel(DevScene s, const float4* __restrict__ rays, uint32_t n,
                                                               RtbHit* __restrict__ hits, unsigned int* cursor, HitCounters* cnt) {
   extern __shared__ float4 smem_pairs[];
   if (kUseSmem) stage_top(s, smem_pairs);
-  BatchIoT<kWide> io{n, 0u, rays, hits, &s};
+  BatchIoT<kWide, kFlat> io{n, 0u, rays, hits, &s};
   trace_loop<kUseSmem>(s, smem_pairs, smem_stack_base(s, smem_pairs, kUseSmem), io, cursor, cnt);
 }
 
@@ -498,7 +549,8 @@ struct PathState {  // what a path carries besides its ray
 // sample and a 32-bit offset i, so the device never divides 64-bit numbers.
 // Camera::GetRay for global sample `sample` of `pixel`: Philox(pixel, sample, stream -1) -> jitter + lens point.
 __device__ __forceinline__ void camera_ray(const RenderConsts& rc, uint32_t pixel, uint32_t sample, float4& ro, float4& rd, PathState& ps) {
-  const int px = (int)(pixel % (uint32_t)rc.cam.width), py = (int)(pixel / (uint32_t)rc.cam.width);
+  const uint32_t row = fast_div(pixel, rc.div_width);
+  const int px = (int)(pixel - row * (uint32_t)rc.cam.width), py = (int)row;
   const uint4 rnd = philox4x32_10(make_uint4(pixel, sample, 0xffffffffu, 0u), rc.round_keys);
   const RtbCamera& c = rc.cam;
   const float jx = u01(rnd.x) - 0.5f, jy = u01(rnd.y) - 0.5f;
@@ -528,7 +580,8 @@ __device__ __forceinline__ void camera_ray(const RenderConsts& rc, uint32_t pixe
 __device__ __forceinline__ void generate_sample(const RenderConsts& rc, const uint32_t* __restrict__ pixel_order, uint32_t s0, uint32_t p0,
                                                 uint32_t i, float4& ro, float4& rd, PathState& ps) {
   const uint32_t t = p0 + i;  // < 2^31: p0 < n_pixels <= 2^30 and i < 2^30 (host-side chunking)
-  const uint32_t s_local = s0 + t / rc.n_pixels, pl = t % rc.n_pixels;
+  const uint32_t q = fast_div(t, rc.div_pixels);
+  const uint32_t s_local = s0 + q, pl = t - q * rc.n_pixels;
   camera_ray(rc, __ldg(&pixel_order[pl]), (uint32_t)rc.spp_begin + s_local, ro, rd, ps);
 }
 
@@ -545,7 +598,7 @@ __device__ __forceinline__ void generate_sample_tiled(const RenderConsts& rc, co
   const uint32_t full = rc.n_pixels & ~31u, n_full_items = full * cnt;  // < 2^30 (host-side chunking)
   uint32_t pl, sl;
   if (i < n_full_items) {
-    const uint32_t c = i >> 5, tile = c / cnt;
+    const uint32_t c = i >> 5, tile = fast_div(c, rc.div_count);
     sl = c - tile * cnt;
     pl = (tile << 5) | (i & 31u);
   } else {
@@ -572,10 +625,12 @@ __global__ void generate_kernel(PathQueue q, uint32_t q_offset, uint32_t count, 
 }
 
 // ---- extend: Bvh::Hit for every live path (src/geom/bvh.h:71-119) ------------------------------
-struct ExtendIo {
+template <bool kFlat_ = false>
+struct ExtendIoT {
   static constexpr int kServiceLanes = RTB_REFILL_LANES;
   static constexpr bool kPostpone = RTB_POSTPONE_LEAF != 0;
   static constexpr bool kWide = false;
+  static constexpr bool kFlat = kFlat_;
   uint32_t n;
   unsigned rays;
   const float4* ro;
@@ -593,13 +648,37 @@ struct ExtendIo {
   }
 };
 
-template <bool kUseSmem>
+using ExtendIo = ExtendIoT<false>;
+
+template <bool kUseSmem, bool kFlat = false>
 __global__ void __launch_bounds__(kTraceBlock, RTB_TRACE_MIN_BLOCKS) extend_kernel(DevScene s, PathQueue q, uint32_t n, float* __restrict__ hit_t,
                                                      uint32_t* __restrict__ hit_ref, unsigned int* cursor, HitCounters* cnt) {
   extern __shared__ float4 smem_pairs[];
   if (kUseSmem) stage_top(s, smem_pairs);
-  ExtendIo io{n, 0u, q.ro, q.rd, hit_t, hit_ref};
+  ExtendIoT<kFlat> io{n, 0u, q.ro, q.rd, hit_t, hit_ref};
   trace_loop<kUseSmem>(s, smem_pairs, smem_stack_base(s, smem_pairs, kUseSmem), io, cursor, cnt);
+}
+
+// Debugging aid (RTB_DEBUG_FLAT_VS_TREE, wavefront mode): the closest hits of the tree loop and of the flat loop for the same queue,
+// compared entry by entry; the first disagreeing rays are kept for the host to print (tools/gpu_flat_mismatch.py feeds them to the oracle).
+struct LoopMismatch {
+  unsigned long long count;
+  float4 ro[16], rd[16];
+  uint32_t ref_a[16], ref_b[16];
+};
+__global__ void __launch_bounds__(256) compare_hits_kernel(PathQueue q, uint32_t n, const float* __restrict__ t_a, const uint32_t* __restrict__ ref_a,
+                                                           const float* __restrict__ t_b, const uint32_t* __restrict__ ref_b, LoopMismatch* out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  (void)t_a; (void)t_b;  // the float t of an extend is the filter's value unless a contest forced the exact replay: only WHICH primitive counts
+  if (ref_a[i] == ref_b[i]) return;
+  const unsigned long long k = atomicAdd(&out->count, 1ull);
+  if (k < 16ull) {
+    out->ro[k] = q.ro[i];
+    out->rd[k] = q.rd[i];
+    out->ref_a[k] = ref_a[i];
+    out->ref_b[k] = ref_b[i];
+  }
 }
 
 // ---- shade -------------------------------------------------------------------------------------
@@ -813,6 +892,7 @@ struct PathIo {
   static constexpr int kServiceLanes = kTune == 2 ? 24 : RTB_PATH_REFILL_LANES;
   static constexpr bool kPostpone = RTB_POSTPONE_LEAF != 0 || kTune == 1;
   static constexpr bool kWide = (kTune & 4) != 0;  // 4: the 4-wide tree (DevScene.quads), 12: the same at 3 CTAs x 80 registers
+  static constexpr bool kFlat = (kTune & 7) == 3;  // 3: no tree at all - every primitive, all lanes in lock step (scenes of <= 16 primitives); 11: at 3 CTAs x 80 registers
   uint32_t n;
   unsigned rays;
   const DevScene& s;
@@ -868,7 +948,7 @@ struct PathIo {
 };
 
 template <bool kUseSmem, bool kFromQueue, bool kAdaptive = false, bool kTileMajor = false, bool kCostMap = false, int kTune = 0>
-__global__ void __launch_bounds__(kTraceBlock, kTune == 12 ? 3 : RTB_PATH_MIN_BLOCKS) path_kernel(DevScene s, PathQueue q, uint32_t n, uint32_t s0, uint32_t p0,
+__global__ void __launch_bounds__(kTraceBlock, (kTune & 8) ? 3 : RTB_PATH_MIN_BLOCKS) path_kernel(DevScene s, PathQueue q, uint32_t n, uint32_t s0, uint32_t p0,
                                                                                RenderConsts rc, const uint32_t* __restrict__ pixel_order,
                                                                                float* accum, unsigned int* cursor,
                                                                                unsigned long long* ray_count, HitCounters* cnt, AdaptivePlanes ad) {
