@@ -410,11 +410,11 @@ __device__ __forceinline__ void trace_loop(const DevScene& s, const float4* smem
       const bool tracing = cur < kIdleMark;
       if (tracing) {  // one loop per primitive type: the type is a compile-time constant inside consider()
 #pragma unroll 1
-        for (uint32_t idx = 0; idx < s.n_spheres; ++idx) consider(s, r, RTB_PRIM_SPHERE, idx, b, cnt);
+        for (uint32_t idx = 0; idx < s.n_spheres; ++idx) consider<false>(s, r, RTB_PRIM_SPHERE, idx, b, cnt);
 #pragma unroll 1
-        for (uint32_t idx = 0; idx < s.n_rects; ++idx) consider(s, r, RTB_PRIM_RECT, idx, b, cnt);
+        for (uint32_t idx = 0; idx < s.n_rects; ++idx) consider<false>(s, r, RTB_PRIM_RECT, idx, b, cnt);
 #pragma unroll 1
-        for (uint32_t idx = 0; idx < s.n_triangles; ++idx) consider(s, r, RTB_PRIM_TRIANGLE, idx, b, cnt);
+        for (uint32_t idx = 0; idx < s.n_triangles; ++idx) consider<false>(s, r, RTB_PRIM_TRIANGLE, idx, b, cnt);
 #ifdef RTB_COUNTERS
         n_sph += s.n_spheres; n_rect += s.n_rects; n_tri += s.n_triangles;
 #endif
