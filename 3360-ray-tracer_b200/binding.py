@@ -106,7 +106,7 @@ assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 16
 
 # Every symbol include/rtb.h and include/rth.h declare (checked by tests/test_abi.py).
 RTB_SYMBOLS = [
-    "rtb_last_error", "rtb_abi_version", "rtb_tree_compile", "rtb_tree_destroy", "rtb_tree_info", "rtb_device_count", "rtb_debug_check_failures", "rtb_init", "rtb_shutdown", "rtb_scene_create",
+    "rtb_last_error", "rtb_abi_version", "rtb_tree_compile", "rtb_tree_destroy", "rtb_tree_info", "rtb_device_count", "rtb_debug_check_failures", "rtb_debug_fast_div", "rtb_init", "rtb_shutdown", "rtb_scene_create",
     "rtb_scene_destroy", "rtb_intersect_batch", "rtb_intersect_batch_static", "rtb_intersect_batch_device", "rtb_render", "rtb_render_device",
     "rtb_render_adaptive", "rtb_render_adaptive_device", "rtb_resolve_counts", "rtb_resolve_counts_device", "rtb_pixel_state_fold", "rtb_render_multi",
     "rtb_resolve_device", "rtb_resolve", "rtb_measure_l2_gbs", "rtb_measure_fp32_tflops", "rtb_measure_fp64_tflops",
@@ -212,6 +212,8 @@ def load(counters: bool = False) -> "_Product":
     lib.rtb_measure_fp64_tflops.argtypes = [C.c_int, C.POINTER(C.c_float)]
     lib.rtb_init.argtypes = [C.c_int]
     lib.rtb_debug_check_failures.argtypes = [C.c_void_p]
+    lib.rtb_debug_fast_div.argtypes = [C.c_uint32, C.c_uint32]
+    lib.rtb_debug_fast_div.restype = C.c_uint32
     prod = _Product(host, lib)
     _LIBS[key] = prod
     return prod

@@ -428,6 +428,8 @@ int rtb_tree_info(const RtbCompiledTree* t, uint32_t info[8]) {
   return RTB_OK;
 }
 
+uint32_t rtb_debug_fast_div(uint32_t n, uint32_t d) { return d ? rtb::fast_div(n, rtb::make_fast_div(d)) : 0u; }
+
 int rtb_debug_check_failures(uint64_t* counts8) {
   if (!counts8) return Fail(RTB_EINVAL, "null argument");
   const bool selftest = counts8[7] == 0x5e1f7e57ull;  // the caller asks for one deliberate violation of class 7 (proves the counting path)

@@ -33,9 +33,13 @@ inline FastDiv make_fast_div(uint32_t d) {  // d >= 1
   f.d = d;
   return f;
 }
-__device__ __forceinline__ uint32_t fast_div(uint32_t n, const FastDiv& f) {
+__host__ __device__ __forceinline__ uint32_t fast_div(uint32_t n, const FastDiv& f) {
 #if RTB_FAST_DIV
+#ifdef __CUDA_ARCH__
   const uint32_t t = __umulhi(f.m, n);
+#else
+  const uint32_t t = (uint32_t)(((unsigned long long)f.m * n) >> 32);  // the host form, for rtb_debug_fast_div (tests/test_abi.py)
+#endif
   return (t + ((n - t) >> f.s1)) >> f.s2;
 #else
   return n / f.d;

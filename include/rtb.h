@@ -260,6 +260,9 @@ int rtb_device_count(void);
  * the size of what it indexes, clamps the access and counts violations per class on the current device since the library was
  * loaded.  Returns 1 and the eight counters from such a build, 0 (RTB_OK) and zeros from a normal build, < 0 on error. */
 int rtb_debug_check_failures(uint64_t* counts8);
+/* Host only: n / d the way the sample generator of the kernels divides (multiply-shift with per-launch constants, csrc/rtb_kernels.cuh
+ * FastDiv) - exists so that the CPU test suite can check the constants against the hardware division; d == 0 returns 0. */
+uint32_t rtb_debug_fast_div(uint32_t n, uint32_t d);
 /* Bind the calling thread to `device` and create the library's stream on it. */
 int rtb_init(int device);
 int rtb_shutdown(void);

@@ -94,3 +94,19 @@ def test_product_never_imports_the_oracle():
         text = p.read_text(errors="ignore")
         assert "oracle" not in text.replace("for the oracle", "").replace("the oracle", "").replace("oracle export", "").replace("oracle's", "").lower() \
             or "import oracle" not in text and "from oracle" not in text and "liboracle" not in text, p
+
+
+def test_sample_generator_division_is_exact(rt):
+    """FastDiv (csrc/rtb_kernels.cuh): the multiply-shift division of the sample generator against Python's, for the divisors the
+    configurations use (widths, pixel counts, samples per launch), the edges of the 32-bit range and a few thousand random pairs."""
+    import numpy as np
+    lib = rt.load()
+    rng = np.random.default_rng(7)
+    divisors = [1, 2, 3, 5, 7, 31, 32, 33, 44, 100, 200, 256, 450, 533, 562, 675, 800, 1000, 1024, 1200, 2160, 3840, 360000, 426400, 562000, 810000,
+                8294400, (1 << 30) - 1, 1 << 30, (1 << 31) - 1, 1 << 31, (1 << 31) + 1, 0xfffffffe, 0xffffffff] + [int(v) for v in rng.integers(1, 1 << 32, 300)]
+    for d in divisors:
+        ns = [0, 1, d - 1, d, d + 1, 2 * d - 1, 2 * d, 0x7fffffff, 0x80000000, 0xfffffffe, 0xffffffff] + [int(v) for v in rng.integers(0, 1 << 32, 40)]
+        for n in ns:
+            n &= 0xffffffff
+            assert lib.rtb_debug_fast_div(n, d) == n // d, (n, d)
+    assert lib.rtb_debug_fast_div(5, 0) == 0
