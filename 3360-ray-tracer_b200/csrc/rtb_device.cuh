@@ -149,6 +149,9 @@ __device__ __forceinline__ float safe_dir(float d) {
 //   2  the same on the packed FP32 pipe: FADD2 / FMUL2 take (lo, hi) of an axis as one operand and the ray
 //      constant as a broadcast scalar — 6 + 6 instructions per pair step and 6 registers fewer than form 0
 //   3  form 0 as 6 FFMA2 with (b_lo, b_hi) as a register pair
+#ifndef RTB_FLAT_UNIFORM_AXIS
+#define RTB_FLAT_UNIFORM_AXIS 0  // 1: flat loop with one warp-uniform branch on the rect's axis instead of per-lane selects - measured SLOWER (Cornell 34.6 -> 36.5 ms)
+#endif
 #ifndef RTB_SLAB_BCAST
 #define RTB_SLAB_BCAST 1  // 0: packs built outside the asm (the compiler hoists them into register pairs: +6 registers, measured slower)
 #endif
@@ -421,13 +424,12 @@ __device__ __forceinline__ int sphere_filter(const DevScene& s, uint32_t idx, co
   return kHit;
 }
 
-// Rect: FP32 throughout (rect.h:19-40).  |t - t^| <= (u|k| + u|k-o_k|)/|d_k| + 3u|t|.
+// The rect test proper for a rect whose axis is known at compile time (kAxis 0..2) or per lane (kAxis < 0, read from the record).
 // kRayInv: take 1 / d_k from the ray's slab constants (live anyway in the tree loops) instead of computing it; the flat loop, where
 // nothing else reads them, computes it (measured: keeping them alive there costs Cornell 7 %).
-template <bool kRayInv = true>
-__device__ __forceinline__ int rect_filter(const DevScene& s, uint32_t idx, const TravRay& r, float thi, float& t_out, float& e_out) {
-  const float4 q0 = __ldg(&s.rect_f[2 * (size_t)idx]), q1 = __ldg(&s.rect_f[2 * (size_t)idx + 1]);  // (k,a0,a1,b0) (b1,axis,mat,-)
-  const int axis = __float_as_int(q1.y);
+template <bool kRayInv, int kAxis>
+__device__ __forceinline__ int rect_test(const TravRay& r, const float4 q0, const float4 q1, float thi, float& t_out, float& e_out) {
+  const int axis = kAxis >= 0 ? kAxis : __float_as_int(q1.y);
   const float ok = axis == 0 ? r.ox : axis == 1 ? r.oy : r.oz, dk = axis == 0 ? r.dx : axis == 1 ? r.dy : r.dz;
   const float oa = axis == 0 ? r.oy : r.ox, da = axis == 0 ? r.dy : r.dx;
   const float ob = axis == 2 ? r.oy : r.oz, db = axis == 2 ? r.dy : r.dz;
@@ -448,6 +450,23 @@ __device__ __forceinline__ int rect_filter(const DevScene& s, uint32_t idx, cons
   e_out = et;
   const bool inside = a >= a0 + sa0 && a <= a1 - sa1 && b >= b0 + sb0 && b <= b1 - sb1 && t - et > r.tmin && t + et < r.tmax;
   return inside ? kHit : kUnsure;
+}
+
+// Rect: FP32 throughout (rect.h:19-40).  |t - t^| <= (u|k| + u|k-o_k|)/|d_k| + 3u|t|.
+// kRayInv = true: the tree loops (every lane stands at its own rect: the axis is selected per lane).  false: the flat loop, where all
+// lanes test the SAME rect - the axis is warp-uniform, one branch picks the body specialised for it (no selects).
+template <bool kRayInv = true>
+__device__ __forceinline__ int rect_filter(const DevScene& s, uint32_t idx, const TravRay& r, float thi, float& t_out, float& e_out) {
+  const float4 q0 = __ldg(&s.rect_f[2 * (size_t)idx]), q1 = __ldg(&s.rect_f[2 * (size_t)idx + 1]);  // (k,a0,a1,b0) (b1,axis,mat,-)
+  if (kRayInv) return rect_test<true, -1>(r, q0, q1, thi, t_out, e_out);
+#if RTB_FLAT_UNIFORM_AXIS
+  const int axis = __float_as_int(q1.y);
+  if (axis == 0) return rect_test<false, 0>(r, q0, q1, thi, t_out, e_out);
+  if (axis == 1) return rect_test<false, 1>(r, q0, q1, thi, t_out, e_out);
+  return rect_test<false, 2>(r, q0, q1, thi, t_out, e_out);
+#else
+  return rect_test<false, -1>(r, q0, q1, thi, t_out, e_out);
+#endif
 }
 
 __device__ __forceinline__ uint32_t rank_of(const DevScene& s, uint32_t ref) {
